@@ -1,0 +1,150 @@
+/*
+ * b200step.h — C ABI of libb200step.so: the sm_100a kernels behind the data-parallel training
+ * step of the reference's task.py (hot loop task.py:303-312).
+ *
+ * The reference has no FFI of its own (it is one Python script that calls torch); each entry
+ * point below names the reference call site whose work it replaces.  Conventions:
+ *   - every function returns 0 on success, non-zero on error; b200_last_error() gives the text;
+ *   - all pointers are DEVICE pointers unless the comment says "host";
+ *   - the library never allocates the caller's data: the host (PyTorch) owns every buffer and
+ *     passes tensor.data_ptr(); work is enqueued on the caller's stream and does not synchronise;
+ *   - matrices are row-major; `ld*` are row strides in ELEMENTS;
+ *   - dtype codes: B200_F32 (fp32 storage, TF32 tensor-core math), B200_BF16 (bf16 storage, fp32 accumulate).
+ */
+#ifndef B200STEP_H_
+#define B200STEP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200_stream_t; /* a cudaStream_t */
+
+#define B200_F32 0
+#define B200_BF16 1
+
+#define B200_FLAG_RELU 1      /* fwd: y = max(y,0);  dgrad: dx *= (act > 0) */
+#define B200_FLAG_ACCUMULATE 2 /* wgrad: dw += ... instead of dw = ... */
+
+/* ---- errors / build info ------------------------------------------------------------------ */
+const char* b200_last_error(void);           /* host string, thread-local */
+int b200_abi_version(void);
+int b200_device_sm_count(int* out_host);     /* SM count of the current device */
+
+/* ---- K-pre: fused batch load + standardise + categorical gather ---------------------------
+ * Replaces the reference's host-side input pipeline for one batch:
+ *   DistributedSampler/DataLoader batching (task.py:260-263: batch b = rows row_idx[cursor*batch + b]),
+ *   transforms.Normalize (task.py:250-251 -> tensor.sub_(mean).div_(std), IEEE fp32 subtract then divide),
+ *   the two H2D copies (task.py:305,307), and the model's embedding lookup + concat.
+ * x_out[b, 0:num_dense]                     = (dense[r] - mean) / std            (bit-exact fp32, RNE to bf16 if x_dtype=BF16)
+ * x_out[b, num_dense + t*dim : +dim]        = tables[t][cat[r,t]]                (bit-exact copy / RNE to bf16)
+ * x_out[b, num_dense + num_cat*dim : ldx]   = 0                                  (K padding for the GEMMs)
+ * y_out[b] = label[r];  idx_out[b,t] = (int32) cat[r,t]  (kept for the embedding backward)
+ * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.
+ */
+int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t* ds_label,
+                    const int64_t* row_idx, const int32_t* cursor,
+                    const float* mean, const float* std, const float* tables,
+                    void* x_out, int64_t* y_out, int32_t* idx_out,
+                    int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
+                    int64_t ldx, int x_dtype, b200_stream_t stream);
+
+/* ---- K-gemm: tcgen05/TMEM linear layers ----------------------------------------------------
+ * M = batch rows, N = out_features, K = in_features for all three.
+ * fwd   (task.py:309, nn.Linear inside model(inputs)):  y[M,N] = act(x[M,K] · w[N,K]^T + bias[N])
+ *        with optional inverted dropout after the activation: keep iff philox(seed,*step,layer,elem) >= p.
+ * dgrad (task.py:311 loss.backward, addmm backward wrt input):
+ *        dx[M,K] = (dy[M,N] · w[N,K]) * (act[M,K] > 0 if RELU) * dscale     (act = the stored layer input)
+ * wgrad (task.py:311, addmm backward wrt weight): dw[N,K] (+)= dy[M,N]^T · x[M,K], fp32 result.
+ * K and ld* must make every row 16-byte aligned (K%4==0 for F32, K%8==0 for BF16; same for N where N is a row length).
+ */
+int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
+                    void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
+                    float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
+                    b200_stream_t stream);
+int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw,
+                      const void* act, int64_t ldact, void* dx, int64_t lddx,
+                      int64_t M, int64_t N, int64_t K, int dtype, int flags, float dscale,
+                      b200_stream_t stream);
+int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx,
+                      float* dw, int64_t lddw, int64_t M, int64_t N, int64_t K, int dtype, int flags,
+                      b200_stream_t stream);
+
+/* ---- K-loss: fused cross-entropy loss + gradient (+ last-layer bias gradient) --------------
+ * Replaces nn.CrossEntropyLoss()(outputs, labels) (task.py:211,310; mean reduction) and its backward
+ * (task.py:311): loss_out[0] = mean_b(logsumexp(z_b) - z_b[y_b]);
+ * dlogits[b,c] = (softmax(z_b)[c] - [c==y_b]) * grad_scale   (grad_scale = 1/(batch*world): DDP's mean, task.py:189)
+ * dbias (nullable) [C] = sum_b dlogits[b,:] as stored (after rounding to dtype), fp32.
+ * scratch: b200_ce_scratch_floats(C) floats of device memory, contents need not be initialised.
+ */
+int64_t b200_ce_scratch_floats(int num_classes);
+int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels,
+                      void* dlogits, int64_t lddl, float* loss_out, float* dbias,
+                      float* scratch, int64_t scratch_floats,
+                      int64_t batch, int num_classes, float grad_scale, int dtype,
+                      b200_stream_t stream);
+
+/* ---- column sum: bias gradients of the hidden layers (task.py:311, addmm backward wrt bias) -
+ * out[N] = sum_m dy[m, :]  (fp32, deterministic two-stage reduction through scratch) */
+int64_t b200_colsum_scratch_floats(int64_t N);
+int b200_colsum(const void* dy, int64_t lddy, float* out, float* scratch, int64_t scratch_floats,
+                int64_t M, int64_t N, int dtype, b200_stream_t stream);
+
+/* ---- K-embbwd: embedding gradient scatter-add (task.py:311; embedding_dense_backward) -------
+ * dtables[t][idx[b,t]][:] += dx[b, num_dense + t*dim : +dim]   (fp32 atomics; dtables must be zeroed by the caller) */
+int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, float* dtables,
+                 int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
+                 int dtype, b200_stream_t stream);
+
+/* ---- K-opt: fused optimizer over the flat parameter buffer ----------------------------------
+ * SGD (torch.optim.SGD, task.py:212-214 + .step() task.py:312; zero_grad task.py:308 is implicit —
+ *      gradients are overwritten by the next backward):
+ *      g' = g + wd*p;  buf = momentum*buf + g'  (buf starts at 0 == torch's first-step clone);  p -= lr*buf
+ * Adam (additive --optimizer adam; torch.optim.Adam semantics, coupled L2): *step is the 0-based count of
+ *      completed steps, the kernel uses t = *step + 1 for the bias corrections.
+ * Hyper-parameters are doubles (python floats) and are rounded to fp32 where torch rounds them.
+ * shadow_bf16 (nullable): bf16 copy of p refreshed for the first n_shadow elements (GEMM operand copy).
+ */
+int b200_sgd_step(float* p, const float* g, float* momentum_buf, void* shadow_bf16,
+                  int64_t n, int64_t n_shadow, double lr, double momentum, double weight_decay,
+                  b200_stream_t stream);
+int b200_adam_step(float* p, const float* g, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                   int64_t n, int64_t n_shadow, double lr, double beta1, double beta2, double eps,
+                   double weight_decay, const int32_t* step, b200_stream_t stream);
+/* fp32 -> bf16 RNE copy (initial shadow weights) */
+int b200_cast_bf16(const float* src, void* dst_bf16, int64_t n, b200_stream_t stream);
+/* zero `bytes` bytes of device memory on the stream (gradient regions that are accumulated with atomics) */
+int b200_zero(void* ptr, int64_t bytes, b200_stream_t stream);
+/* advance the device-side batch cursor (wraps at steps_per_epoch) and the global step counter */
+int b200_advance_step(int32_t* cursor, int32_t* step, int32_t steps_per_epoch, b200_stream_t stream);
+
+/* ---- K-comm: gradient all-reduce (DistributedDataParallel, task.py:189/194) -----------------
+ * NCCL over NVLink; SUM in place on a bucket of the flat fp32 gradient buffer (the 1/world factor is folded
+ * into grad_scale of b200_ce_loss_grad).  unique id: 128 host bytes made on rank 0 and shared by the host
+ * (torch.distributed store) — the counterpart of DDP's process-group bootstrap at task.py:148. */
+int b200_comm_unique_id(void* out_host_128);
+int b200_comm_init(const void* unique_id_host_128, int rank, int world);
+int b200_comm_allreduce_sum(float* buf, int64_t count, b200_stream_t stream);
+int b200_comm_broadcast(float* buf, int64_t count, int root, b200_stream_t stream); /* DDP ctor param sync */
+int b200_comm_destroy(void);
+
+/* ---- streams / events / graphs (host plumbing for the step schedule) ------------------------ */
+int b200_stream_create(b200_stream_t* out_host, int high_priority);
+int b200_stream_destroy(b200_stream_t s);
+int b200_stream_sync(b200_stream_t s);
+int b200_event_create(void** out_host, int timing);
+int b200_event_destroy(void* ev);
+int b200_event_record(void* ev, b200_stream_t s);
+int b200_stream_wait_event(b200_stream_t s, void* ev);
+int b200_event_elapsed_ms(void* start, void* stop, float* out_host);
+int b200_graph_begin(b200_stream_t s);
+int b200_graph_end(b200_stream_t s, void** out_exec_host);
+int b200_graph_launch(void* exec, b200_stream_t s);
+int b200_graph_destroy(void* exec);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200STEP_H_ */

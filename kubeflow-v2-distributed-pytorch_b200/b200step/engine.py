@@ -1,0 +1,355 @@
+"""TrainStep — the schedule of one data-parallel training step on one B200 (one process per GPU).
+
+This is the body of the reference's hot loop (task.py:303-312) re-laid for the GPU:
+
+    task.py:305,307  H2D copies of the batch          -> none: the dataset is resident in HBM; K-pre gathers rows
+    task.py:308      optimizer.zero_grad()            -> none: every gradient is overwritten (or memset) below
+    task.py:309      outputs = model(inputs)          -> K-pre, then one tcgen05 GEMM per Linear (bias/ReLU/dropout fused)
+    task.py:310      loss = criterion(outputs, y)     -> K-loss (loss + dlogits + output-layer bias gradient)
+    task.py:311      loss.backward()  [+ DDP hooks]   -> per layer: dgrad GEMM (ReLU mask fused), wgrad GEMM (split-K, fp32
+                                                         into the flat gradient buffer), column-sum bias gradient, embedding
+                                                         scatter-add; each finished bucket is all-reduced by NCCL on a side
+                                                         stream while the rest of backward keeps running
+    task.py:312      optimizer.step()                 -> one fused SGD/Adam pass over the flat buffers
+
+All kernels are enqueued through the C ABI (libb200step.so).  The steady-state step (full batches) is captured
+once into a CUDA graph and replayed; the per-step variables (batch cursor, step count) live in device memory.
+PyTorch owns the memory and the streams and does nothing else here.
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from .data import TabularDataset
+from .lib import B200Error, get_lib
+from .model import FlatLayout, ModelSpec
+
+
+@dataclasses.dataclass
+class StepConfig:
+    batch_size: int                      # per process, like the reference's --batch_size
+    world: int = 1
+    rank: int = 0
+    precision: str = "bf16"              # "bf16" (bf16 storage, fp32 accumulate/master) | "fp32" (TF32 tensor cores)
+    optimizer: str = "sgd"               # task.py:212-214 | additive "adam"
+    lr: float = 0.1                      # task.py:59
+    momentum: float = 0.9                # task.py:68
+    weight_decay: float = 1e-4           # task.py:70
+    beta1: float = 0.9
+    beta2: float = 0.999
+    eps: float = 1e-8
+    dropout_seed: int = 0
+    use_graph: bool = True
+    overlap_comm: bool = True            # all-reduce buckets on a side stream under the rest of backward
+    first_bucket_bytes: int = 1 << 20    # DDP defaults
+    bucket_cap_bytes: int = 25 << 20
+    keep_logits: bool = False            # keep logits and dlogits in separate buffers (tests)
+
+
+class Communicator:
+    """NCCL communicator living inside libb200step.so (one per process)."""
+
+    def __init__(self, rank: int, world: int, unique_id: bytes):
+        self.rank, self.world = rank, world
+        buf = (torch.frombuffer(bytearray(unique_id), dtype=torch.uint8)).clone()
+        get_lib().comm_init(buf.data_ptr(), rank, world)
+        self._alive = True
+
+    @staticmethod
+    def make_unique_id() -> bytes:
+        buf = torch.zeros(128, dtype=torch.uint8)
+        get_lib().comm_unique_id(buf.data_ptr())
+        return bytes(buf.numpy().tobytes())
+
+    def allreduce_sum(self, t: torch.Tensor, stream: torch.cuda.Stream) -> None:
+        get_lib().comm_allreduce_sum(t.data_ptr(), t.numel(), stream.cuda_stream)
+
+    def broadcast(self, t: torch.Tensor, root: int, stream: torch.cuda.Stream) -> None:
+        get_lib().comm_broadcast(t.data_ptr(), t.numel(), root, stream.cuda_stream)
+
+    def close(self) -> None:
+        if self._alive:
+            get_lib().comm_destroy()
+            self._alive = False
+
+
+class TrainStep:
+    def __init__(self, spec: ModelSpec, init_params: Dict[str, torch.Tensor], dataset: TabularDataset,
+                 row_idx: torch.Tensor, cfg: StepConfig, comm: Optional[Communicator] = None,
+                 device: Optional[torch.device] = None):
+        if not torch.cuda.is_available():
+            raise B200Error("no CUDA device: the B200 training step has no CPU fallback")
+        if cfg.precision not in ("bf16", "fp32"):
+            raise ValueError(f"precision must be bf16 or fp32, got {cfg.precision}")
+        if cfg.optimizer not in ("sgd", "adam"):
+            raise ValueError(f"optimizer must be sgd or adam, got {cfg.optimizer}")
+        if cfg.world > 1 and comm is None:
+            raise ValueError("world > 1 needs a Communicator")
+        self.lib = get_lib()  # raises when libb200step.so is missing
+        self.spec, self.cfg, self.comm = spec, cfg, comm
+        self.dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.layout = FlatLayout(spec)
+        self.dt = torch.bfloat16 if cfg.precision == "bf16" else torch.float32
+        B, dev, lay = cfg.batch_size, self.dev, self.layout
+
+        # ---- dataset (resident in HBM) and this rank's sample order (task.py:260-263)
+        self.ds = dataset.to(dev)
+        self.row_idx = row_idx.to(dev, dtype=torch.int64).contiguous()
+        self.num_samples = int(row_idx.numel())
+        self.steps_per_epoch_full = self.num_samples // B
+        self.tail = self.num_samples - self.steps_per_epoch_full * B
+        if self.steps_per_epoch_full == 0 and self.tail == 0:
+            raise ValueError("empty sample list")
+
+        # ---- flat parameter / gradient / optimizer-state buffers
+        self.p = lay.flatten(init_params).to(dev)
+        self.g = torch.zeros_like(self.p)
+        self.s1 = torch.zeros_like(self.p)                    # SGD momentum buffer | Adam exp_avg
+        self.s2 = torch.zeros_like(self.p) if cfg.optimizer == "adam" else None
+        self.shadow = None
+        if self.dt == torch.bfloat16:
+            self.shadow = torch.zeros(lay.n_shadow, dtype=torch.bfloat16, device=dev)
+        self.wsrc = self.shadow if self.shadow is not None else self.p   # GEMM weight operands
+        self.tables = self.p[lay.tables_offset: lay.tables_offset + max(lay.tables_numel, 1)]
+        self.gtables = self.g[lay.tables_offset: lay.total]
+
+        # ---- activations / gradients (row stride = feature count, K of layer 0 padded)
+        dims = spec.layer_dims
+        self.L = len(dims)
+        self.k0 = spec.in_features_padded
+        self.x0 = torch.zeros(B, self.k0, dtype=self.dt, device=dev)
+        self.acts = [torch.zeros(B, o, dtype=self.dt, device=dev) for (_, o) in dims]  # acts[-1] = logits
+        self.dlogits = torch.zeros_like(self.acts[-1]) if cfg.keep_logits else self.acts[-1]
+        wmax = (max([o for (_, o) in dims[:-1]] + [8]) + 7) // 8 * 8
+        self.dh = [torch.zeros(B, wmax, dtype=self.dt, device=dev) for _ in range(2)]  # ping-pong hidden grads
+        self.dx0 = torch.zeros(B, self.k0, dtype=self.dt, device=dev)
+        self.y = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.idx = torch.zeros(B, max(spec.num_cat, 1), dtype=torch.int32, device=dev)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ce_scratch = torch.empty(ops.ce_scratch_floats(spec.num_classes), dtype=torch.float32, device=dev)
+        self.cs_scratch = torch.empty(ops.colsum_scratch_floats(wmax), dtype=torch.float32, device=dev)
+        self.identity_idx = None  # lazily built for host-fed batches
+
+        # ---- streams / events
+        self.main = torch.cuda.Stream(device=dev)
+        self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.buckets = lay.buckets(cfg.first_bucket_bytes, cfg.bucket_cap_bytes)
+        self._ev_ready = [torch.cuda.Event() for _ in self.buckets]
+        self._ev_done = [torch.cuda.Event() for _ in self.buckets]
+        self.graph = None
+        self.kernels_per_step = 0
+        self.host_steps = 0
+
+        torch.cuda.synchronize(dev)  # allocations/fills above ran on torch's default stream
+        with torch.cuda.stream(self.main):
+            if self.shadow is not None:
+                ops.cast_bf16(self.p[: lay.n_shadow], self.shadow, stream=self.main)
+            if comm is not None and cfg.world > 1:
+                # DDP's constructor broadcast of parameters from rank 0 (task.py:189)
+                comm.broadcast(self.p, 0, self.main)
+                if self.shadow is not None:
+                    ops.cast_bf16(self.p[: lay.n_shadow], self.shadow, stream=self.main)
+        self.main.synchronize()
+
+    # ------------------------------------------------------------------------------------------ helpers
+    def _w(self, li: int) -> torch.Tensor:
+        seg = self.layout.weight(li)
+        return self.wsrc[seg.offset: seg.offset + seg.numel_stored].view(seg.rows, seg.ld)
+
+    def _gw(self, li: int) -> torch.Tensor:
+        seg = self.layout.weight(li)
+        return self.g[seg.offset: seg.offset + seg.numel_stored].view(seg.rows, seg.ld)
+
+    def _b(self, li: int, grad: bool = False) -> torch.Tensor:
+        seg = self.layout.bias(li)
+        return (self.g if grad else self.p)[seg.offset: seg.offset + seg.cols]
+
+    # --------------------------------------------------------------------------------------- the schedule
+    def _enqueue(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
+                 cursor: Optional[torch.Tensor], advance: bool) -> int:
+        """Enqueue one full step on self.main for `batch` rows; returns the number of kernels launched."""
+        spec, cfg, lay, st = self.spec, self.cfg, self.layout, self.main
+        ds = src or self.ds
+        n = 0
+        dims = spec.layer_dims
+        L = self.L
+        # K-pre ------------------------------------------------------------------------------------------
+        ops.preprocess(ds.dense, ds.cat, ds.label, row_idx, cursor, ds.mean, ds.std,
+                       self.tables if spec.num_cat else None, self.x0, self.y, self.idx, batch=batch,
+                       num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
+                       embed_dim=spec.embed_dim, stream=st)
+        n += 1
+        # forward ----------------------------------------------------------------------------------------
+        inp = self.x0
+        for li, (k, o) in enumerate(dims):
+            kk = self.k0 if li == 0 else k
+            last = li == L - 1
+            ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li], M=batch, N=o, K=kk, relu=not last,
+                           dropout_p=0.0 if last else spec.dropout, seed=cfg.dropout_seed, step=self.step_ctr,
+                           layer_id=li, stream=st)
+            n += 1
+            inp = self.acts[li]
+        # loss + dlogits + db_L ---------------------------------------------------------------------------
+        ops.ce_loss_grad(self.acts[-1], self.y, self.dlogits, self.loss, self._b(L - 1, grad=True),
+                         self.ce_scratch, batch=batch, num_classes=spec.num_classes,
+                         grad_scale=1.0 / (batch * cfg.world), stream=st)
+        n += 2
+        # backward ---------------------------------------------------------------------------------------
+        inv_keep = 1.0 / (1.0 - spec.dropout) if spec.dropout > 0 else 1.0
+        bucket_of = {ready: bi for bi, (_, _, ready) in enumerate(self.buckets)}
+        dy = self.dlogits
+        for li in range(L - 1, -1, -1):
+            k, o = dims[li]
+            kk = self.k0 if li == 0 else k
+            x_in = self.x0 if li == 0 else self.acts[li - 1]
+            if li > 0:
+                dx = self.dh[li % 2][:, :kk]
+                ops.linear_dgrad(dy, self._w(li), x_in, dx, M=batch, N=o, K=kk, relu=True, dscale=inv_keep,
+                                 stream=st)
+                n += 1
+            elif spec.num_cat:
+                dx = self.dx0
+                ops.linear_dgrad(dy, self._w(li), None, dx, M=batch, N=o, K=kk, relu=False, stream=st)
+                n += 1
+            else:
+                dx = None
+            ops.linear_wgrad(dy, x_in, self._gw(li), M=batch, N=o, K=kk, stream=st)
+            n += 2  # memset (split-K) + GEMM
+            if li < L - 1:
+                ops.colsum(dy, self._b(li, grad=True), self.cs_scratch, M=batch, N=o, stream=st)
+                n += 2
+            if li in bucket_of:
+                n += self._reduce_bucket(bucket_of[li])
+            dy = dx
+        if spec.num_cat:
+            ops.zero(self.gtables, stream=st)
+            ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, num_dense=spec.num_dense,
+                        num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
+            n += 2
+            if -1 in bucket_of:
+                n += self._reduce_bucket(bucket_of[-1])
+        # join the comm stream, then the optimizer ----------------------------------------------------------
+        if cfg.world > 1 and cfg.overlap_comm:
+            for ev in self._ev_done:
+                st.wait_event(ev)
+        n_shadow = lay.n_shadow if self.shadow is not None else 0
+        if cfg.optimizer == "sgd":
+            ops.sgd_step(self.p, self.g, self.s1, self.shadow, n_shadow=n_shadow, lr=cfg.lr,
+                         momentum=cfg.momentum, weight_decay=cfg.weight_decay, stream=st)
+        else:
+            ops.adam_step(self.p, self.g, self.s1, self.s2, self.shadow, self.step_ctr, n_shadow=n_shadow,
+                          lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
+                          weight_decay=cfg.weight_decay, stream=st)
+        n += 1
+        if advance:
+            ops.advance_step(self.cursor, self.step_ctr, max(self.steps_per_epoch_full, 1), stream=st)
+        else:
+            ops.advance_step(None, self.step_ctr, 1, stream=st)
+        n += 1
+        return n
+
+    def _reduce_bucket(self, bi: int) -> int:
+        """DDP's bucket all-reduce (task.py:189 hooks): SUM over ranks; 1/world is already in grad_scale."""
+        if self.cfg.world <= 1:
+            return 0
+        s, e, _ = self.buckets[bi]
+        if self.cfg.overlap_comm:
+            self._ev_ready[bi].record(self.main)
+            self.comm_stream.wait_event(self._ev_ready[bi])
+            self.comm.allreduce_sum(self.g[s:e], self.comm_stream)
+            self._ev_done[bi].record(self.comm_stream)
+        else:
+            self.comm.allreduce_sum(self.g[s:e], self.main)
+        return 1
+
+    # ---------------------------------------------------------------------------------------- public API
+    def capture(self) -> None:
+        """Capture the steady-state (full-batch) step into a CUDA graph.  One eager step must have run before
+        (it configures the kernels and warms NCCL), which `step()` guarantees."""
+        if self.graph is not None:
+            return
+        import ctypes as C
+
+        self.main.synchronize()
+        self.comm_stream.synchronize()
+        self.lib.graph_begin(self.main.cuda_stream)
+        try:
+            self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
+        finally:
+            out = C.c_void_p()
+            self.lib.graph_end(self.main.cuda_stream, C.byref(out))
+        self.graph = out
+
+    def step(self) -> None:
+        """One optimizer step on the next full batch of this rank (asynchronous; see `loss_value`)."""
+        if self.steps_per_epoch_full == 0:
+            raise B200Error("batch_size larger than this rank's sample count: use step_tail()")
+        if self.cfg.use_graph:
+            if self.host_steps == 0:
+                self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
+            else:
+                if self.graph is None:
+                    self.capture()
+                self.lib.graph_launch(self.graph, self.main.cuda_stream)
+        else:
+            self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
+        self.host_steps += 1
+
+    def step_tail(self) -> None:
+        """The last, partial batch of an epoch (DataLoader drop_last=False, task.py:263): eager launch with the
+        smaller row count; does not move the full-batch cursor."""
+        if self.tail == 0:
+            return
+        off = self.steps_per_epoch_full * self.cfg.batch_size
+        self._enqueue(self.tail, None, self.row_idx[off:], None, False)
+        self.host_steps += 1
+
+    def step_from_host(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> None:
+        """One step on a batch that lives in (pinned) HOST memory: the reference's per-step H2D copies
+        (task.py:305,307) followed by the same device step.  Used for the end-to-end measurement."""
+        B = dense.shape[0]
+        if B > self.cfg.batch_size:
+            raise ValueError("host batch larger than the configured batch size")
+        if self.identity_idx is None:
+            self.identity_idx = torch.arange(self.cfg.batch_size, dtype=torch.int64, device=self.dev)
+            bs = self.cfg.batch_size
+            self._stage = TabularDataset(
+                torch.empty(bs, self.spec.num_dense, dtype=torch.float32, device=self.dev),
+                torch.empty(bs, self.spec.num_cat, dtype=torch.int64, device=self.dev),
+                torch.empty(bs, dtype=torch.int64, device=self.dev), self.ds.mean, self.ds.std)
+        with torch.cuda.stream(self.main):
+            self._stage.dense[:B].copy_(dense, non_blocking=True)
+            self._stage.cat[:B].copy_(cat, non_blocking=True)
+            self._stage.label[:B].copy_(label, non_blocking=True)
+        self._enqueue(B, self._stage, self.identity_idx, None, False)
+        self.host_steps += 1
+
+    def loss_value(self) -> float:
+        """Blocking read of the last step's local mean loss (what `loss` holds at task.py:310)."""
+        self.main.synchronize()
+        return float(self.loss.item())
+
+    def synchronize(self) -> None:
+        self.main.synchronize()
+        self.comm_stream.synchronize()
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """Same keys/shapes as the reference's `model.state_dict()` under DDP (task.py:283/287)."""
+        self.synchronize()
+        return self.layout.unflatten(self.p)
+
+    def grads(self) -> Dict[str, torch.Tensor]:
+        self.synchronize()
+        return self.layout.unflatten(self.g, prefix="")
+
+    def close(self) -> None:
+        self.synchronize()
+        if self.graph is not None:
+            self.lib.graph_destroy(self.graph)
+            self.graph = None

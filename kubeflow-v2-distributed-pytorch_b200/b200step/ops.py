@@ -1,0 +1,128 @@
+"""Tensor-level wrappers over the C ABI: torch tensors in, raw device pointers out.
+
+PyTorch is only the owner of device memory and streams here; every function below enqueues one (or two)
+hand-written sm_100a kernels from libb200step.so on the given stream (default: torch's current stream).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import lib as _l
+from .lib import BF16, F32, FLAG_ACCUMULATE, FLAG_RELU, get_lib, ptr
+
+__all__ = [
+    "dtype_code", "preprocess", "linear_fwd", "linear_dgrad", "linear_wgrad", "ce_loss_grad", "colsum",
+    "emb_bwd", "sgd_step", "adam_step", "cast_bf16", "advance_step", "F32", "BF16", "FLAG_RELU",
+    "FLAG_ACCUMULATE",
+]
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float32:
+        return F32
+    if dt == torch.bfloat16:
+        return BF16
+    raise TypeError(f"unsupported dtype {dt}: the B200 step computes in float32 (TF32) or bfloat16")
+
+
+def _stream(stream) -> int:
+    if stream is None:
+        return torch.cuda.current_stream().cuda_stream
+    if isinstance(stream, torch.cuda.Stream):
+        return stream.cuda_stream
+    return int(stream)
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _l.B200Error("the B200 step has no CPU path: all tensors must be CUDA tensors")
+
+
+def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x_out, y_out, idx_out, *,
+               batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, stream=None):
+    _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out)
+    get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
+                         ptr(std), ptr(tables), ptr(x_out), ptr(y_out), ptr(idx_out), batch, num_dense,
+                         num_cat, table_rows, embed_dim, x_out.stride(0), dtype_code(x_out.dtype),
+                         _stream(stream))
+
+
+def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,
+               step=None, layer_id: int = 0, stream=None):
+    _cuda(x, w, bias, y)
+    get_lib().linear_fwd(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(y), y.stride(0), M, N, K,
+                         dtype_code(x.dtype), FLAG_RELU if relu else 0, float(dropout_p), int(seed),
+                         ptr(step), layer_id, _stream(stream))
+
+
+def linear_dgrad(dy, w, act, dx, *, M: int, N: int, K: int, relu: bool, dscale: float = 1.0, stream=None):
+    _cuda(dy, w, act, dx)
+    get_lib().linear_dgrad(ptr(dy), dy.stride(0), ptr(w), w.stride(0), ptr(act),
+                           act.stride(0) if act is not None else 0, ptr(dx), dx.stride(0), M, N, K,
+                           dtype_code(dy.dtype), FLAG_RELU if relu else 0, float(dscale), _stream(stream))
+
+
+def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False, stream=None):
+    _cuda(dy, x, dw)
+    get_lib().linear_wgrad(ptr(dy), dy.stride(0), ptr(x), x.stride(0), ptr(dw), dw.stride(0), M, N, K,
+                           dtype_code(dy.dtype), FLAG_ACCUMULATE if accumulate else 0, _stream(stream))
+
+
+def ce_scratch_floats(num_classes: int) -> int:
+    return int(get_lib().ce_scratch_floats(num_classes))
+
+
+def ce_loss_grad(logits, labels, dlogits, loss_out, dbias, scratch, *, batch: int, num_classes: int,
+                 grad_scale: float, stream=None):
+    _cuda(logits, labels, dlogits, loss_out, dbias, scratch)
+    get_lib().ce_loss_grad(ptr(logits), logits.stride(0), ptr(labels), ptr(dlogits), dlogits.stride(0),
+                           ptr(loss_out), ptr(dbias), ptr(scratch), scratch.numel(), batch, num_classes,
+                           float(grad_scale), dtype_code(logits.dtype), _stream(stream))
+
+
+def colsum_scratch_floats(n: int) -> int:
+    return int(get_lib().colsum_scratch_floats(n))
+
+
+def colsum(dy, out, scratch, *, M: int, N: int, stream=None):
+    _cuda(dy, out, scratch)
+    get_lib().colsum(ptr(dy), dy.stride(0), ptr(out), ptr(scratch), scratch.numel(), M, N,
+                     dtype_code(dy.dtype), _stream(stream))
+
+
+def emb_bwd(dx, idx, dtables, *, batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int,
+            stream=None):
+    _cuda(dx, idx, dtables)
+    get_lib().emb_bwd(ptr(dx), dx.stride(0), ptr(idx), ptr(dtables), batch, num_dense, num_cat, table_rows,
+                      embed_dim, dtype_code(dx.dtype), _stream(stream))
+
+
+def sgd_step(p, g, buf, shadow, *, n_shadow: int, lr: float, momentum: float, weight_decay: float, stream=None):
+    _cuda(p, g, buf, shadow)
+    get_lib().sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), p.numel(), n_shadow, lr, momentum, weight_decay,
+                       _stream(stream))
+
+
+def adam_step(p, g, m, v, shadow, step, *, n_shadow: int, lr: float, beta1: float, beta2: float, eps: float,
+              weight_decay: float, stream=None):
+    _cuda(p, g, m, v, shadow, step)
+    get_lib().adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), n_shadow, lr, beta1, beta2,
+                        eps, weight_decay, ptr(step), _stream(stream))
+
+
+def cast_bf16(src, dst, stream=None):
+    _cuda(src, dst)
+    get_lib().cast_bf16(ptr(src), ptr(dst), src.numel(), _stream(stream))
+
+
+def advance_step(cursor, step, steps_per_epoch: int, stream=None):
+    _cuda(cursor, step)
+    get_lib().advance_step(ptr(cursor), ptr(step), steps_per_epoch, _stream(stream))
+
+
+def zero(t, stream=None):
+    _cuda(t)
+    get_lib().zero(ptr(t), t.numel() * t.element_size(), _stream(stream))

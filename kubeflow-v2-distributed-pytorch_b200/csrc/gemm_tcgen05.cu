@@ -1,0 +1,472 @@
+// gemm_tcgen05.cu — K-gemm: the linear layers of the step as tcgen05/TMEM GEMMs (sm_100a only).
+//
+// One persistent, warp-specialised kernel template covers the three contractions of nn.Linear
+// (reference call sites: forward task.py:309, backward task.py:311):
+//   fwd   D[batch,N]   = X[batch,K] · W[N,K]^T      A K-major,  B K-major   epilogue: +bias, ReLU, dropout
+//   dgrad D[batch,K]   = dY[batch,N] · W[N,K]       A K-major,  B MN-major  epilogue: *dscale, ReLU mask
+//   wgrad D[N,K]       = dY[batch,N]^T · X[batch,K] A MN-major, B MN-major  epilogue: fp32 store / split-K red.add
+// Operands are staged by TMA into 128B-swizzled shared-memory tiles, multiplied by single-thread
+// tcgen05.mma (UMMA 128 x 256 x {16 bf16 | 8 tf32}) into double-buffered TMEM accumulators, and drained
+// by four epilogue warps with tcgen05.ld while the next tile's MMAs run.
+//
+// Roles (256 threads): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator, warps4-7 = epilogue.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_N = 256;
+constexpr int GEMM_THREADS = 256;
+constexpr int A_TILE_BYTES = BLOCK_M * 128;  // 128 rows (or 128-byte swizzle rows) per stage
+constexpr int B_TILE_BYTES = BLOCK_N * 128;
+constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;  // 48 KiB
+constexpr int NUM_STAGES = 4;                              // 192 KiB ring
+constexpr int NUM_ACC = 2;                                 // TMEM accumulator double buffer (2 x 256 columns)
+constexpr int GEMM_SMEM_BYTES = NUM_STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+
+struct GemmParams {
+  int M, N;          // D is M x N
+  int k_blocks;      // ceil(contraction / BLOCK_K)
+  int m_tiles, n_tiles, splits, kb_per_split;
+  void* out;
+  long long ldo;
+  const float* bias;
+  const void* act;
+  long long ldact;
+  float dscale;
+  int flags;
+  float dropout_p;
+  unsigned long long seed;
+  const int* step;
+  int layer_id;
+};
+
+// ---- UMMA descriptors (bit layout: PTX ISA "tcgen05 matrix/instruction descriptor") ------------
+// shared-memory matrix descriptor, 128-byte swizzle, version 1 (Blackwell)
+// layout_type 2 = SWIZZLE_128B (16-byte atoms); 1 = SWIZZLE_128B_BASE32B (32-byte atoms), the only layout the
+// tensor core accepts for MN-major 32-bit (tf32) operands.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type = 2) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version
+  d |= (uint64_t)layout_type << 61;
+  return d;
+}
+// instruction descriptor: fp32 accumulate, A/B format bf16(1) or tf32(2), majors, N>>3, M>>4
+__host__ __device__ constexpr uint32_t make_idesc(int fmt, int a_mn, int b_mn, int m, int n) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)a_mn << 15) |
+         ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+template <int kTf32, bool kAMN, bool kBMN, int kEpi>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const GemmParams p) {
+  constexpr int ESIZE = kTf32 ? 4 : 2;
+  constexpr int BLOCK_K = 128 / ESIZE;          // one 128-byte swizzle row of K (K-major) / BLOCK_K rows (MN-major)
+  constexpr int UMMA_K = 32 / ESIZE;            // 16 (bf16) or 8 (tf32)
+  constexpr int EPR = 128 / ESIZE;              // elements per 128-byte row
+  constexpr int MN_BOX_BYTES = BLOCK_K * 128;   // one TMA box of an MN-major operand: BLOCK_K rows x 128 B
+  constexpr uint32_t MN_SBO = kTf32 ? 512 : 1024;   // swizzle atom height: 4 rows (32B atoms) / 8 rows (16B atoms)
+  constexpr uint32_t MN_LAYOUT = kTf32 ? 1 : 2;
+  constexpr uint32_t IDESC = make_idesc(kTf32 ? 2 : 1, kAMN, kBMN, BLOCK_M, BLOCK_N);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES);
+  uint64_t* full_bar = bars;                       // [NUM_STAGES]
+  uint64_t* empty_bar = bars + NUM_STAGES;         // [NUM_STAGES]
+  uint64_t* acc_full = bars + 2 * NUM_STAGES;      // [NUM_ACC]
+  uint64_t* acc_empty = acc_full + NUM_ACC;        // [NUM_ACC]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + NUM_ACC);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < NUM_STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < NUM_ACC; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, NUM_ACC * BLOCK_N);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int total = tiles * p.splits;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int tile = w % tiles, split = w / tiles;
+        const int m0 = (tile / p.n_tiles) * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_TILE_BYTES;
+          if constexpr (!kAMN) {
+            tma_load_2d(sa, &tmA, &full_bar[s], kb * BLOCK_K, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / EPR; ++j)
+              tma_load_2d(sa + j * MN_BOX_BYTES, &tmA, &full_bar[s], m0 + j * EPR, kb * BLOCK_K);
+          }
+          if constexpr (!kBMN) {
+            tma_load_2d(sb, &tmB, &full_bar[s], kb * BLOCK_K, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / EPR; ++j)
+              tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], n0 + j * EPR, kb * BLOCK_K);
+          }
+          if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+        const int split = w / tiles;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+        const int a = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&acc_empty[a], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * BLOCK_N;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          const uint32_t sb = sa + A_TILE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            // K-major: advance 32 B inside the swizzle row; MN-major: advance UMMA_K rows of 128 B
+            // (MN-major: LBO = next 128-byte MN atom = next TMA box, SBO = next group of 8 (bf16) / 4 (tf32) K rows)
+            const uint64_t ad = kAMN ? make_smem_desc(sa + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT)
+                                     : make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t bd = kBMN ? make_smem_desc(sb + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT)
+                                     : make_smem_desc(sb + k * 32, 16, 1024);
+            umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs retire
+          if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&acc_full[a]);  // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    int it = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+      const int tile = w % tiles;
+      const int m0 = (tile / p.n_tiles) * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
+      const int a = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(&acc_full[a], aph);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        if constexpr (kEpi == EPI_WGRAD) {
+          float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
+          const bool atomic = (p.splits > 1) || (p.flags & B200_FLAG_ACCUMULATE);
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (col0 + j < p.N) {
+              if (atomic) {
+                red_add_v4(o + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                           __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              } else {
+                *reinterpret_cast<uint4*>(o + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              }
+            }
+          }
+        } else {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if constexpr (kEpi == EPI_FWD) {
+            if (p.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+            }
+            if (p.flags & B200_FLAG_RELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+            }
+            if (p.dropout_p > 0.0f) {
+              // keep iff u32 >= p * 2^32; counter = linear element index / 4, key = (seed, layer, step)
+              const uint32_t thresh = (uint32_t)fminf(p.dropout_p * 4294967296.0f, 4294967040.0f);
+              const float inv_keep = 1.0f / (1.0f - p.dropout_p);
+              const uint32_t stepv = p.step ? (uint32_t)(*p.step) : 0u;
+              const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32) ^ stepv);
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const unsigned long long e = (unsigned long long)row * (unsigned long long)p.N + (col0 + j);
+                const uint4 r = philox4x32_10(
+                    make_uint4((uint32_t)(e >> 2), (uint32_t)(e >> 34), (uint32_t)p.layer_id, 0u), key);
+                f[j + 0] = (r.x >= thresh) ? f[j + 0] * inv_keep : 0.0f;
+                f[j + 1] = (r.y >= thresh) ? f[j + 1] * inv_keep : 0.0f;
+                f[j + 2] = (r.z >= thresh) ? f[j + 2] * inv_keep : 0.0f;
+                f[j + 3] = (r.w >= thresh) ? f[j + 3] * inv_keep : 0.0f;
+              }
+            }
+          } else {  // EPI_DGRAD
+            if (p.dscale != 1.0f) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] *= p.dscale;
+            }
+            if ((p.flags & B200_FLAG_RELU) && p.act != nullptr) {
+              if constexpr (kTf32) {
+                const float* ar = reinterpret_cast<const float*>(p.act) + (long long)row * p.ldact + col0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  if (col0 + j < p.N) {
+                    const float4 h = *reinterpret_cast<const float4*>(ar + j);
+                    f[j + 0] = h.x > 0.f ? f[j + 0] : 0.f;
+                    f[j + 1] = h.y > 0.f ? f[j + 1] : 0.f;
+                    f[j + 2] = h.z > 0.f ? f[j + 2] : 0.f;
+                    f[j + 3] = h.w > 0.f ? f[j + 3] : 0.f;
+                  }
+                }
+              } else {
+                const uint16_t* ar = reinterpret_cast<const uint16_t*>(p.act) + (long long)row * p.ldact + col0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                  if (col0 + j < p.N) {
+                    const uint4 h = *reinterpret_cast<const uint4*>(ar + j);
+                    const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                      f[j + 2 * t + 0] = bf16_lo(hw[t]) > 0.f ? f[j + 2 * t + 0] : 0.f;
+                      f[j + 2 * t + 1] = bf16_hi(hw[t]) > 0.f ? f[j + 2 * t + 1] : 0.f;
+                    }
+                  }
+                }
+              }
+            }
+          }
+          // store in the operand dtype
+          if constexpr (kTf32) {
+            float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              if (col0 + j < p.N)
+                *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          } else {
+            uint16_t* o = reinterpret_cast<uint16_t*>(p.out) + (long long)row * p.ldo + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8)
+              if (col0 + j < p.N)
+                *reinterpret_cast<uint4*>(o + j) =
+                    make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
+                               pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[a]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, NUM_ACC * BLOCK_N);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !sym) {
+    set_error("cudaGetDriverEntryPoint(cuTensorMapEncodeTiled) failed: %s", cudaGetErrorString(e));
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+// 2-D row-major tensor [outer, inner] with row stride ld (elements); box = box_inner x box_outer, 128B swizzle.
+// mn_major operands in fp32 use the 32-byte-atom flavour of the 128B swizzle (see make_smem_desc).
+static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
+                     uint32_t box_inner, uint32_t box_outer, bool mn_major = false) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return 1;
+  const uint64_t es = tf32 ? 4 : 2;
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "GEMM operand %p is not 16-byte aligned", ptr);
+  B200_REQUIRE((ld * es) % 16 == 0, "GEMM operand row stride %llu elements is not a multiple of 16 bytes",
+               (unsigned long long)ld);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * es};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu)",
+               (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld);
+  return 0;
+}
+
+template <int kTf32, bool kAMN, bool kBMN, int kEpi>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  auto kern = gemm_kernel<kTf32, kAMN, kBMN, kEpi>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    configured = true;
+  }
+  const int total = p.m_tiles * p.n_tiles * p.splits;
+  const int grid = total < sm_count() ? total : sm_count();
+  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int check_dims(int64_t M, int64_t N, int64_t K, int dtype) {
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "GEMM dims must be positive (M=%lld N=%lld K=%lld)", (long long)M,
+               (long long)N, (long long)K);
+  B200_REQUIRE(M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "GEMM dims must fit int32");
+  const int v = dtype == B200_F32 ? 4 : 8;
+  B200_REQUIRE(N % v == 0 && K % v == 0, "N=%lld and K=%lld must be multiples of %d for dtype %d", (long long)N,
+               (long long)K, v, dtype);
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
+                               void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
+                               float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
+                               b200_stream_t stream) {
+  if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "dropout_p=%f out of [0,1)", dropout_p);
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;
+  CUtensorMap ta, tb;
+  if (int r = make_tmap(&ta, tf32, x, K, M, ldx, bk, BLOCK_M)) return r;
+  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, BLOCK_N)) return r;
+  GemmParams p{};
+  p.M = (int)M; p.N = (int)N;
+  p.k_blocks = (int)((K + bk - 1) / bk);
+  p.m_tiles = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  p.n_tiles = (int)((N + BLOCK_N - 1) / BLOCK_N);
+  p.splits = 1; p.kb_per_split = p.k_blocks;
+  p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f;
+  p.dropout_p = dropout_p; p.seed = seed; p.step = step; p.layer_id = layer_id;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, p, st)
+              : launch_gemm<0, false, false, EPI_FWD>(ta, tb, p, st);
+}
+
+extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw, const void* act,
+                                 int64_t ldact, void* dx, int64_t lddx, int64_t M, int64_t N, int64_t K,
+                                 int dtype, int flags, float dscale, b200_stream_t stream) {
+  if (int r = check_dims(M, N, K, dtype)) return r;
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;   // contraction (over N) elements per stage
+  const int epr = tf32 ? 32 : 64;  // elements per 128-byte row
+  CUtensorMap ta, tb;
+  // A = dY [M, N], contraction dim N contiguous (K-major)
+  if (int r = make_tmap(&ta, tf32, dy, N, M, lddy, bk, BLOCK_M)) return r;
+  // B(n'=k, k'=n) = W[n, k]: output dim contiguous (MN-major); box = 128 B of k x bk rows of n
+  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, epr, bk, true)) return r;
+  GemmParams p{};
+  p.M = (int)M; p.N = (int)K;
+  p.k_blocks = (int)((N + bk - 1) / bk);
+  p.m_tiles = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
+  p.splits = 1; p.kb_per_split = p.k_blocks;
+  p.out = dx; p.ldo = lddx; p.act = act; p.ldact = ldact; p.flags = flags; p.dscale = dscale;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, p, st)
+              : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, p, st);
+}
+
+extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx, float* dw,
+                                 int64_t lddw, int64_t M, int64_t N, int64_t K, int dtype, int flags,
+                                 b200_stream_t stream) {
+  if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(lddw % 4 == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
+               "wgrad output must be 16-byte aligned with lddw %% 4 == 0");
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;   // batch rows per stage
+  const int epr = tf32 ? 32 : 64;
+  CUtensorMap ta, tb;
+  // A(m'=n, k'=b) = dY[b, n]; B(n'=k, k'=b) = X[b, k]: both MN-major
+  if (int r = make_tmap(&ta, tf32, dy, N, M, lddy, epr, bk, true)) return r;
+  if (int r = make_tmap(&tb, tf32, x, K, M, ldx, epr, bk, true)) return r;
+  GemmParams p{};
+  p.M = (int)N; p.N = (int)K;
+  p.k_blocks = (int)((M + bk - 1) / bk);
+  p.m_tiles = (int)((N + BLOCK_M - 1) / BLOCK_M);
+  p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
+  const int tiles = p.m_tiles * p.n_tiles;
+  int splits = sm_count() / tiles;
+  if (splits < 1) splits = 1;
+  if (splits > p.k_blocks) splits = p.k_blocks;
+  p.kb_per_split = (p.k_blocks + splits - 1) / splits;
+  p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+  p.out = dw; p.ldo = lddw; p.flags = flags; p.dscale = 1.f;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p.splits > 1 && !(flags & B200_FLAG_ACCUMULATE)) {
+    // split-K partial tiles are summed with red.add: start from zero
+    B200_CHECK_CUDA(cudaMemset2DAsync(dw, lddw * sizeof(float), 0, K * sizeof(float), N, st));
+  }
+  return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, p, st)
+              : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, p, st);
+}

@@ -1,0 +1,283 @@
+"""Kernel-level parity on the GPU: every C-ABI kernel against a plain PyTorch restatement of the same op.
+
+Integer / index / byte work (preprocess, gathers) is compared bit-exactly; floating-point kernels with the
+tolerance written next to each assert.  The step-level parity against the CPU oracle lives in
+test_step_parity_gpu.py.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from b200step import ops as _ops
+    from b200step.lib import get_lib
+
+    get_lib()  # raises if libb200step.so is missing: no fallback
+    return _ops
+
+
+def _rand(shape, dtype, seed, scale=1.0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype).cuda()
+
+
+# ------------------------------------------------------------------------------------------------ GEMMs
+GEMM_SHAPES = [
+    # (M, N, K)   M = batch rows, N = out features, K = in features
+    (128, 256, 64),
+    (256, 512, 448),
+    (1000, 512, 512),     # ragged M
+    (4096, 1000, 512),    # ragged N (output layer: 1000 classes)
+    (333, 1000, 448),
+    (4096, 512, 448),
+]
+
+
+def _tols(dtype):
+    # bf16: inputs exact in bf16, fp32 accumulate, output rounded to bf16 (rel 2^-8); tf32: 10-bit mantissa inputs
+    return (2e-2, 2e-2) if dtype == torch.bfloat16 else (5e-3, 5e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_linear_fwd(ops, dtype, M, N, K):
+    x = _rand((M, K), dtype, 1)
+    w = _rand((N, K), dtype, 2, 0.05)
+    b = _rand((N,), torch.float32, 3)
+    y = torch.full((M, N), float("nan"), dtype=dtype, device="cuda")
+    for relu in (False, True):
+        ops.linear_fwd(x, w, b, y, M=M, N=N, K=K, relu=relu)
+        torch.cuda.synchronize()
+        ref = x.double() @ w.double().t() + b.double()
+        if relu:
+            ref = ref.clamp_min(0)
+        rtol, atol = _tols(dtype)
+        torch.testing.assert_close(y.double(), ref, rtol=rtol, atol=atol)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_linear_dgrad(ops, dtype, M, N, K):
+    dy = _rand((M, N), dtype, 4)
+    w = _rand((N, K), dtype, 5, 0.05)
+    act = _rand((M, K), dtype, 6)
+    dx = torch.full((M, K), float("nan"), dtype=dtype, device="cuda")
+    rtol, atol = _tols(dtype)
+    ops.linear_dgrad(dy, w, None, dx, M=M, N=N, K=K, relu=False)
+    torch.cuda.synchronize()
+    ref = dy.double() @ w.double()
+    torch.testing.assert_close(dx.double(), ref, rtol=rtol, atol=atol * 2)
+    ops.linear_dgrad(dy, w, act, dx, M=M, N=N, K=K, relu=True, dscale=2.0)
+    torch.cuda.synchronize()
+    ref = ref * (act.double() > 0) * 2.0
+    torch.testing.assert_close(dx.double(), ref, rtol=rtol, atol=atol * 4)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES + [(65536, 512, 448)])
+def test_linear_wgrad(ops, dtype, M, N, K):
+    dy = _rand((M, N), dtype, 7, 0.1)
+    x = _rand((M, K), dtype, 8)
+    dw = torch.full((N, K), float("nan"), dtype=torch.float32, device="cuda")
+    ops.linear_wgrad(dy, x, dw, M=M, N=N, K=K)
+    torch.cuda.synchronize()
+    ref = dy.double().t() @ x.double()
+    # fp32 result of an M-term sum: error grows ~ sqrt(M) * eps_in * |dy||x|
+    scale = (M ** 0.5) * 0.1
+    tol = (1e-5 if dtype == torch.bfloat16 else 2e-3) * scale + 1e-5
+    assert (dw.double() - ref).abs().max().item() <= tol * 4
+    # accumulate flag adds on top of what is there
+    ops.linear_wgrad(dy, x, dw, M=M, N=N, K=K, accumulate=True)
+    torch.cuda.synchronize()
+    assert (dw.double() - 2 * ref).abs().max().item() <= tol * 8
+
+
+def test_gemm_rejects_misaligned(ops):
+    from b200step.lib import B200Error
+
+    x = torch.zeros(128, 60, dtype=torch.bfloat16, device="cuda")
+    w = torch.zeros(64, 60, dtype=torch.bfloat16, device="cuda")
+    y = torch.zeros(128, 64, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(B200Error):
+        ops.linear_fwd(x, w, None, y, M=128, N=64, K=60, relu=False)
+
+
+def test_dropout_mask_matches_philox_oracle(ops):
+    from oracle.philox import dropout_keep_mask
+
+    M, N, K = 256, 512, 64
+    x = _rand((M, K), torch.bfloat16, 11)
+    w = _rand((N, K), torch.bfloat16, 12, 0.1)
+    y0 = torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+    y1 = torch.empty_like(y0)
+    step = torch.tensor([3], dtype=torch.int32, device="cuda")
+    ops.linear_fwd(x, w, None, y0, M=M, N=N, K=K, relu=False)
+    ops.linear_fwd(x, w, None, y1, M=M, N=N, K=K, relu=False, dropout_p=0.25, seed=1234, step=step, layer_id=2)
+    torch.cuda.synchronize()
+    keep = torch.from_numpy(dropout_keep_mask(M, N, p=0.25, seed=1234, step=3, layer_id=2)).cuda()
+    ref = torch.where(keep, (y0.float() / (1 - 0.25)), torch.zeros((), device="cuda")).to(torch.bfloat16)
+    # the kernel scales the fp32 accumulator before rounding; y0 is already rounded -> 1 bf16 ulp slack
+    torch.testing.assert_close(y1.float(), ref.float(), rtol=1.6e-2, atol=1e-3)
+    assert torch.equal(y1 != 0, keep & (y0 != 0)) or ((y1 != 0) ^ (keep & (y0 != 0))).sum().item() <= 2
+
+
+# ------------------------------------------------------------------------------------------- preprocess
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+@pytest.mark.parametrize("batch,nd,nc,rows,dim,ldx", [
+    (4096, 13, 26, 1000, 16, 448),
+    (1000, 13, 26, 1000, 16, 448),   # ragged batch (last CTA tile partial)
+    (257, 13, 26, 65536, 64, 1728),  # T1 row shape
+    (64, 13, 0, 1, 4, 16),           # no categorical features
+    (96, 5, 40, 50, 8, 328),         # > 32 tables
+])
+def test_preprocess_bit_exact(ops, dtype, batch, nd, nc, rows, dim, ldx):
+    g = torch.Generator().manual_seed(5)
+    nrows = 3 * batch + 17
+    dense = (torch.randn(nrows, nd, generator=g) * 3 + 1).cuda()
+    cat = torch.randint(0, rows, (nrows, max(nc, 1)), generator=g)[:, :nc].contiguous().cuda()
+    label = torch.randint(0, 10, (nrows,), generator=g).cuda()
+    mean = dense.mean(0).contiguous()
+    std = dense.std(0).contiguous()
+    tables = torch.randn(max(nc, 1) * rows * dim, generator=g).cuda()
+    steps = 2
+    row_idx = torch.randperm(nrows, generator=g)[: steps * batch].cuda()
+    cursor = torch.tensor([1], dtype=torch.int32, device="cuda")
+    x = torch.full((batch, ldx), float("nan"), dtype=dtype, device="cuda")
+    y = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+    idx = torch.full((batch, max(nc, 1)), -1, dtype=torch.int32, device="cuda")
+    ops.preprocess(dense, cat, label, row_idx, cursor, mean, std, tables, x, y, idx, batch=batch, num_dense=nd,
+                   num_cat=nc, table_rows=rows, embed_dim=dim)
+    torch.cuda.synchronize()
+    r = row_idx[batch: 2 * batch]
+    ref = torch.zeros(batch, ldx, dtype=torch.float32, device="cuda")
+    ref[:, :nd] = dense[r].sub(mean).div(std)  # reference rule: tensor.sub_(mean).div_(std)
+    if nc:
+        tv = tables.view(nc, rows, dim)
+        emb = torch.stack([tv[t][cat[r, t]] for t in range(nc)], 1).reshape(batch, nc * dim)
+        ref[:, nd: nd + nc * dim] = emb
+        assert torch.equal(idx[:, :nc].long(), cat[r])
+    ref = ref.to(dtype)
+    assert torch.equal(x.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
+                       ref.view(torch.int16 if dtype == torch.bfloat16 else torch.int32))
+    assert torch.equal(y, label[r])
+
+
+# ------------------------------------------------------------------------------------------------- loss
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+@pytest.mark.parametrize("batch,C", [(4096, 1000), (1000, 1000), (37, 16), (65536, 1000), (512, 1024)])
+def test_ce_loss_grad(ops, dtype, batch, C):
+    logits = _rand((batch, C), dtype, 21, 2.0)
+    labels = torch.randint(0, min(C, 10), (batch,), generator=torch.Generator().manual_seed(22)).cuda()
+    dlogits = torch.full((batch, C), float("nan"), dtype=dtype, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    dbias = torch.full((C,), float("nan"), device="cuda")
+    scratch = torch.empty(ops.ce_scratch_floats(C), device="cuda")
+    scale = 1.0 / (batch * 2)  # world = 2
+    ops.ce_loss_grad(logits, labels, dlogits, loss, dbias, scratch, batch=batch, num_classes=C, grad_scale=scale)
+    torch.cuda.synchronize()
+    z = logits.double().requires_grad_(True)
+    ref_loss = torch.nn.functional.cross_entropy(z, labels)
+    ref_loss.backward()
+    ref_d = z.grad * (batch * scale)
+    # loss: fp32 exp/log + fp32 tree sums -> rel 1e-5
+    assert abs(loss.item() - ref_loss.item()) <= 1e-5 * max(1.0, abs(ref_loss.item()))
+    if dtype == torch.float32:
+        torch.testing.assert_close(dlogits.double(), ref_d, rtol=1e-4, atol=1e-9)
+    else:  # one bf16 rounding of the fp32 gradient
+        torch.testing.assert_close(dlogits.double(), ref_d, rtol=8e-3, atol=1e-9)
+    # bias gradient = column sums of what was stored
+    torch.testing.assert_close(dbias.double(), dlogits.double().sum(0), rtol=1e-4, atol=1e-7)
+    # deterministic: bit-identical on a second call
+    loss2 = torch.zeros(1, device="cuda")
+    dbias2 = torch.empty_like(dbias)
+    ops.ce_loss_grad(logits, labels, dlogits, loss2, dbias2, scratch, batch=batch, num_classes=C, grad_scale=scale)
+    torch.cuda.synchronize()
+    assert torch.equal(loss, loss2) and torch.equal(dbias, dbias2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+@pytest.mark.parametrize("M,N", [(4096, 512), (1000, 1000), (65536, 512), (7, 8), (300, 4096)])
+def test_colsum(ops, dtype, M, N):
+    dy = _rand((M, N), dtype, 31)
+    out = torch.full((N,), float("nan"), device="cuda")
+    scratch = torch.empty(ops.colsum_scratch_floats(N), device="cuda")
+    ops.colsum(dy, out, scratch, M=M, N=N)
+    torch.cuda.synchronize()
+    ref = dy.double().sum(0)
+    torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
+
+
+# -------------------------------------------------------------------------------------------- embedding
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+def test_emb_bwd(ops, dtype):
+    batch, nd, nc, rows, dim, ldx = 4096, 13, 26, 1000, 16, 448
+    dx = _rand((batch, ldx), dtype, 41, 0.01)
+    idx = torch.randint(0, rows, (batch, nc), generator=torch.Generator().manual_seed(42)).int().cuda()
+    dt = torch.zeros(nc * rows * dim, device="cuda")
+    ops.emb_bwd(dx, idx, dt, batch=batch, num_dense=nd, num_cat=nc, table_rows=rows, embed_dim=dim)
+    torch.cuda.synchronize()
+    ref = torch.zeros(nc, rows, dim, dtype=torch.float64, device="cuda")
+    for t in range(nc):
+        ref[t].index_add_(0, idx[:, t].long(), dx[:, nd + t * dim: nd + (t + 1) * dim].double())
+    # fp32 atomics in arbitrary order: |err| <= n_adds * eps * max|term|
+    torch.testing.assert_close(dt.view(nc, rows, dim).double(), ref, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------- optimizers
+@pytest.mark.parametrize("n", [1024, 1411816 + 3, 17])
+def test_sgd_matches_torch(ops, n):
+    g = torch.Generator().manual_seed(51)
+    p0 = torch.randn(n, generator=g)
+    n_shadow = (n // 2) // 4 * 4
+    p = p0.clone().cuda()
+    buf = torch.zeros(n, device="cuda")
+    shadow = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    ref_p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9, weight_decay=1e-4)
+    for it in range(3):
+        grad = torch.randn(n, generator=g) * 0.1
+        ref_p.grad = grad.clone()
+        opt.step()
+        ops.sgd_step(p, grad.cuda(), buf, shadow, n_shadow=n_shadow, lr=0.1, momentum=0.9, weight_decay=1e-4)
+    torch.cuda.synchronize()
+    # same fp32 operation order as torch's SGD; FMA contraction may differ by 1 ulp per op
+    torch.testing.assert_close(p.cpu(), ref_p.data, rtol=1e-6, atol=1e-7)
+    assert torch.equal(shadow[:n_shadow], p[:n_shadow].to(torch.bfloat16))
+    assert torch.count_nonzero(shadow[n_shadow:]).item() == 0
+
+
+@pytest.mark.parametrize("n", [4096, 100003])
+def test_adam_matches_torch(ops, n):
+    g = torch.Generator().manual_seed(61)
+    p0 = torch.randn(n, generator=g)
+    p = p0.clone().cuda()
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    step = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ref_p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ref_p], lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4)
+    for it in range(4):
+        grad = torch.randn(n, generator=g) * 0.1
+        ref_p.grad = grad.clone()
+        opt.step()
+        ops.adam_step(p, grad.cuda(), m, v, None, step, n_shadow=0, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
+                      weight_decay=1e-4)
+        ops.advance_step(None, step, 1)
+    torch.cuda.synchronize()
+    assert step.item() == 4
+    torch.testing.assert_close(p.cpu(), ref_p.data, rtol=2e-6, atol=2e-7)
+
+
+def test_cast_and_advance(ops):
+    src = _rand((1000003,), torch.float32, 71)
+    dst = torch.zeros(1000003, dtype=torch.bfloat16, device="cuda")
+    ops.cast_bf16(src, dst)
+    cursor = torch.tensor([2], dtype=torch.int32, device="cuda")
+    step = torch.tensor([9], dtype=torch.int32, device="cuda")
+    ops.advance_step(cursor, step, 3)
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src.to(torch.bfloat16))
+    assert cursor.item() == 0 and step.item() == 10
