@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py — train samples/sec of the B200 data-parallel training step (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+           bench.py --gpus N --steps K --warmup W
+
+One "step" = one pass of the hot path (task.py:303-312) over one synthetic batch: K-pre -> forward GEMMs ->
+loss -> backward GEMMs -> gradient all-reduce (N>1) -> optimizer.  Rank 0 prints ONE JSON line.
+
+Workloads (BASELINE.json configs):
+  t0_bf16_b65536  (default) T0 tabular MLP, bf16, batch 65536 per GPU — the per-GPU workload of config 3, the one
+                  the 1/2/4/8-GPU metric is quoted on (weak scaling: per-GPU batch fixed)
+  t0_fp32_b4096   config 2: T0, fp32 storage / TF32 tensor cores, batch 4096, single GPU
+  t1_bf16_b65536  config 4: widened MLP (4x1024, 26 x 65536 x 64 embeddings), bf16, batch 65536 per GPU
+Timing: CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks.  The per-step
+working set (activations of a 65536-row batch, > 500 MB) is larger than the 126 MB L2, so no explicit flush.
+"""
+from __future__ import annotations
+
+import argparse
+import dataclasses
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "kubeflow-v2-distributed-pytorch_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+WORKLOADS = {
+    "t0_bf16_b65536": dict(arch="tabular_mlp", precision="bf16", batch=65536, optimizer="sgd"),
+    "t0_fp32_b4096": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd"),
+    "t1_bf16_b65536": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="sgd"),
+    "t1_bf16_b65536_adam": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="adam"),
+}
+BATCHES_PER_RANK = 8          # distinct batches per rank, cycled (N = W*B*8 rows)
+RAW_BYTES_PER_SAMPLE = None   # filled from the spec: 4*num_dense + 8*num_cat + 8
+REF_SAMPLE_CAP = 65536        # rows per step of the CPU arms (bounded sample)
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                toks = [t for t in vis.split(",") if t.strip() != ""]
+                if index < len(toks) and toks[index].strip().isdigit():
+                    phys = int(toks[index])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------------- CPU arms
+def _cpu_oracle_throughput(spec, ds_rows, batch, world, steps, warmup, threads=None):
+    """Times the oracle port (oracle/reference_step.py: the reference's step with .cuda() removed, true fp32)
+    on the host cores.  `batch` rows per step (a bounded sample of the GPU arm's per-step work)."""
+    import torch
+
+    from b200step.data import make_synthetic
+    from oracle.reference_step import OracleTrainer
+
+    if threads:
+        torch.set_num_threads(threads)
+    sd = dataclasses.asdict(spec)
+    sd.pop("name")
+    ds = make_synthetic(ds_rows, spec)
+    tr = OracleTrainer(sd, ds, world=1, batch_size=batch, precision="fp32")
+    for _ in range(warmup):
+        tr.step()
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        tr.step()
+        times.append(time.perf_counter() - t0)
+    return {"samples_per_s": batch * steps / sum(times), "ms_per_step": 1e3 * sum(times) / steps,
+            "cores": torch.get_num_threads(), "min_ms": 1e3 * min(times)}
+
+
+def run_reference(args, rank):
+    """`--impl reference`: the reference's own CPU path for this step.  task.py itself cannot run without CUDA
+    and the network, so this is the oracle PORT on all host threads; rank 0 only."""
+    if rank != 0:
+        return
+    import torch
+
+    from b200step.model import ARCHS
+
+    wl = WORKLOADS[args.workload]
+    spec = ARCHS[wl["arch"]]
+    sample = min(wl["batch"] * args.gpus, REF_SAMPLE_CAP)
+    steps = max(1, min(args.steps, 8))
+    warm = max(1, min(args.warmup, 2))
+    r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, steps, warm, threads=os.cpu_count())
+    out = {
+        "impl": "reference", "metric": "train samples/sec", "value": r["samples_per_s"], "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "arch": wl["arch"], "per_gpu_batch": wl["batch"],
+                   "optimizer": wl["optimizer"]},
+        "cpu_baseline": {"value": r["samples_per_s"], "unit": "samples/s", "cores": r["cores"], "kind": "port",
+                         "sample": f"{steps} steps of {sample} rows (global batch capped at {REF_SAMPLE_CAP}), "
+                                   f"fp32 torch CPU, host threads={r['cores']} of {os.cpu_count()} logical cpus"},
+        "e2e": {"value": r["samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(out), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- GPU arm
+def run_b200(args, rank, local_rank, world):
+    import torch
+
+    from b200step.data import make_synthetic
+    from b200step.engine import Communicator, StepConfig, TrainStep
+    from b200step.model import ARCHS, FlatLayout, init_parameters
+    from b200step.sampler import rank_indices
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl b200 needs a CUDA device: the training step has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    wl = WORKLOADS[args.workload]
+    spec = ARCHS[wl["arch"]]
+    B = wl["batch"]
+    comm = None
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group(backend="nccl", init_method="env://", world_size=world, rank=rank,
+                                device_id=dev)
+        uid = [Communicator.make_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        comm = Communicator(rank, world, uid[0])
+
+    rows = world * B * BATCHES_PER_RANK
+    ds = make_synthetic(rows, spec)
+    cfg = StepConfig(batch_size=B, world=world, rank=rank, precision=wl["precision"], optimizer=wl["optimizer"])
+    idx = rank_indices(rows, world, rank)
+    # keep only this rank's rows resident (same values as the global dataset, re-indexed 0..n-1)
+    local = dataclasses.replace(ds, dense=ds.dense[idx], cat=ds.cat[idx], label=ds.label[idx])
+    host_local = local
+    eng = TrainStep(spec, init_parameters(spec, 0), local, torch.arange(idx.numel()), cfg, comm, device=dev)
+    del ds
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident measurement ("value") -------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        eng.step()
+    eng.synchronize()
+    sampler = ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.start()
+    e0.record(eng.main)
+    for _ in range(args.steps):
+        eng.step()
+    e1.record(eng.main)
+    eng.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    loss_after = eng.loss_value()
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * B * args.steps / (ms / 1e3)
+
+    # ---- end-to-end measurement: host batches, H2D inside the timed region, loss read back every step --------
+    nb = min(BATCHES_PER_RANK, 4)
+    host = [(host_local.dense[i * B:(i + 1) * B].pin_memory(), host_local.cat[i * B:(i + 1) * B].pin_memory(),
+             host_local.label[i * B:(i + 1) * B].pin_memory()) for i in range(nb)]
+    e2e_steps = max(3, min(args.steps, 20))
+    for i in range(2):
+        eng.step_from_host(*host[i % nb])
+        eng.loss_value()
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(eng.main)
+    for i in range(e2e_steps):
+        eng.step_from_host(*host[i % nb])
+        _ = eng.loss_value()          # device->host read of the step's result
+    g1.record(eng.main)
+    eng.synchronize()
+    barrier()
+    e2e_ms = g0.elapsed_time(g1)   # spans host gaps too: every step ends with a blocking loss read
+    if dist is not None:
+        t = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    raw_bytes = 4 * spec.num_dense + 8 * spec.num_cat + 8
+    e2e = {"value": world * B * e2e_steps / (e2e_ms / 1e3), "unit": "samples/s",
+           "h2d_bytes_per_step": B * raw_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps}
+
+    # ---- per-kernel timing of one eager step (CUDA events around each launch) -> roofline --------------------
+    prof = profile_kernels(eng, spec, B, world)
+    barrier()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    peaks = _peaks()
+    top = max(prof, key=lambda r: r["ms"])
+    if top["bound"] == "tensor":
+        peak = peaks["bf16_tflops"] if wl["precision"] == "bf16" else peaks["bf16_tflops"] / 2.0
+        roof = {"bound": "tensor", "kernel": top["name"], "achieved": top["tflops"], "peak": peak, "unit": "TFLOP/s",
+                "frac": top["tflops"] / peak, "traffic": None,
+                "peak_source": peaks["source"] + (" bf16 burst" if wl["precision"] == "bf16"
+                                                  else " bf16 burst / 2 (tf32 runs at half the bf16 rate)")}
+    else:
+        roof = {"bound": "hbm", "kernel": top["name"], "achieved": top["gbs"], "peak": peaks["hbm_gbs"],
+                "unit": "GB/s", "frac": top["gbs"] / peaks["hbm_gbs"], "traffic": None,
+                "peak_source": peaks["source"] + " copy bandwidth"}
+    flops = spec.flops_per_sample()["total"]
+    step_tflops = flops * B / (ms / args.steps / 1e3) / 1e12
+    out = {
+        "metric": "train samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16" if wl["precision"] == "bf16" else "tf32", "data": "synthetic",
+        "config": {"workload": args.workload, "arch": wl["arch"], "per_gpu_batch": B, "global_batch": B * world,
+                   "optimizer": wl["optimizer"], "params": spec.num_params, "parallelism": f"dp{world}",
+                   "l2": "per-step working set > 126 MB L2 (no flush needed)" if B >= 32768 else
+                         "working set fits L2: dataset cycles 8 batches",
+                   "cuda_graph": True},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": eng.kernels_per_step * args.steps,
+        "roofline": roof, "kernels": prof, "step_tflops_per_gpu": step_tflops,
+        "final_loss": loss_after,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        sample = min(B, REF_SAMPLE_CAP)
+        r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, 5, 2)
+        out["cpu_baseline"] = {"value": r["samples_per_s"], "unit": "samples/s", "cores": r["cores"], "kind": "port",
+                               "sample": f"5 steps of {sample} rows after 2 warm-up, oracle port (torch CPU fp32), "
+                                         f"{r['cores']} threads"}
+    print(json.dumps(out), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def profile_kernels(eng, spec, B, world):
+    """Average device time of each kernel class over a few eager steps (events on the launching stream), with the
+    algorithmic FLOPs / bytes per launch -> achieved TFLOP/s or GB/s."""
+    import torch
+
+    from b200step import ops
+
+    names = ["preprocess", "linear_fwd", "ce_loss_grad", "linear_dgrad", "linear_wgrad", "colsum", "emb_bwd",
+             "zero", "sgd_step", "adam_step"]
+    records = []
+    orig = {n: getattr(ops, n) for n in names}
+    es = 2 if eng.dt == torch.bfloat16 else 4
+
+    def wrap(name, fn):
+        def inner(*a, **k):
+            st = k.get("stream") or eng.main
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(st)
+            r = fn(*a, **k)
+            a1.record(st)
+            label, work = name, {}
+            if name.startswith("linear_"):
+                M, N, K = k["M"], k["N"], k["K"]
+                label = f"{name}[{M}x{N}x{K}]"
+                work = {"flops": 2.0 * M * N * K}
+            elif name == "preprocess":
+                raw = 4 * spec.num_dense + 8 * spec.num_cat + 8 + 8
+                work = {"bytes": B * (raw + 4 * spec.num_cat * spec.embed_dim + es * eng.k0 + 8 + 4 * spec.num_cat)}
+            elif name == "ce_loss_grad":
+                work = {"bytes": B * (2 * es * spec.num_classes + 8)}
+            elif name == "colsum":
+                work = {"bytes": k["M"] * k["N"] * es}
+            elif name == "emb_bwd":
+                work = {"bytes": B * spec.num_cat * spec.embed_dim * (es + 8) + 4 * B * spec.num_cat}
+            elif name == "zero":
+                work = {"bytes": a[0].numel() * a[0].element_size()}
+            elif name == "sgd_step":
+                work = {"bytes": a[0].numel() * 20 + 2 * k.get("n_shadow", 0)}
+            elif name == "adam_step":
+                work = {"bytes": a[0].numel() * 28 + 2 * k.get("n_shadow", 0)}
+            records.append((label, a0, a1, work))
+            return r
+        return inner
+
+    reps = 3
+    try:
+        for n in names:
+            setattr(ops, n, wrap(n, orig[n]))
+        for _ in range(reps):
+            eng._enqueue(B, None, eng.row_idx, eng.cursor, True)
+        eng.synchronize()
+    finally:
+        for n in names:
+            setattr(ops, n, orig[n])
+    agg = {}
+    for label, a0, a1, work in records:
+        d = agg.setdefault(label, {"ms": 0.0, "launches": 0, "work": work})
+        d["ms"] += a0.elapsed_time(a1)
+        d["launches"] += 1
+    out = []
+    for label, d in agg.items():
+        per = d["ms"] / d["launches"]
+        rec = {"name": label, "ms": per, "per_step": d["launches"] // reps}
+        if "flops" in d["work"]:
+            rec.update(bound="tensor", tflops=d["work"]["flops"] / (per / 1e3) / 1e12)
+        else:
+            rec.update(bound="hbm", gbs=d["work"]["bytes"] / (per / 1e3) / 1e9)
+        out.append(rec)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="t0_bf16_b65536")
+    ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            # launched without torchrun: re-exec under torch.distributed.run
+            import subprocess
+
+            port = 29500 + (os.getpid() % 2000)
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+            sys.exit(subprocess.call(cmd))
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    run_b200(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -10,6 +10,8 @@
 // by four epilogue warps with tcgen05.ld while the next tile's MMAs run.
 //
 // Roles (256 threads): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator, warps4-7 = epilogue.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -349,7 +351,12 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
   cuuint64_t strides[1] = {ld * es};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+  // fp32 operands: the TFLOAT32 tensor-map type rounds to tf32 (nearest) on the way into shared memory; with
+  // plain FLOAT32 the tensor core would truncate the low 13 mantissa bits, a biased error that accumulates.
+  static const bool tf32_truncate = getenv("B200STEP_TF32_TRUNCATE") != nullptr;  // debugging knob
+  const CUtensorMapDataType dt = !tf32 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                 : (tf32_truncate ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32);
+  CUresult r = fn(m, dt, 2,
                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

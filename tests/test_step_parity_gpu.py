@@ -45,13 +45,19 @@ def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, l
 
 
 def _param_err(oracle, eng):
+    """Worst per-tensor relative L2 error  ||p_gpu - p_oracle|| / ||p_oracle||  and the cosine of the whole
+    parameter vector (SURVEY.md §8c states the parameter bar as a cosine)."""
     so, sg = oracle.state_dict(), eng.state_dict()
     assert list(so.keys()) == list(sg.keys())
     worst = 0.0
     for k in so:
         assert so[k].shape == sg[k].shape, k
-        scale = max(so[k].abs().max().item(), 1e-6)
-        worst = max(worst, (so[k] - sg[k]).abs().max().item() / scale)
+        worst = max(worst, ((so[k] - sg[k]).norm() / so[k].norm().clamp_min(1e-12)).item())
+    a = torch.cat([v.flatten() for v in so.values()]).double()
+    b = torch.cat([v.flatten() for v in sg.values()]).double()
+    cos = torch.nn.functional.cosine_similarity(a, b, dim=0).item()
+    print(f"param parity: worst rel-L2 {worst:.3e}, cosine {cos:.8f}")
+    assert cos >= 0.9999, cos
     return worst
 
 
@@ -85,7 +91,9 @@ def test_small_model_n_steps(precision, optimizer):
     for a, b in zip(lo, lg):
         assert abs(a - b) <= 2e-3 * max(1.0, abs(a)), (lo, lg)
     assert lg[-1] < lg[0]
-    assert _param_err(oracle, eng) <= (5e-3 if precision == "fp32" else 1e-2)
+    # SGD: rel-L2 1e-2; Adam divides by sqrt(v): elements whose gradient is rounding noise move by +-lr per
+    # step in either path, so its bar is looser
+    assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
