@@ -92,6 +92,21 @@ int64_t b200_colsum_scratch_floats(int64_t N);
 int b200_colsum(const void* dy, int64_t lddy, float* out, float* scratch, int64_t scratch_floats,
                 int64_t M, int64_t N, int dtype, b200_stream_t stream);
 
+/* Column sum for callers that can neither pass scratch nor tolerate an allocation inside the call (a bare C
+ * binding with no allocator of its own; a process whose framework memory pool already owns the card, where a raw
+ * cudaMalloc can fail or fragment the pool; a step that overlaps communication, which the device-wide
+ * synchronisation of cudaMalloc/cudaFree would stall).  No counterpart in the reference: it exists only for
+ * those callers.  Same result as b200_colsum (the partials may be grouped differently, so sums agree to fp32
+ * rounding, not bit for bit).  The partial sums live in a 1 MiB device array that is part of the library and
+ * stays resident on every GPU that loads it; the call allocates nothing.
+ *   - limit: N <= 4096 columns, otherwise the call fails with an explanatory error;
+ *   - the first call on each device looks up the array's device address; make that first call outside any
+ *     stream capture;
+ *   - all calls share the one array: two calls that can overlap on the GPU (different streams, no ordering)
+ *     race on it — order them, or use b200_colsum with separate scratch buffers. */
+int b200_colsum_static(const void* dy, int64_t lddy, float* out, int64_t M, int64_t N, int dtype,
+                       b200_stream_t stream);
+
 /* ---- K-embbwd: embedding gradient scatter-add (task.py:311; embedding_dense_backward) -------
  * dtables[t][idx[b,t]][:] += dx[b, num_dense + t*dim : +dim]   (fp32 atomics; dtables must be zeroed by the caller) */
 int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, float* dtables,

@@ -36,6 +36,7 @@ SIGNATURES = {
     "b200_ce_loss_grad": (_i, [_p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i, _f, _i, _p]),
     "b200_colsum_scratch_floats": (_i64, [_i64]),
     "b200_colsum": (_i, [_p, _i64, _p, _p, _i64, _i64, _i64, _i, _p]),
+    "b200_colsum_static": (_i, [_p, _i64, _p, _i64, _i64, _i, _p]),
     "b200_emb_bwd": (_i, [_p, _i64, _p, _p, _i64, _i, _i, _i64, _i, _i, _p]),
     "b200_sgd_step": (_i, [_p, _p, _p, _p, _i64, _i64, _d, _d, _d, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _d, _d, _d, _d, _d, _p, _p]),

@@ -305,3 +305,65 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---- column sum without any allocation --------------------------------------------------------------------
+// Some hosts of this library cannot hand it scratch memory and must not see it allocate either: a thin C
+// binding that only forwards the tensors it was given has no allocator to call; a process whose framework pool
+// (PyTorch's caching allocator, for instance) has already reserved the card's HBM can see a raw cudaMalloc fail
+// or fragment that pool; and cudaMalloc / cudaFree synchronise the whole device, which stalls the gradient
+// all-reduce running on the side stream.  For them the partial sums of the column sum live in this file-scope
+// device array instead: 1 MiB, part of the loaded module, held by every GPU that loads the library until the
+// process exits.
+constexpr long long CS_STATIC_FLOATS = 256 * 1024;  // 1 MiB of fp32 partials
+constexpr int CS_STATIC_MAX_N = 4096;               // widest row the static variant accepts
+constexpr int CS_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) float g_colsum_static_scratch[CS_STATIC_FLOATS];
+
+// The array's name is only a host-side handle in host code; the address a kernel can use has to be asked for,
+// per device, with that device current.
+static int colsum_static_scratch_ptr(float** out) {
+  static float* ptrs[CS_STATIC_MAX_DEVICES] = {nullptr};
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < CS_STATIC_MAX_DEVICES, "device ordinal %d out of range", dev);
+  if (ptrs[dev] == nullptr) {
+    float* p = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch));
+    B200_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int64_t M, int64_t N, int dtype,
+                                  b200_stream_t stream) {
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
+  const int vec = dtype == B200_F32 ? 4 : 8;
+  B200_REQUIRE(M > 0 && N > 0 && N % vec == 0 && lddy % vec == 0, "colsum: N and lddy must be multiples of %d", vec);
+  B200_REQUIRE(N <= CS_STATIC_MAX_N,
+               "b200_colsum_static: N=%lld exceeds the static scratch limit of %d columns; use b200_colsum with "
+               "caller-provided scratch", (long long)N, CS_STATIC_MAX_N);
+  float* scratch = nullptr;
+  if (int r = colsum_static_scratch_ptr(&scratch)) return r;  // first call on this device does the set-up
+  const int nvec = (int)(N / vec);
+  const int panels = (nvec + CS_THREADS - 1) / CS_THREADS;
+  long long slabs = ((long long)sm_count() * 4 + panels - 1) / panels;
+  if (slabs > CS_STATIC_FLOATS / N) slabs = CS_STATIC_FLOATS / N;  // partial rows must fit the static array
+  if (slabs > M) slabs = M;
+  if (slabs < 1) slabs = 1;
+  const int rows_per_block = (int)((M + slabs - 1) / slabs);
+  slabs = (M + rows_per_block - 1) / rows_per_block;
+  B200_REQUIRE(slabs * N <= CS_STATIC_FLOATS, "b200_colsum_static: internal sizing error");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // every partial row that the second kernel reads is written by the first one in this same call, so nothing
+  // in the shared array has to start at zero
+  if (dtype == B200_BF16)
+    colsum_kernel<true><<<(int)slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+  else
+    colsum_kernel<false><<<(int)slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+  B200_CHECK_CUDA(cudaGetLastError());
+  reduce_partials_kernel<<<(int)((N + 255) / 256), 256, 0, st>>>(scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
