@@ -170,31 +170,53 @@ class TrainStep:
         seg = self.layout.bias(li)
         return (self.g if grad else self.p)[seg.offset: seg.offset + seg.cols]
 
-    # --------------------------------------------------------------------------------------- the schedule
-    def _enqueue(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
-                 cursor: Optional[torch.Tensor], advance: bool) -> int:
-        """Enqueue one full step on self.main for `batch` rows; returns the number of kernels launched."""
-        spec, cfg, lay, st = self.spec, self.cfg, self.layout, self.main
+    def _forward(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
+                 cursor: Optional[torch.Tensor], training: bool) -> int:
+        """K-pre + the Linear stack (task.py:309); dropout only when training (model.train(), task.py:301)."""
+        spec, cfg, st = self.spec, self.cfg, self.main
         ds = src or self.ds
-        n = 0
         dims = spec.layer_dims
-        L = self.L
-        # K-pre ------------------------------------------------------------------------------------------
+        n = 0
         ops.preprocess(ds.dense, ds.cat, ds.label, row_idx, cursor, ds.mean, ds.std,
                        self.tables if spec.num_cat else None, self.x0, self.y, self.idx, batch=batch,
                        num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
                        embed_dim=spec.embed_dim, stream=st)
         n += 1
-        # forward ----------------------------------------------------------------------------------------
         inp = self.x0
         for li, (k, o) in enumerate(dims):
             kk = self.k0 if li == 0 else k
-            last = li == L - 1
+            last = li == self.L - 1
             ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li], M=batch, N=o, K=kk, relu=not last,
-                           dropout_p=0.0 if last else spec.dropout, seed=cfg.dropout_seed, step=self.step_ctr,
-                           layer_id=li, stream=st)
+                           dropout_p=spec.dropout if (training and not last) else 0.0, seed=cfg.dropout_seed,
+                           step=self.step_ctr, layer_id=li, stream=st)
             n += 1
             inp = self.acts[li]
+        return n
+
+    def evaluate(self) -> float:
+        """Top-1 accuracy over the whole resident dataset in its stored order (the reference's evaluate(),
+        task.py:30-46, over a shuffle=False loader, task.py:267): forward only, eval mode (no dropout)."""
+        n_rows, B = len(self.ds), self.cfg.batch_size
+        order = torch.arange(n_rows, dtype=torch.int64, device=self.dev)
+        correct = torch.zeros((), dtype=torch.int64, device=self.dev)
+        torch.cuda.synchronize(self.dev)
+        with torch.cuda.stream(self.main):
+            for s in range(0, n_rows, B):
+                b = min(B, n_rows - s)
+                self._forward(b, None, order[s:], None, training=False)
+                pred = self.acts[-1][:b].argmax(dim=1)          # torch.max(outputs, 1), task.py:40
+                correct += (pred == self.y[:b]).sum()           # task.py:42
+        self.main.synchronize()
+        return correct.item() / n_rows
+
+    # --------------------------------------------------------------------------------------- the schedule
+    def _enqueue(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
+                 cursor: Optional[torch.Tensor], advance: bool) -> int:
+        """Enqueue one full step on self.main for `batch` rows; returns the number of kernels launched."""
+        spec, cfg, lay, st = self.spec, self.cfg, self.layout, self.main
+        dims = spec.layer_dims
+        L = self.L
+        n = self._forward(batch, src, row_idx, cursor, training=True)
         # loss + dlogits + db_L ---------------------------------------------------------------------------
         ops.ce_loss_grad(self.acts[-1], self.y, self.dlogits, self.loss, self._b(L - 1, grad=True),
                          self.ce_scratch, batch=batch, num_classes=spec.num_classes,
