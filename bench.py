@@ -95,7 +95,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.01)
 
     def start(self):
         if self.nv is not None:
@@ -324,7 +324,7 @@ def profile_kernels(eng, spec, B, world):
             label, work = name, {}
             if name.startswith("linear_"):
                 M, N, K = k["M"], k["N"], k["K"]
-                label = f"{name}[{M}x{N}x{K}]"
+                label = f"{name}[{M}x{N}x{K}]" + ("+dbias" if k.get("dbias") is not None else "")
                 work = {"flops": 2.0 * M * N * K}
             elif name == "preprocess":
                 raw = 4 * spec.num_dense + 8 * spec.num_cat + 8 + 8
@@ -334,7 +334,8 @@ def profile_kernels(eng, spec, B, world):
             elif name == "colsum":
                 work = {"bytes": k["M"] * k["N"] * es}
             elif name == "emb_bwd":
-                work = {"bytes": B * spec.num_cat * spec.embed_dim * (es + 8) + 4 * B * spec.num_cat}
+                # dX columns + ids read once; the table gradients are L2-resident atomics (counted once: zero + final)
+                work = {"bytes": B * spec.num_cat * (spec.embed_dim * es + 4) + 8 * spec.num_cat * spec.cardinality * spec.embed_dim}
             elif name == "zero":
                 work = {"bytes": a[0].numel() * a[0].element_size()}
             elif name == "sgd_step":

@@ -57,17 +57,24 @@ int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t*
  *        with optional inverted dropout after the activation: keep iff philox(seed,*step,layer,elem) >= p.
  * dgrad (task.py:311 loss.backward, addmm backward wrt input):
  *        dx[M,K] = (dy[M,N] · w[N,K]) * (act[M,K] > 0 if RELU) * dscale     (act = the stored layer input)
+ *        relu_mask (nullable, either side): 1 bit per element, word [row, col/32], row stride ldmask words; the
+ *        forward writes (y > 0) and the backward of the NEXT layer reads it instead of re-reading `act`.
+ *        dbias (nullable) [K] = column sums of the stored dx = bias gradient of the layer that produced `act`
+ *        (addmm backward wrt bias), deterministic two-stage reduction through `scratch`.
  * wgrad (task.py:311, addmm backward wrt weight): dw[N,K] (+)= dy[M,N]^T · x[M,K], fp32 result.
  * K and ld* must make every row 16-byte aligned (K%4==0 for F32, K%8==0 for BF16; same for N where N is a row length).
  */
 int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
                     void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
                     float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
-                    b200_stream_t stream);
+                    uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream);
 int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw,
                       const void* act, int64_t ldact, void* dx, int64_t lddx,
                       int64_t M, int64_t N, int64_t K, int dtype, int flags, float dscale,
-                      b200_stream_t stream);
+                      const uint32_t* relu_mask, int64_t ldmask,
+                      float* dbias, float* scratch, int64_t scratch_floats, b200_stream_t stream);
+/* scratch floats b200_linear_dgrad needs when dbias != NULL */
+int64_t b200_dgrad_scratch_floats(int64_t M, int64_t K);
 int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx,
                       float* dw, int64_t lddw, int64_t M, int64_t N, int64_t K, int dtype, int flags,
                       b200_stream_t stream);

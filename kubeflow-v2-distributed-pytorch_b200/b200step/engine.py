@@ -133,7 +133,10 @@ class TrainStep:
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ce_scratch = torch.empty(ops.ce_scratch_floats(spec.num_classes), dtype=torch.float32, device=dev)
-        self.cs_scratch = torch.empty(ops.colsum_scratch_floats(wmax), dtype=torch.float32, device=dev)
+        # 1 bit per hidden activation (ReLU/dropout mask for backward), row stride padded to 16 bytes
+        self.masks = [torch.zeros(B, ((o + 31) // 32 + 3) // 4 * 4, dtype=torch.int32, device=dev)
+                      for (_, o) in dims[:-1]]
+        self.dg_scratch = torch.empty(max(ops.dgrad_scratch_floats(B, wmax), 4), dtype=torch.float32, device=dev)
         self.identity_idx = None  # lazily built for host-fed batches
 
         # ---- streams / events
@@ -188,7 +191,8 @@ class TrainStep:
             last = li == self.L - 1
             ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li], M=batch, N=o, K=kk, relu=not last,
                            dropout_p=spec.dropout if (training and not last) else 0.0, seed=cfg.dropout_seed,
-                           step=self.step_ctr, layer_id=li, stream=st)
+                           step=self.step_ctr, layer_id=li,
+                           relu_mask=self.masks[li] if (training and not last) else None, stream=st)
             n += 1
             inp = self.acts[li]
         return n
@@ -232,9 +236,11 @@ class TrainStep:
             x_in = self.x0 if li == 0 else self.acts[li - 1]
             if li > 0:
                 dx = self.dh[li % 2][:, :kk]
-                ops.linear_dgrad(dy, self._w(li), x_in, dx, M=batch, N=o, K=kk, relu=True, dscale=inv_keep,
-                                 stream=st)
-                n += 1
+                # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums = bias gradient of layer l-1
+                ops.linear_dgrad(dy, self._w(li), None, dx, M=batch, N=o, K=kk, relu=True, dscale=inv_keep,
+                                 relu_mask=self.masks[li - 1], dbias=self._b(li - 1, grad=True),
+                                 scratch=self.dg_scratch, stream=st)
+                n += 2
             elif spec.num_cat:
                 dx = self.dx0
                 ops.linear_dgrad(dy, self._w(li), None, dx, M=batch, N=o, K=kk, relu=False, stream=st)
@@ -243,9 +249,6 @@ class TrainStep:
                 dx = None
             ops.linear_wgrad(dy, x_in, self._gw(li), M=batch, N=o, K=kk, stream=st)
             n += 2  # memset (split-K) + GEMM
-            if li < L - 1:
-                ops.colsum(dy, self._b(li, grad=True), self.cs_scratch, M=batch, N=o, stream=st)
-                n += 2
             if li in bucket_of:
                 n += self._reduce_bucket(bucket_of[li])
             dy = dx

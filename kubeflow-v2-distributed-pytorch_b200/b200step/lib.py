@@ -29,8 +29,10 @@ SIGNATURES = {
     "b200_abi_version": (_i, []),
     "b200_device_sm_count": (_i, [C.POINTER(_i)]),
     "b200_preprocess": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _i, _i, _i64, _i, _i64, _i, _p]),
-    "b200_linear_fwd": (_i, [_p, _i64, _p, _i64, _p, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _u64, _p, _i, _p]),
-    "b200_linear_dgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _p]),
+    "b200_linear_fwd": (_i, [_p, _i64, _p, _i64, _p, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _u64, _p, _i, _p, _i64, _p]),
+    "b200_linear_dgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _p, _i64, _p,
+                               _p, _i64, _p]),
+    "b200_dgrad_scratch_floats": (_i64, [_i64, _i64]),
     "b200_linear_wgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _p]),
     "b200_ce_scratch_floats": (_i64, [_i]),
     "b200_ce_loss_grad": (_i, [_p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i, _f, _i, _p]),
@@ -63,7 +65,8 @@ SIGNATURES = {
 }
 
 # functions whose int return value is NOT an error code
-_NO_CHECK = {"b200_last_error", "b200_abi_version", "b200_ce_scratch_floats", "b200_colsum_scratch_floats"}
+_NO_CHECK = {"b200_last_error", "b200_abi_version", "b200_ce_scratch_floats", "b200_colsum_scratch_floats",
+             "b200_dgrad_scratch_floats"}
 
 
 class B200Error(RuntimeError):

@@ -51,18 +51,26 @@ def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x
 
 
 def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,
-               step=None, layer_id: int = 0, stream=None):
-    _cuda(x, w, bias, y)
+               step=None, layer_id: int = 0, relu_mask=None, stream=None):
+    _cuda(x, w, bias, y, relu_mask)
     get_lib().linear_fwd(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(y), y.stride(0), M, N, K,
                          dtype_code(x.dtype), FLAG_RELU if relu else 0, float(dropout_p), int(seed),
-                         ptr(step), layer_id, _stream(stream))
+                         ptr(step), layer_id, ptr(relu_mask),
+                         relu_mask.stride(0) if relu_mask is not None else 0, _stream(stream))
 
 
-def linear_dgrad(dy, w, act, dx, *, M: int, N: int, K: int, relu: bool, dscale: float = 1.0, stream=None):
-    _cuda(dy, w, act, dx)
+def dgrad_scratch_floats(M: int, K: int) -> int:
+    return int(get_lib().dgrad_scratch_floats(M, K))
+
+
+def linear_dgrad(dy, w, act, dx, *, M: int, N: int, K: int, relu: bool, dscale: float = 1.0, relu_mask=None,
+                 dbias=None, scratch=None, stream=None):
+    _cuda(dy, w, act, dx, relu_mask, dbias, scratch)
     get_lib().linear_dgrad(ptr(dy), dy.stride(0), ptr(w), w.stride(0), ptr(act),
                            act.stride(0) if act is not None else 0, ptr(dx), dx.stride(0), M, N, K,
-                           dtype_code(dy.dtype), FLAG_RELU if relu else 0, float(dscale), _stream(stream))
+                           dtype_code(dy.dtype), FLAG_RELU if relu else 0, float(dscale), ptr(relu_mask),
+                           relu_mask.stride(0) if relu_mask is not None else 0, ptr(dbias), ptr(scratch),
+                           scratch.numel() if scratch is not None else 0, _stream(stream))
 
 
 def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False, stream=None):

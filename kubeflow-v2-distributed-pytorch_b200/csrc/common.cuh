@@ -31,6 +31,8 @@ void set_error(const char* fmt, ...);
   } while (0)
 
 int sm_count();  // cached per process (current device at first call)
+// out[c] = sum_r partials[r * row_stride + c] for c < ncols, fixed order (defined in loss.cu)
+int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out, cudaStream_t st);
 
 // ---- small device helpers -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -126,6 +128,21 @@ __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, 
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
                "r"(smem_u32(smem_src)), "r"(bytes)
                : "memory");
+}
+// 2-D tiled store shared -> global (clips to the tensor bounds)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void st_shared_v4(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() {

@@ -9,7 +9,8 @@
 // tcgen05.mma (UMMA 128 x 256 x {16 bf16 | 8 tf32}) into double-buffered TMEM accumulators, and drained
 // by four epilogue warps with tcgen05.ld while the next tile's MMAs run.
 //
-// Roles (256 threads): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator, warps4-7 = epilogue.
+// Roles (384 threads): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator, warps4-11 = epilogue
+// (two warps per TMEM lane quarter, each draining half of the tile's columns).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -18,13 +19,17 @@ namespace b200 {
 
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 256;
-constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_THREADS = 384;  // 4 control warps + 8 epilogue warps
+constexpr int EPI_WARPS = 8;
 constexpr int A_TILE_BYTES = BLOCK_M * 128;  // 128 rows (or 128-byte swizzle rows) per stage
 constexpr int B_TILE_BYTES = BLOCK_N * 128;
 constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;  // 48 KiB
 constexpr int NUM_STAGES = 4;                              // 192 KiB ring
 constexpr int NUM_ACC = 2;                                 // TMEM accumulator double buffer (2 x 256 columns)
-constexpr int GEMM_SMEM_BYTES = NUM_STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int EPI_BUF_BYTES = 32 * 128;                       // one epilogue slab: 32 rows x 128 B, one per warp
+constexpr int EPI_STAGING_BYTES = EPI_WARPS * EPI_BUF_BYTES;  // 32 KiB
+constexpr int GEMM_SMEM_BYTES =
+    NUM_STAGES * STAGE_BYTES + EPI_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
 
@@ -37,6 +42,10 @@ struct GemmParams {
   const float* bias;
   const void* act;
   long long ldact;
+  uint32_t* mask_out;        // fwd: bit j of word [row, col/32] = (output[row, col] > 0)
+  const uint32_t* mask_in;   // dgrad: same layout, replaces reading `act`
+  long long ldmask;          // row stride of the bit mask in 32-bit words
+  float* cs_partials;        // dgrad: per (m_tile, warp) column sums of the stored output, [m_tiles*4, N]
   float dscale;
   int flags;
   float dropout_p;
@@ -68,7 +77,7 @@ __host__ __device__ constexpr uint32_t make_idesc(int fmt, int a_mn, int b_mn, i
 template <int kTf32, bool kAMN, bool kBMN, int kEpi>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const GemmParams p) {
+            const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int ESIZE = kTf32 ? 4 : 2;
   constexpr int BLOCK_K = 128 / ESIZE;          // one 128-byte swizzle row of K (K-major) / BLOCK_K rows (MN-major)
   constexpr int UMMA_K = 32 / ESIZE;            // 16 (bf16) or 8 (tf32)
@@ -80,7 +89,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES + EPI_STAGING_BYTES);
   uint64_t* full_bar = bars;                       // [NUM_STAGES]
   uint64_t* empty_bar = bars + NUM_STAGES;         // [NUM_STAGES]
   uint64_t* acc_full = bars + 2 * NUM_STAGES;      // [NUM_ACC]
@@ -93,6 +102,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (kEpi != EPI_WGRAD) tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < NUM_STAGES; ++i) {
@@ -101,7 +111,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < NUM_ACC; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrive per epilogue warp
+      mbar_init(&acc_empty[i], EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -184,9 +194,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> global =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    // ===================== epilogue: TMEM -> registers -> (swizzled smem -> TMA store | red.add) =============
+    // Two warps share each TMEM lane quarter (a warp may only read lanes 32*(warp%4)..+31) and split the tile's
+    // columns: with a single warp per scheduler the epilogue ALU work could not hide its own issue latency.
+    const int q = warp & 3;             // TMEM lane quarter
+    const int chalf = (warp - 4) >> 2;  // column half of the tile this warp drains
     int it = 0;
+    uint8_t* sbuf_ptr = smem + NUM_STAGES * STAGE_BYTES + (warp - 4) * EPI_BUF_BYTES;
+    // dgrad: running column sums of everything this warp stores (lane i owns column chunk*32 + i); the host sizes
+    // the grid to a multiple of n_tiles, so a CTA sees the same n_tile in every tile it processes
+    float csacc[4] = {0.f, 0.f, 0.f, 0.f};
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
       const int tile = w % tiles;
       const int m0 = (tile / p.n_tiles) * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
@@ -194,18 +211,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&acc_full[a], aph);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
+      const int row0 = m0 + q * 32;
+      const int row = row0 + lane;
       const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BLOCK_N;
+      if constexpr (kEpi == EPI_WGRAD) {
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        const int col0 = n0 + c * 32;
-        if (col0 >= p.N) break;  // warp-uniform
-        uint32_t v[32];
-        tmem_ld32(taddr + c * 32, v);
-        tmem_ld_wait();
-        if (!row_ok) continue;
-        if constexpr (kEpi == EPI_WGRAD) {
+        for (int c = chalf * (BLOCK_N / 64); c < (chalf + 1) * (BLOCK_N / 64); ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (!row_ok) continue;
           float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
           const bool atomic = (p.splits > 1) || (p.flags & B200_FLAG_ACCUMULATE);
 #pragma unroll
@@ -219,87 +237,148 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
-        } else {
-          float f[32];
+        }
+      } else {
+        // Output leaves in groups of one 128-byte row per thread (64 bf16 / 32 fp32 columns): each warp builds a
+        // 32-row x 128-byte slab in 128B-swizzled shared memory and one lane hands it to the TMA engine, which
+        // writes full lines and clips rows >= M / columns >= N.
+        constexpr int GROUP_COLS = EPR;
+        constexpr int LDS_PER_GROUP = GROUP_COLS / 32;
+        constexpr int GROUPS_PER_WARP = BLOCK_N / GROUP_COLS / 2;
+        static_assert(GROUPS_PER_WARP * LDS_PER_GROUP == 4, "csacc holds four 32-column chunks per warp");
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if constexpr (kEpi == EPI_FWD) {
-            if (p.bias != nullptr) {
+        for (int gi = 0; gi < GROUPS_PER_WARP; ++gi) {
+          const int g = chalf * GROUPS_PER_WARP + gi;
+          const int gcol0 = n0 + g * GROUP_COLS;
+          if (gcol0 >= p.N) break;  // warp-uniform
+          if (lane == 0) bulk_wait_read<0>();  // the previous store of this warp has finished reading the slab
+          __syncwarp();
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
-            }
-            if (p.flags & B200_FLAG_RELU) {
+          for (int h = 0; h < LDS_PER_GROUP; ++h) {
+            const int col0 = gcol0 + h * 32;
+            uint32_t v[32];
+            tmem_ld32(taddr + g * GROUP_COLS + h * 32, v);
+            tmem_ld_wait();
+            float f[32];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
-            }
-            if (p.dropout_p > 0.0f) {
-              // keep iff u32 >= p * 2^32; counter = linear element index / 4, key = (seed, layer, step)
-              const uint32_t thresh = (uint32_t)fminf(p.dropout_p * 4294967296.0f, 4294967040.0f);
-              const float inv_keep = 1.0f / (1.0f - p.dropout_p);
-              const uint32_t stepv = p.step ? (uint32_t)(*p.step) : 0u;
-              const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32) ^ stepv);
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) {
-                const unsigned long long e = (unsigned long long)row * (unsigned long long)p.N + (col0 + j);
-                const uint4 r = philox4x32_10(
-                    make_uint4((uint32_t)(e >> 2), (uint32_t)(e >> 34), (uint32_t)p.layer_id, 0u), key);
-                f[j + 0] = (r.x >= thresh) ? f[j + 0] * inv_keep : 0.0f;
-                f[j + 1] = (r.y >= thresh) ? f[j + 1] * inv_keep : 0.0f;
-                f[j + 2] = (r.z >= thresh) ? f[j + 2] * inv_keep : 0.0f;
-                f[j + 3] = (r.w >= thresh) ? f[j + 3] * inv_keep : 0.0f;
-              }
-            }
-          } else {  // EPI_DGRAD
-            if (p.dscale != 1.0f) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] *= p.dscale;
-            }
-            if ((p.flags & B200_FLAG_RELU) && p.act != nullptr) {
-              if constexpr (kTf32) {
-                const float* ar = reinterpret_cast<const float*>(p.act) + (long long)row * p.ldact + col0;
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            if constexpr (kEpi == EPI_FWD) {
+              if (p.bias != nullptr) {
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
-                  if (col0 + j < p.N) {
-                    const float4 h = *reinterpret_cast<const float4*>(ar + j);
-                    f[j + 0] = h.x > 0.f ? f[j + 0] : 0.f;
-                    f[j + 1] = h.y > 0.f ? f[j + 1] : 0.f;
-                    f[j + 2] = h.z > 0.f ? f[j + 2] : 0.f;
-                    f[j + 3] = h.w > 0.f ? f[j + 3] : 0.f;
+                  if (col0 + j < p.N) {  // N % 4 == 0: a float4 never straddles the edge
+                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                    f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
                   }
                 }
-              } else {
-                const uint16_t* ar = reinterpret_cast<const uint16_t*>(p.act) + (long long)row * p.ldact + col0;
+              }
+              if (p.flags & B200_FLAG_RELU) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                  if (col0 + j < p.N) {
-                    const uint4 h = *reinterpret_cast<const uint4*>(ar + j);
-                    const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+                for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+              }
+              if (p.dropout_p > 0.0f) {
+                // keep iff u32 >= p * 2^32; counter = linear element index / 4, key = (seed, layer, step)
+                const uint32_t thresh = (uint32_t)fminf(p.dropout_p * 4294967296.0f, 4294967040.0f);
+                const float inv_keep = 1.0f / (1.0f - p.dropout_p);
+                const uint32_t stepv = p.step ? (uint32_t)(*p.step) : 0u;
+                const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32) ^ stepv);
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                      f[j + 2 * t + 0] = bf16_lo(hw[t]) > 0.f ? f[j + 2 * t + 0] : 0.f;
-                      f[j + 2 * t + 1] = bf16_hi(hw[t]) > 0.f ? f[j + 2 * t + 1] : 0.f;
+                for (int j = 0; j < 32; j += 4) {
+                  const unsigned long long e = (unsigned long long)row * (unsigned long long)p.N + (col0 + j);
+                  const uint4 r = philox4x32_10(
+                      make_uint4((uint32_t)(e >> 2), (uint32_t)(e >> 34), (uint32_t)p.layer_id, 0u), key);
+                  f[j + 0] = (r.x >= thresh) ? f[j + 0] * inv_keep : 0.0f;
+                  f[j + 1] = (r.y >= thresh) ? f[j + 1] * inv_keep : 0.0f;
+                  f[j + 2] = (r.z >= thresh) ? f[j + 2] * inv_keep : 0.0f;
+                  f[j + 3] = (r.w >= thresh) ? f[j + 3] * inv_keep : 0.0f;
+                }
+              }
+              if (p.mask_out != nullptr && row_ok) {  // 1 bit per element for the backward ReLU(/dropout) mask
+                uint32_t mbits = 0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) mbits |= (f[j] > 0.0f) ? (1u << j) : 0u;
+                p.mask_out[(long long)row * p.ldmask + (col0 >> 5)] = mbits;
+              }
+            } else {  // EPI_DGRAD
+              if (p.dscale != 1.0f) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] *= p.dscale;
+              }
+              if ((p.flags & B200_FLAG_RELU) && p.mask_in != nullptr) {
+                const uint32_t mbits = row_ok ? __ldg(p.mask_in + (long long)row * p.ldmask + (col0 >> 5)) : 0u;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] = (mbits & (1u << j)) ? f[j] : 0.0f;
+              } else if ((p.flags & B200_FLAG_RELU) && p.act != nullptr && row_ok) {
+                if constexpr (kTf32) {
+                  const float* ar = reinterpret_cast<const float*>(p.act) + (long long)row * p.ldact + col0;
+#pragma unroll
+                  for (int j = 0; j < 32; j += 4) {
+                    if (col0 + j < p.N) {
+                      const float4 hh = *reinterpret_cast<const float4*>(ar + j);
+                      f[j + 0] = hh.x > 0.f ? f[j + 0] : 0.f;
+                      f[j + 1] = hh.y > 0.f ? f[j + 1] : 0.f;
+                      f[j + 2] = hh.z > 0.f ? f[j + 2] : 0.f;
+                      f[j + 3] = hh.w > 0.f ? f[j + 3] : 0.f;
+                    }
+                  }
+                } else {
+                  const uint16_t* ar = reinterpret_cast<const uint16_t*>(p.act) + (long long)row * p.ldact + col0;
+#pragma unroll
+                  for (int j = 0; j < 32; j += 8) {
+                    if (col0 + j < p.N) {
+                      const uint4 hh = *reinterpret_cast<const uint4*>(ar + j);
+                      const uint32_t hw[4] = {hh.x, hh.y, hh.z, hh.w};
+#pragma unroll
+                      for (int t = 0; t < 4; ++t) {
+                        f[j + 2 * t + 0] = bf16_lo(hw[t]) > 0.f ? f[j + 2 * t + 0] : 0.f;
+                        f[j + 2 * t + 1] = bf16_hi(hw[t]) > 0.f ? f[j + 2 * t + 1] : 0.f;
+                      }
                     }
                   }
                 }
               }
             }
+            if constexpr (kEpi == EPI_DGRAD) {
+              if (p.cs_partials != nullptr) {
+                // column sums over this warp's 32 rows of what is stored (rounded to the output dtype):
+                // halving butterfly, 31 shuffles, lane i ends with the sum of column col0 + i
+                float r[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  r[j] = kTf32 ? f[j] : __bfloat162float(__float2bfloat16_rn(f[j]));
+#pragma unroll
+                for (int half = 16; half >= 1; half >>= 1) {
+                  const bool upper = (lane & half) != 0;
+#pragma unroll
+                  for (int j = 0; j < half; ++j) {
+                    const float send = upper ? r[j] : r[j + half];
+                    const float keep = upper ? r[j + half] : r[j];
+                    r[j] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+                  }
+                }
+                csacc[gi * LDS_PER_GROUP + h] += r[0];
+              }
+            }
+            // registers -> swizzled slab: 16-byte chunk c of row `lane` lives at chunk (c ^ (lane & 7))
+            const uint32_t srow = smem_u32(sbuf_ptr) + lane * 128;
+            if constexpr (kTf32) {
+#pragma unroll
+              for (int c = 0; c < 8; ++c)
+                st_shared_v4(srow + ((c ^ (lane & 7)) << 4), __float_as_uint(f[4 * c]), __float_as_uint(f[4 * c + 1]),
+                             __float_as_uint(f[4 * c + 2]), __float_as_uint(f[4 * c + 3]));
+            } else {
+#pragma unroll
+              for (int c = 0; c < 4; ++c)
+                st_shared_v4(srow + (((h * 4 + c) ^ (lane & 7)) << 4), pack_bf16x2(f[8 * c], f[8 * c + 1]),
+                             pack_bf16x2(f[8 * c + 2], f[8 * c + 3]), pack_bf16x2(f[8 * c + 4], f[8 * c + 5]),
+                             pack_bf16x2(f[8 * c + 6], f[8 * c + 7]));
+            }
           }
-          // store in the operand dtype
-          if constexpr (kTf32) {
-            float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              if (col0 + j < p.N)
-                *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-          } else {
-            uint16_t* o = reinterpret_cast<uint16_t*>(p.out) + (long long)row * p.ldo + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8)
-              if (col0 + j < p.N)
-                *reinterpret_cast<uint4*>(o + j) =
-                    make_uint4(pack_bf16x2(f[j], f[j + 1]), pack_bf16x2(f[j + 2], f[j + 3]),
-                               pack_bf16x2(f[j + 4], f[j + 5]), pack_bf16x2(f[j + 6], f[j + 7]));
+          fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
+          __syncwarp();
+          if (lane == 0 && row0 < p.M) {
+            tma_store_2d(&tmC, sbuf_ptr, gcol0, row0);
+            bulk_commit();
           }
         }
       }
@@ -307,6 +386,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[a]);
     }
+    if constexpr (kEpi == EPI_DGRAD) {
+      if (p.cs_partials != nullptr) {
+        // one partial row per (CTA group, lane quarter); row stride = n_tiles * BLOCK_N
+        const long long prow = (long long)(blockIdx.x / p.n_tiles) * 4 + q;
+        float* dst = p.cs_partials + prow * ((long long)p.n_tiles * BLOCK_N) +
+                     (blockIdx.x % p.n_tiles) * BLOCK_N + chalf * (BLOCK_N / 2) + lane;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) dst[k * 32] = csacc[k];
+      }
+    }
+    if (lane == 0) bulk_wait_all();  // all output writes issued by this warp have completed
   }
 
   tc_fence_before();
@@ -340,7 +430,7 @@ static EncodeTiledFn get_encode_fn() {
 // 2-D row-major tensor [outer, inner] with row stride ld (elements); box = box_inner x box_outer, 128B swizzle.
 // mn_major operands in fp32 use the 32-byte-atom flavour of the 128B swizzle (see make_smem_desc).
 static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
-                     uint32_t box_inner, uint32_t box_outer, bool mn_major = false) {
+                     uint32_t box_inner, uint32_t box_outer, bool mn_major = false, bool is_output = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return 1;
   const uint64_t es = tf32 ? 4 : 2;
@@ -355,7 +445,8 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
   // plain FLOAT32 the tensor core would truncate the low 13 mantissa bits, a biased error that accumulates.
   static const bool tf32_truncate = getenv("B200STEP_TF32_TRUNCATE") != nullptr;  // debugging knob
   const CUtensorMapDataType dt = !tf32 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
-                                 : (tf32_truncate ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32);
+                                 : ((tf32_truncate || is_output) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                                                 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32);
   CUresult r = fn(m, dt, 2,
                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
@@ -367,7 +458,8 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
 }
 
 template <int kTf32, bool kAMN, bool kBMN, int kEpi>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+                       cudaStream_t st, int grid_override = 0) {
   auto kern = gemm_kernel<kTf32, kAMN, kBMN, kEpi>;
   static bool configured = false;  // per instantiation
   if (!configured) {
@@ -375,8 +467,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     configured = true;
   }
   const int total = p.m_tiles * p.n_tiles * p.splits;
-  const int grid = total < sm_count() ? total : sm_count();
-  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, p);
+  const int grid = grid_override > 0 ? grid_override : (total < sm_count() ? total : sm_count());
+  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, tc, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -399,14 +491,18 @@ using namespace b200;
 extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
                                void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
                                float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
-                               b200_stream_t stream) {
+                               uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream) {
   if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(relu_mask == nullptr || ldmask * 32 >= N, "relu_mask row stride %lld words is too small for N=%lld",
+               (long long)ldmask, (long long)N);
   B200_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "dropout_p=%f out of [0,1)", dropout_p);
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64;
   CUtensorMap ta, tb;
   if (int r = make_tmap(&ta, tf32, x, K, M, ldx, bk, BLOCK_M)) return r;
   if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, BLOCK_N)) return r;
+  CUtensorMap tc;  // output slabs: one 128-byte row x 32 rows per TMA store
+  if (int r = make_tmap(&tc, tf32, y, N, M, ldy, bk, 32, false, true)) return r;
   GemmParams p{};
   p.M = (int)M; p.N = (int)N;
   p.k_blocks = (int)((K + bk - 1) / bk);
@@ -415,15 +511,21 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f;
   p.dropout_p = dropout_p; p.seed = seed; p.step = step; p.layer_id = layer_id;
+  p.mask_out = relu_mask; p.ldmask = ldmask;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, p, st)
-              : launch_gemm<0, false, false, EPI_FWD>(ta, tb, p, st);
+  return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, tc, p, st)
+              : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);
 }
 
 extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw, const void* act,
                                  int64_t ldact, void* dx, int64_t lddx, int64_t M, int64_t N, int64_t K,
-                                 int dtype, int flags, float dscale, b200_stream_t stream) {
+                                 int dtype, int flags, float dscale, const uint32_t* relu_mask, int64_t ldmask,
+                                 float* dbias, float* scratch, int64_t scratch_floats, b200_stream_t stream) {
   if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(relu_mask == nullptr || ldmask * 32 >= K, "relu_mask row stride %lld words is too small for K=%lld",
+               (long long)ldmask, (long long)K);
+  B200_REQUIRE(dbias == nullptr || (scratch != nullptr && scratch_floats >= b200_dgrad_scratch_floats(M, K)),
+               "dgrad bias-gradient scratch too small: need %lld floats", (long long)b200_dgrad_scratch_floats(M, K));
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64;   // contraction (over N) elements per stage
   const int epr = tf32 ? 32 : 64;  // elements per 128-byte row
@@ -432,6 +534,8 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
   if (int r = make_tmap(&ta, tf32, dy, N, M, lddy, bk, BLOCK_M)) return r;
   // B(n'=k, k'=n) = W[n, k]: output dim contiguous (MN-major); box = 128 B of k x bk rows of n
   if (int r = make_tmap(&tb, tf32, w, K, N, ldw, epr, bk, true)) return r;
+  CUtensorMap tc;
+  if (int r = make_tmap(&tc, tf32, dx, K, M, lddx, epr, 32, false, true)) return r;
   GemmParams p{};
   p.M = (int)M; p.N = (int)K;
   p.k_blocks = (int)((N + bk - 1) / bk);
@@ -439,9 +543,26 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
   p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = dx; p.ldo = lddx; p.act = act; p.ldact = ldact; p.flags = flags; p.dscale = dscale;
+  p.mask_in = relu_mask; p.ldmask = ldmask; p.cs_partials = dbias ? scratch : nullptr;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, p, st)
-              : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, p, st);
+  // with bias-gradient accumulation every CTA must keep one n_tile: grid = multiple of n_tiles
+  const int total = p.m_tiles * p.n_tiles;
+  int grid = total < sm_count() ? total : sm_count();
+  grid = grid / p.n_tiles * p.n_tiles;
+  B200_REQUIRE(grid >= p.n_tiles, "dgrad: too many column tiles (%d) for this device", p.n_tiles);
+  if (int r = tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st, grid)
+                   : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st, grid))
+    return r;
+  if (dbias)
+    return launch_reduce_partials(scratch, (grid / p.n_tiles) * 4, p.n_tiles * BLOCK_N, (int)K, dbias, st);
+  return 0;
+}
+
+// one partial row per (CTA group, lane quarter), row stride n_tiles*BLOCK_N: at most sm_count * 4 * BLOCK_N floats
+extern "C" int64_t b200_dgrad_scratch_floats(int64_t M, int64_t K) {
+  (void)M;
+  (void)K;
+  return (int64_t)sm_count() * 4 * BLOCK_N;
 }
 
 extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx, float* dw,
@@ -474,6 +595,6 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
     // split-K partial tiles are summed with red.add: start from zero
     B200_CHECK_CUDA(cudaMemset2DAsync(dw, lddw * sizeof(float), 0, K * sizeof(float), N, st));
   }
-  return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, p, st)
-              : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, p, st);
+  return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
+              : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st);
 }

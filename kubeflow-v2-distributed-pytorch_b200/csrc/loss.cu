@@ -142,30 +142,50 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
   }
 }
 
-// out[c] = sum over partial rows (fixed order); column `loss_col` (if >= 0) is scaled and written to loss_out
-__global__ void reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
-                                       float* __restrict__ out, int loss_col, float loss_scale,
-                                       float* __restrict__ loss_out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= row_stride) return;
+// out[c] = sum over partial rows in a fixed order; column `loss_col` (if >= 0) is scaled and written to loss_out.
+// One CTA per 32 columns: warp w walks rows w, w+8, ... (128 contiguous bytes per warp and row, four
+// independent loads in flight), then the 8 per-warp sums are combined in a fixed order -> deterministic.
+constexpr int RED_THREADS = 256;
+__global__ void __launch_bounds__(RED_THREADS)
+reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
+                       float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out) {
+  __shared__ float part[RED_THREADS / 32][33];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c = blockIdx.x * 32 + lane;
   const bool is_loss = (c == loss_col);
-  if (c >= ncols && !is_loss) return;
-  if (!is_loss && out == nullptr) return;
+  const bool live = c < row_stride && (c < ncols || is_loss) && (is_loss || out != nullptr);
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  int r = 0;
-  for (; r + 4 <= nrows; r += 4) {
-    s0 += partials[(long long)(r + 0) * row_stride + c];
-    s1 += partials[(long long)(r + 1) * row_stride + c];
-    s2 += partials[(long long)(r + 2) * row_stride + c];
-    s3 += partials[(long long)(r + 3) * row_stride + c];
+  if (live) {
+    const float* col = partials + c;
+    int r = warp;
+    for (; r + 24 < nrows; r += 32) {
+      s0 += col[(long long)(r + 0) * row_stride];
+      s1 += col[(long long)(r + 8) * row_stride];
+      s2 += col[(long long)(r + 16) * row_stride];
+      s3 += col[(long long)(r + 24) * row_stride];
+    }
+    for (; r < nrows; r += 8) s0 += col[(long long)r * row_stride];
   }
-  for (; r < nrows; ++r) s0 += partials[(long long)r * row_stride + c];
-  const float s = (s0 + s1) + (s2 + s3);
-  if (is_loss) {
-    if (loss_out) loss_out[0] = s * loss_scale;
-  } else {
-    out[c] = s;
+  part[warp][lane] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (warp == 0 && live) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < RED_THREADS / 32; ++w) s += part[w][lane];
+    if (is_loss) {
+      if (loss_out) loss_out[0] = s * loss_scale;
+    } else {
+      out[c] = s;
+    }
   }
+}
+
+int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out,
+                           cudaStream_t st) {
+  reduce_partials_kernel<<<(row_stride + 31) / 32, RED_THREADS, 0, st>>>(partials, nrows, row_stride, ncols, out, -1, 0.f,
+                                                                 nullptr);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 // ---- column sum (hidden-layer bias gradients) -------------------------------------------------------
@@ -272,7 +292,7 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
                                                             num_classes, grad_scale, dbias != nullptr);
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
-  reduce_partials_kernel<<<(stride + 255) / 256, 256, 0, st>>>(scratch, grid, stride, num_classes, dbias,
+  reduce_partials_kernel<<<(stride + 31) / 32, RED_THREADS, 0, st>>>(scratch, grid, stride, num_classes, dbias,
                                                              num_classes, 1.0f / (float)batch, loss_out);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -301,7 +321,7 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   else
     colsum_kernel<false><<<slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
   B200_CHECK_CUDA(cudaGetLastError());
-  reduce_partials_kernel<<<(int)((N + 255) / 256), 256, 0, st>>>(scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
+  reduce_partials_kernel<<<(int)((N + 31) / 32), RED_THREADS, 0, st>>>(scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -363,7 +383,7 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   else
     colsum_kernel<false><<<(int)slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
   B200_CHECK_CUDA(cudaGetLastError());
-  reduce_partials_kernel<<<(int)((N + 255) / 256), 256, 0, st>>>(scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
+  reduce_partials_kernel<<<(int)((N + 31) / 32), RED_THREADS, 0, st>>>(scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -95,6 +95,39 @@ def test_linear_wgrad(ops, dtype, M, N, K):
     assert (dw.double() - 2 * ref).abs().max().item() <= tol * 8
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,K", [(1000, 512, 448), (4096, 1000, 512), (65536, 512, 512)])
+def test_relu_bitmask_and_fused_bias_grad(ops, dtype, M, N, K):
+    """fwd writes 1 bit per output (y > 0); the next layer's dgrad consumes it instead of re-reading the
+    activation, and emits the column sums of what it stores (= bias gradient of the layer below)."""
+    x = _rand((M, K), dtype, 1)
+    w = _rand((N, K), dtype, 2, 0.05)
+    y = torch.empty((M, N), dtype=dtype, device="cuda")
+    words = ((N + 31) // 32 + 3) // 4 * 4
+    mask = torch.zeros((M, words), dtype=torch.int32, device="cuda")
+    ops.linear_fwd(x, w, None, y, M=M, N=N, K=K, relu=True, relu_mask=mask)
+    torch.cuda.synchronize()
+    bits = ((mask[:, :, None] >> torch.arange(32, device="cuda", dtype=torch.int32)) & 1).reshape(M, -1)[:, :N]
+    assert torch.equal(bits.bool(), y > 0)                       # bit-exact
+    # backward of a layer whose INPUT was y: dx[M,N] = (dy2[M,N2] @ w2[N2,N]) * (y > 0)
+    N2 = 256
+    dy2 = _rand((M, N2), dtype, 4)
+    w2 = _rand((N2, N), dtype, 5, 0.05)
+    dx_act = torch.empty((M, N), dtype=dtype, device="cuda")
+    dx_mask = torch.full((M, N), float("nan"), dtype=dtype, device="cuda")
+    db = torch.full((N,), float("nan"), device="cuda")
+    scratch = torch.empty(ops.dgrad_scratch_floats(M, N), device="cuda")
+    ops.linear_dgrad(dy2, w2, y, dx_act, M=M, N=N2, K=N, relu=True)
+    ops.linear_dgrad(dy2, w2, None, dx_mask, M=M, N=N2, K=N, relu=True, relu_mask=mask, dbias=db, scratch=scratch)
+    torch.cuda.synchronize()
+    assert torch.equal(dx_act, dx_mask)                          # same kernel math, mask from bits == mask from y
+    torch.testing.assert_close(db.double(), dx_mask.double().sum(0), rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
+    db2 = torch.empty_like(db)
+    ops.linear_dgrad(dy2, w2, None, dx_mask, M=M, N=N2, K=N, relu=True, relu_mask=mask, dbias=db2, scratch=scratch)
+    torch.cuda.synchronize()
+    assert torch.equal(db, db2)                                  # deterministic reduction order
+
+
 def test_gemm_rejects_misaligned(ops):
     from b200step.lib import B200Error
 
