@@ -21,15 +21,12 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 256;
 constexpr int GEMM_THREADS = 384;  // 4 control warps + 8 epilogue warps
 constexpr int EPI_WARPS = 8;
-constexpr int A_TILE_BYTES = BLOCK_M * 128;  // 128 rows (or 128-byte swizzle rows) per stage
-constexpr int B_TILE_BYTES = BLOCK_N * 128;
-constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;  // 48 KiB
-constexpr int NUM_STAGES = 4;                              // 192 KiB ring
-constexpr int NUM_ACC = 2;                                 // TMEM accumulator double buffer (2 x 256 columns)
+constexpr int A_TILE_BYTES = BLOCK_M * 128;  // 128 rows (or 128-byte swizzle rows) per stage and CTA
+constexpr int PIPE_BYTES = 192 * 1024;       // operand ring: 4 x 48 KiB (single CTA) or 6 x 32 KiB (CTA pair)
+constexpr int NUM_ACC = 2;                   // TMEM accumulator double buffer (2 x 256 columns)
 constexpr int EPI_BUF_BYTES = 32 * 128;                       // one epilogue slab: 32 rows x 128 B, one per warp
 constexpr int EPI_STAGING_BYTES = EPI_WARPS * EPI_BUF_BYTES;  // 32 KiB
-constexpr int GEMM_SMEM_BYTES =
-    NUM_STAGES * STAGE_BYTES + EPI_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int GEMM_SMEM_BYTES = PIPE_BYTES + EPI_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
 
@@ -74,7 +71,11 @@ __host__ __device__ constexpr uint32_t make_idesc(int fmt, int a_mn, int b_mn, i
          ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-template <int kTf32, bool kAMN, bool kBMN, int kEpi>
+// kCtas = 2: the two CTAs of a cluster form a pair (tcgen05 cta_group::2).  The pair owns a 256 x 256 tile: each CTA
+// loads its own 128 rows of A and HALF of the B tile (so L2->smem operand traffic per FLOP drops by a third), the
+// leader CTA's single MMA thread issues M=256 UMMAs that read both CTAs' shared memory and write both CTAs'
+// TMEM, and each CTA drains its own 128 accumulator rows.
+template <int kTf32, bool kAMN, bool kBMN, int kEpi, int kCtas>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
@@ -85,11 +86,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr int MN_BOX_BYTES = BLOCK_K * 128;   // one TMA box of an MN-major operand: BLOCK_K rows x 128 B
   constexpr uint32_t MN_SBO = kTf32 ? 512 : 1024;   // swizzle atom height: 4 rows (32B atoms) / 8 rows (16B atoms)
   constexpr uint32_t MN_LAYOUT = kTf32 ? 1 : 2;
-  constexpr uint32_t IDESC = make_idesc(kTf32 ? 2 : 1, kAMN, kBMN, BLOCK_M, BLOCK_N);
+  constexpr uint32_t IDESC = make_idesc(kTf32 ? 2 : 1, kAMN, kBMN, BLOCK_M * kCtas, BLOCK_N);
+  constexpr int B_ROWS = BLOCK_N / kCtas;             // B-tile rows (output columns) staged by this CTA
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_ROWS * 128;
+  constexpr int NUM_STAGES = PIPE_BYTES / STAGE_BYTES;
+  constexpr int TILE_M = BLOCK_M * kCtas;             // output rows per work item (per CTA pair)
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES + EPI_STAGING_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + PIPE_BYTES + EPI_STAGING_BYTES);
   uint64_t* full_bar = bars;                       // [NUM_STAGES]
   uint64_t* empty_bar = bars + NUM_STAGES;         // [NUM_STAGES]
   uint64_t* acc_full = bars + 2 * NUM_STAGES;      // [NUM_ACC]
@@ -98,6 +103,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = kCtas == 2 ? (int)cluster_ctarank() : 0;   // 0 = leader of the pair
+  const int unit = blockIdx.x / kCtas, nunits = gridDim.x / kCtas;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -111,13 +118,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < NUM_ACC; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], EPI_WARPS);  // one arrive per epilogue warp
+      mbar_init(&acc_empty[i], EPI_WARPS * kCtas);  // one arrive per epilogue warp (of both CTAs)
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, NUM_ACC * BLOCK_N);
+  if (warp == 2) {
+    if constexpr (kCtas == 2) tmem_alloc_pair(tmem_slot, NUM_ACC * BLOCK_N);
+    else tmem_alloc(tmem_slot, NUM_ACC * BLOCK_N);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCtas == 2) cluster_sync_all();  // peer barriers must be initialised before any remote arrive
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -129,29 +140,50 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      for (int w = unit; w < total; w += nunits) {
         const int tile = w % tiles, split = w / tiles;
-        const int m0 = (tile / p.n_tiles) * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
+        const int m0 = (tile / p.n_tiles) * TILE_M + rank * BLOCK_M;     // this CTA's rows of A
+        const int n0 = (tile % p.n_tiles) * BLOCK_N + rank * B_ROWS;     // this CTA's share of the B tile
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
           uint8_t* sa = smem + s * STAGE_BYTES;
           uint8_t* sb = sa + A_TILE_BYTES;
-          if constexpr (!kAMN) {
-            tma_load_2d(sa, &tmA, &full_bar[s], kb * BLOCK_K, m0);
-          } else {
+          if constexpr (kCtas == 2) {
+            // both CTAs' bytes are credited to the LEADER's full barrier (the MMA thread waits there)
+            if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+            const uint32_t fb = smem_u32(&full_bar[s]) & 0xFEFFFFFFu;  // same offset in the leader CTA
+            if constexpr (!kAMN) {
+              tma_load_2d_pair(sa, &tmA, fb, kb * BLOCK_K, m0);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BLOCK_M / EPR; ++j)
-              tma_load_2d(sa + j * MN_BOX_BYTES, &tmA, &full_bar[s], m0 + j * EPR, kb * BLOCK_K);
-          }
-          if constexpr (!kBMN) {
-            tma_load_2d(sb, &tmB, &full_bar[s], kb * BLOCK_K, n0);
-          } else {
+              for (int j = 0; j < BLOCK_M / EPR; ++j)
+                tma_load_2d_pair(sa + j * MN_BOX_BYTES, &tmA, fb, m0 + j * EPR, kb * BLOCK_K);
+            }
+            if constexpr (!kBMN) {
+              tma_load_2d_pair(sb, &tmB, fb, kb * BLOCK_K, n0);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / EPR; ++j)
-              tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], n0 + j * EPR, kb * BLOCK_K);
+              for (int j = 0; j < B_ROWS / EPR; ++j)
+                tma_load_2d_pair(sb + j * MN_BOX_BYTES, &tmB, fb, n0 + j * EPR, kb * BLOCK_K);
+            }
+          } else {
+            mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+            if constexpr (!kAMN) {
+              tma_load_2d(sa, &tmA, &full_bar[s], kb * BLOCK_K, m0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BLOCK_M / EPR; ++j)
+                tma_load_2d(sa + j * MN_BOX_BYTES, &tmA, &full_bar[s], m0 + j * EPR, kb * BLOCK_K);
+            }
+            if constexpr (!kBMN) {
+              tma_load_2d(sb, &tmB, &full_bar[s], kb * BLOCK_K, n0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < B_ROWS / EPR; ++j)
+                tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], n0 + j * EPR, kb * BLOCK_K);
+            }
           }
           if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
         }
@@ -159,11 +191,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+      for (int w = unit; w < total; w += nunits, ++it) {
         const int split = w / tiles;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
@@ -185,12 +217,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                      : make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t bd = kBMN ? make_smem_desc(sb + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT)
                                      : make_smem_desc(sb + k * 32, 16, 1024);
-            umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (kCtas == 2) umma_ss_pair<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs retire
+          // frees the smem stage (in both CTAs of a pair) once these MMAs retire
+          if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[s], 3);
+          else umma_commit(&empty_bar[s]);
           if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
         }
-        umma_commit(&acc_full[a]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs)
+        if constexpr (kCtas == 2) umma_commit_pair(&acc_full[a], 3);
+        else umma_commit(&acc_full[a]);
       }
     }
   } else if (warp >= 4) {
@@ -200,13 +237,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int q = warp & 3;             // TMEM lane quarter
     const int chalf = (warp - 4) >> 2;  // column half of the tile this warp drains
     int it = 0;
-    uint8_t* sbuf_ptr = smem + NUM_STAGES * STAGE_BYTES + (warp - 4) * EPI_BUF_BYTES;
+    uint8_t* sbuf_ptr = smem + PIPE_BYTES + (warp - 4) * EPI_BUF_BYTES;
     // dgrad: running column sums of everything this warp stores (lane i owns column chunk*32 + i); the host sizes
     // the grid to a multiple of n_tiles, so a CTA sees the same n_tile in every tile it processes
     float csacc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+    for (int w = unit; w < total; w += nunits, ++it) {
       const int tile = w % tiles;
-      const int m0 = (tile / p.n_tiles) * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
+      const int m0 = (tile / p.n_tiles) * TILE_M + rank * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
       const int a = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&acc_full[a], aph);
@@ -384,14 +421,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[a]);
+      if (lane == 0) {  // the accumulator stage may be overwritten: tell the (leader's) MMA thread
+        if constexpr (kCtas == 2) mbar_arrive_cluster(&acc_empty[a], 0);
+        else mbar_arrive(&acc_empty[a]);
+      }
     }
     if constexpr (kEpi == EPI_DGRAD) {
       if (p.cs_partials != nullptr) {
         // one partial row per (CTA group, lane quarter); row stride = n_tiles * BLOCK_N
-        const long long prow = (long long)(blockIdx.x / p.n_tiles) * 4 + q;
+        const long long prow = ((long long)(unit / p.n_tiles) * kCtas + rank) * 4 + q;
         float* dst = p.cs_partials + prow * ((long long)p.n_tiles * BLOCK_N) +
-                     (blockIdx.x % p.n_tiles) * BLOCK_N + chalf * (BLOCK_N / 2) + lane;
+                     (unit % p.n_tiles) * BLOCK_N + chalf * (BLOCK_N / 2) + lane;
 #pragma unroll
         for (int k = 0; k < 4; ++k) dst[k * 32] = csacc[k];
       }
@@ -400,10 +440,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCtas == 2) cluster_sync_all();  // neither CTA may leave while its peer can still touch it
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, NUM_ACC * BLOCK_N);
+    if constexpr (kCtas == 2) tmem_dealloc_pair(tmem_base, NUM_ACC * BLOCK_N);
+    else tmem_dealloc(tmem_base, NUM_ACC * BLOCK_N);
   }
 }
 
@@ -457,20 +499,54 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
   return 0;
 }
 
-template <int kTf32, bool kAMN, bool kBMN, int kEpi>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
-                       cudaStream_t st, int grid_override = 0) {
-  auto kern = gemm_kernel<kTf32, kAMN, kBMN, kEpi>;
+// CTAs per work item: 2 = CTA pairs (default), 1 = single-CTA kernel (B200STEP_GEMM_CTAS=1, for A/B runs)
+static int gemm_ctas() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("B200STEP_GEMM_CTAS");
+    v = (e && atoi(e) == 1) ? 1 : 2;
+  }
+  return v;
+}
+
+// Launch on min(work items, available units) units, rounded down to a multiple of `unit_multiple`.
+template <int kTf32, bool kAMN, bool kBMN, int kEpi, int kCtas>
+static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+                         cudaStream_t st, int unit_multiple, int* units_out) {
+  auto kern = gemm_kernel<kTf32, kAMN, kBMN, kEpi, kCtas>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
     configured = true;
   }
   const int total = p.m_tiles * p.n_tiles * p.splits;
-  const int grid = grid_override > 0 ? grid_override : (total < sm_count() ? total : sm_count());
-  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, tc, p);
-  B200_CHECK_CUDA(cudaGetLastError());
+  int units = sm_count() / kCtas;
+  if (units > total) units = total;
+  if (unit_multiple > 1) units = units / unit_multiple * unit_multiple;
+  B200_REQUIRE(units >= 1, "GEMM: no schedulable work units (tiles=%d, multiple=%d)", total, unit_multiple);
+  if (units_out) *units_out = units;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(units * kCtas);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = GEMM_SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, p));
   return 0;
+}
+
+template <int kTf32, bool kAMN, bool kBMN, int kEpi>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+                       cudaStream_t st, int unit_multiple = 1, int* units_out = nullptr) {
+  return gemm_ctas() == 2
+             ? launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 2>(ta, tb, tc, p, st, unit_multiple, units_out)
+             : launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 1>(ta, tb, tc, p, st, unit_multiple, units_out);
 }
 
 static int check_dims(int64_t M, int64_t N, int64_t K, int dtype) {
@@ -500,13 +576,14 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
   const int bk = tf32 ? 32 : 64;
   CUtensorMap ta, tb;
   if (int r = make_tmap(&ta, tf32, x, K, M, ldx, bk, BLOCK_M)) return r;
-  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, BLOCK_N)) return r;
+  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, BLOCK_N / gemm_ctas())) return r;  // a pair splits the B tile
   CUtensorMap tc;  // output slabs: one 128-byte row x 32 rows per TMA store
   if (int r = make_tmap(&tc, tf32, y, N, M, ldy, bk, 32, false, true)) return r;
   GemmParams p{};
   p.M = (int)M; p.N = (int)N;
+  const int tile_m = BLOCK_M * gemm_ctas();
   p.k_blocks = (int)((K + bk - 1) / bk);
-  p.m_tiles = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  p.m_tiles = (int)((M + tile_m - 1) / tile_m);
   p.n_tiles = (int)((N + BLOCK_N - 1) / BLOCK_N);
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f;
@@ -538,23 +615,22 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
   if (int r = make_tmap(&tc, tf32, dx, K, M, lddx, epr, 32, false, true)) return r;
   GemmParams p{};
   p.M = (int)M; p.N = (int)K;
+  const int tile_m = BLOCK_M * gemm_ctas();
   p.k_blocks = (int)((N + bk - 1) / bk);
-  p.m_tiles = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  p.m_tiles = (int)((M + tile_m - 1) / tile_m);
   p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = dx; p.ldo = lddx; p.act = act; p.ldact = ldact; p.flags = flags; p.dscale = dscale;
   p.mask_in = relu_mask; p.ldmask = ldmask; p.cs_partials = dbias ? scratch : nullptr;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // with bias-gradient accumulation every CTA must keep one n_tile: grid = multiple of n_tiles
-  const int total = p.m_tiles * p.n_tiles;
-  int grid = total < sm_count() ? total : sm_count();
-  grid = grid / p.n_tiles * p.n_tiles;
-  B200_REQUIRE(grid >= p.n_tiles, "dgrad: too many column tiles (%d) for this device", p.n_tiles);
-  if (int r = tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st, grid)
-                   : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st, grid))
+  // with bias-gradient accumulation every work unit must keep one n_tile: units = multiple of n_tiles
+  int units = 0;
+  if (int r = tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st, dbias ? p.n_tiles : 1, &units)
+                   : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st, dbias ? p.n_tiles : 1, &units))
     return r;
   if (dbias)
-    return launch_reduce_partials(scratch, (grid / p.n_tiles) * 4, p.n_tiles * BLOCK_N, (int)K, dbias, st);
+    return launch_reduce_partials(scratch, (units / p.n_tiles) * gemm_ctas() * 4, p.n_tiles * BLOCK_N, (int)K,
+                                  dbias, st);
   return 0;
 }
 
@@ -580,11 +656,12 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
   if (int r = make_tmap(&tb, tf32, x, K, M, ldx, epr, bk, true)) return r;
   GemmParams p{};
   p.M = (int)N; p.N = (int)K;
+  const int tile_m = BLOCK_M * gemm_ctas();
   p.k_blocks = (int)((M + bk - 1) / bk);
-  p.m_tiles = (int)((N + BLOCK_M - 1) / BLOCK_M);
+  p.m_tiles = (int)((N + tile_m - 1) / tile_m);
   p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
   const int tiles = p.m_tiles * p.n_tiles;
-  int splits = sm_count() / tiles;
+  int splits = (sm_count() / gemm_ctas()) / tiles;  // fill every CTA (pair) with one slice of the batch
   if (splits < 1) splits = 1;
   if (splits > p.k_blocks) splits = p.k_blocks;
   p.kb_per_split = (p.k_blocks + splits - 1) / splits;
