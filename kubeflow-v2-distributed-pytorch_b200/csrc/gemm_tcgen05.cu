@@ -246,11 +246,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int m0 = (tile / p.n_tiles) * TILE_M + rank * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
       const int a = it & 1;
       const uint32_t aph = (it >> 1) & 1;
-      mbar_wait(&acc_full[a], aph);
-      tc_fence_after();
       const int row0 = m0 + q * 32;
       const int row = row0 + lane;
       const bool row_ok = row < p.M;
+      // this row's 128 ReLU-mask bits for the warp's column half.  dgrad: fetched while the MMAs still run;
+      // fwd: collected chunk by chunk and written once per tile
+      uint32_t mrow[4] = {0u, 0u, 0u, 0u};
+      if constexpr (kEpi == EPI_DGRAD) {
+        if ((p.flags & B200_FLAG_RELU) && p.mask_in != nullptr && row_ok) {
+          const long long wbase = (n0 >> 5) + chalf * 4;  // ldmask % 4 == 0: the uint4 is fully in or fully out
+          if (wbase + 4 <= p.ldmask) {
+            const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(p.mask_in + (long long)row * p.ldmask + wbase));
+            mrow[0] = m4.x; mrow[1] = m4.y; mrow[2] = m4.z; mrow[3] = m4.w;
+          }
+        }
+      }
+      mbar_wait(&acc_full[a], aph);
+      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BLOCK_N;
       if constexpr (kEpi == EPI_WGRAD) {
 #pragma unroll 1
@@ -288,17 +300,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int g = chalf * GROUPS_PER_WARP + gi;
           const int gcol0 = n0 + g * GROUP_COLS;
           if (gcol0 >= p.N) break;  // warp-uniform
-          if (lane == 0) bulk_wait_read<0>();  // the previous store of this warp has finished reading the slab
-          __syncwarp();
+          if (p.flags & 0x200) break;  // timing experiment
+          uint32_t vv[LDS_PER_GROUP][32];  // the whole group's accumulators: one TMEM round trip, not two
+#pragma unroll
+          for (int h = 0; h < LDS_PER_GROUP; ++h) tmem_ld32(taddr + g * GROUP_COLS + h * 32, vv[h]);
+          tmem_ld_wait();
 #pragma unroll
           for (int h = 0; h < LDS_PER_GROUP; ++h) {
             const int col0 = gcol0 + h * 32;
-            uint32_t v[32];
-            tmem_ld32(taddr + g * GROUP_COLS + h * 32, v);
-            tmem_ld_wait();
             float f[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(vv[h][j]);
             if constexpr (kEpi == EPI_FWD) {
               if (p.bias != nullptr) {
 #pragma unroll
@@ -330,11 +342,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                   f[j + 3] = (r.w >= thresh) ? f[j + 3] * inv_keep : 0.0f;
                 }
               }
-              if (p.mask_out != nullptr && row_ok) {  // 1 bit per element for the backward ReLU(/dropout) mask
+              if (p.mask_out != nullptr) {  // 1 bit per element for the backward ReLU(/dropout) mask
                 uint32_t mbits = 0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) mbits |= (f[j] > 0.0f) ? (1u << j) : 0u;
-                p.mask_out[(long long)row * p.ldmask + (col0 >> 5)] = mbits;
+                mrow[gi * LDS_PER_GROUP + h] = mbits;
               }
             } else {  // EPI_DGRAD
               if (p.dscale != 1.0f) {
@@ -342,7 +354,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 for (int j = 0; j < 32; ++j) f[j] *= p.dscale;
               }
               if ((p.flags & B200_FLAG_RELU) && p.mask_in != nullptr) {
-                const uint32_t mbits = row_ok ? __ldg(p.mask_in + (long long)row * p.ldmask + (col0 >> 5)) : 0u;
+                const uint32_t mbits = mrow[gi * LDS_PER_GROUP + h];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) f[j] = (mbits & (1u << j)) ? f[j] : 0.0f;
               } else if ((p.flags & B200_FLAG_RELU) && p.act != nullptr && row_ok) {
@@ -396,6 +408,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 csacc[gi * LDS_PER_GROUP + h] += r[0];
               }
             }
+            if (h == 0) {  // the previous store of this warp must have finished READING the slab before we refill it
+              if (lane == 0) bulk_wait_read<0>();
+              __syncwarp();
+            }
             // registers -> swizzled slab: 16-byte chunk c of row `lane` lives at chunk (c ^ (lane & 7))
             const uint32_t srow = smem_u32(sbuf_ptr) + lane * 128;
             if constexpr (kTf32) {
@@ -413,9 +429,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
           __syncwarp();
-          if (lane == 0 && row0 < p.M) {
+          if (lane == 0 && row0 < p.M && !(p.flags & 0x100)) {
             tma_store_2d(&tmC, sbuf_ptr, gcol0, row0);
             bulk_commit();
+          }
+        }
+        if constexpr (kEpi == EPI_FWD) {
+          // the row's 128 mask bits of this column half leave as one 16-byte store
+          if (p.mask_out != nullptr && row_ok && !(p.flags & 0x400)) {
+            const long long wbase = (n0 >> 5) + chalf * 4;
+            if (wbase + 4 <= p.ldmask)
+              *reinterpret_cast<uint4*>(p.mask_out + (long long)row * p.ldmask + wbase) =
+                  make_uint4(mrow[0], mrow[1], mrow[2], mrow[3]);
           }
         }
       }
@@ -541,9 +566,19 @@ static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUt
   return 0;
 }
 
+// timing experiments only (results are wrong): bit 8 = do not issue the output TMA stores, bit 9 = skip the
+// epilogue math and staging, bit 10 = skip the ReLU bit-mask store
+static int gemm_debug_flags() {
+  static int v = -1;
+  if (v < 0) v = getenv("B200STEP_GEMM_DEBUG") ? (atoi(getenv("B200STEP_GEMM_DEBUG")) << 8) : 0;
+  return v;
+}
+
 template <int kTf32, bool kAMN, bool kBMN, int kEpi>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p_in,
                        cudaStream_t st, int unit_multiple = 1, int* units_out = nullptr) {
+  GemmParams p = p_in;
+  p.flags |= gemm_debug_flags();
   return gemm_ctas() == 2
              ? launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 2>(ta, tb, tc, p, st, unit_multiple, units_out)
              : launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 1>(ta, tb, tc, p, st, unit_multiple, units_out);
@@ -569,7 +604,9 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
                                float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
                                uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream) {
   if (int r = check_dims(M, N, K, dtype)) return r;
-  B200_REQUIRE(relu_mask == nullptr || ldmask * 32 >= N, "relu_mask row stride %lld words is too small for N=%lld",
+  B200_REQUIRE(relu_mask == nullptr || (ldmask * 32 >= N && ldmask % 4 == 0 &&
+                                        (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
+               "relu_mask needs a 16-byte aligned base and a row stride (%lld words) that is a multiple of 4 and covers N=%lld",
                (long long)ldmask, (long long)N);
   B200_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "dropout_p=%f out of [0,1)", dropout_p);
   const int tf32 = dtype == B200_F32;
@@ -599,7 +636,9 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
                                  int dtype, int flags, float dscale, const uint32_t* relu_mask, int64_t ldmask,
                                  float* dbias, float* scratch, int64_t scratch_floats, b200_stream_t stream) {
   if (int r = check_dims(M, N, K, dtype)) return r;
-  B200_REQUIRE(relu_mask == nullptr || ldmask * 32 >= K, "relu_mask row stride %lld words is too small for K=%lld",
+  B200_REQUIRE(relu_mask == nullptr || (ldmask * 32 >= K && ldmask % 4 == 0 &&
+                                        (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
+               "relu_mask needs a 16-byte aligned base and a row stride (%lld words) that is a multiple of 4 and covers K=%lld",
                (long long)ldmask, (long long)K);
   B200_REQUIRE(dbias == nullptr || (scratch != nullptr && scratch_floats >= b200_dgrad_scratch_floats(M, K)),
                "dgrad bias-gradient scratch too small: need %lld floats", (long long)b200_dgrad_scratch_floats(M, K));
@@ -661,7 +700,9 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
   p.m_tiles = (int)((N + tile_m - 1) / tile_m);
   p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
   const int tiles = p.m_tiles * p.n_tiles;
-  int splits = (sm_count() / gemm_ctas()) / tiles;  // fill every CTA (pair) with one slice of the batch
+  // two batch slices per CTA (pair): the epilogue of the first overlaps the MMAs of the second
+  static const int wgrad_waves = getenv("B200STEP_WGRAD_WAVES") ? atoi(getenv("B200STEP_WGRAD_WAVES")) : 1;
+  int splits = wgrad_waves * (sm_count() / gemm_ctas()) / tiles;
   if (splits < 1) splits = 1;
   if (splits > p.k_blocks) splits = p.k_blocks;
   p.kb_per_split = (p.k_blocks + splits - 1) / splits;

@@ -11,116 +11,178 @@
 
 namespace b200 {
 
-constexpr int CE_THREADS = 256;
+constexpr int CE_THREADS = 512;
 constexpr int CE_WARPS = CE_THREADS / 32;
 constexpr int CE_MAX_BLOCKS = 1024;
 constexpr int CE_MAX_CLASSES = 1024;  // 32 lanes x 32 register-resident values
+constexpr int CE_BUFS = 3;            // load(i+1) | compute(i) | store(i-1)
 
+// Persistent CTAs walk tiles of 32 (bf16) / 16 (fp32) logits rows.  A tile is a contiguous block of global memory,
+// so it is fetched with 1-D TMA bulk copies into shared memory while the previous tile is being processed and the
+// one before that is being written back: the copy engine, not the register file, holds the bytes in flight.
+// Each warp then reads its rows from shared memory (conflict-free 128-bit accesses), does the softmax
+// arithmetic in registers, and overwrites the row in place with the gradient; the finished tile leaves through a
+// bulk store.  Per-column sums of the stored gradient (output-layer bias gradient) and the loss ride along in
+// registers; one partial row per CTA, reduced in a fixed order by reduce_partials_kernel (deterministic).
 template <bool kBf16>
-__global__ void __launch_bounds__(CE_THREADS)
+__global__ void __launch_bounds__(CE_THREADS, 1)
 ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64_t* __restrict__ labels,
                     void* __restrict__ dlogits_, long long lddl, float* __restrict__ partials,
                     long long batch, int C, float scale, int want_dbias) {
-  constexpr int VEC = kBf16 ? 8 : 4;         // elements per 16-byte vector
-  constexpr int ITERS = 32 / VEC;            // vectors per lane (covers 1024 columns)
-  __shared__ float red[CE_WARPS][CE_MAX_CLASSES];
+  constexpr int VEC = kBf16 ? 8 : 4;          // elements per 16-byte vector
+  constexpr int ITERS = 32 / VEC;             // vectors per lane (covers 1024 columns)
+  constexpr int ES = kBf16 ? 2 : 4;
+  constexpr int TILE_ROWS = kBf16 ? 32 : 16;  // 64*C bytes per buffer either way
+  extern __shared__ __align__(128) uint8_t ce_smem[];
+  __shared__ uint64_t full_bar[CE_BUFS];
   __shared__ float red_loss[CE_WARPS];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = C / VEC;
+  const uint32_t row_bytes = (uint32_t)C * ES;
+  const uint32_t buf_bytes = TILE_ROWS * row_bytes;
+  const long long num_tiles = (batch + TILE_ROWS - 1) / TILE_ROWS;
+  const uint8_t* gin = reinterpret_cast<const uint8_t*>(logits_);
+  uint8_t* gout = reinterpret_cast<uint8_t*>(dlogits_);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < CE_BUFS; ++i) mbar_init(&full_bar[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  auto issue_load = [&](long long tile, int buf) {  // one thread
+    const long long r0 = tile * TILE_ROWS;
+    const int rows = (int)min((long long)TILE_ROWS, batch - r0);
+    mbar_expect_tx(&full_bar[buf], rows * row_bytes);
+    uint8_t* dst = ce_smem + (size_t)buf * buf_bytes;
+    if (ldl == C) {
+      bulk_load_1d(dst, gin + r0 * ldl * ES, rows * row_bytes, &full_bar[buf]);
+    } else {
+      for (int r = 0; r < rows; ++r)
+        bulk_load_1d(dst + r * row_bytes, gin + (r0 + r) * ldl * ES, row_bytes, &full_bar[buf]);
+    }
+  };
+
   float dbacc[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) dbacc[i] = 0.f;
   float loss_acc = 0.f;
 
-  for (long long row = (long long)blockIdx.x * CE_WARPS + warp; row < batch;
-       row += (long long)gridDim.x * CE_WARPS) {
-    const int y = (int)__ldg(labels + row);
-    float z[32];
-    float zmax = -INFINITY, zy = 0.f;
+  if (threadIdx.x == 0 && blockIdx.x < num_tiles) issue_load(blockIdx.x, 0);
+  int it = 0;
+  for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int b = it % CE_BUFS;
+    if (threadIdx.x == 0) {
+      const long long tn = tile + gridDim.x;
+      if (tn < num_tiles) {
+        bulk_wait_read<1>();  // the store that last read buffer (it+1)%3 (two tiles ago) has drained it
+        issue_load(tn, (it + 1) % CE_BUFS);
+      }
+    }
+    mbar_wait(&full_bar[b], (it / CE_BUFS) & 1);
+    const long long r0 = tile * TILE_ROWS;
+    const int rows = (int)min((long long)TILE_ROWS, batch - r0);
+    const uint32_t sbuf = smem_u32(ce_smem + (size_t)b * buf_bytes);
+    for (int rr = warp; rr < rows; rr += CE_WARPS) {
+      const long long row = r0 + rr;
+      const uint32_t srow = sbuf + rr * row_bytes;
+      const int y = (int)__ldg(labels + row);
+      float z[32];
+      float zmax = -INFINITY, zy = 0.f;
 #pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-      const int v = lane + 32 * it;
-      if (v < nvec) {
-        if constexpr (kBf16) {
-          const uint4 raw = ldg_stream(reinterpret_cast<const uint16_t*>(logits_) + row * ldl + v * 8);
-          const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+      for (int i = 0; i < ITERS; ++i) {
+        const int v = lane + 32 * i;
+        if (v < nvec) {
+          const uint4 raw = ld_shared_v4(srow + v * 16);
+          if constexpr (kBf16) {
+            const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
 #pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            z[it * 8 + 2 * t] = bf16_lo(w[t]);
-            z[it * 8 + 2 * t + 1] = bf16_hi(w[t]);
+            for (int t = 0; t < 4; ++t) {
+              z[i * 8 + 2 * t] = bf16_lo(w[t]);
+              z[i * 8 + 2 * t + 1] = bf16_hi(w[t]);
+            }
+          } else {
+            z[i * 4 + 0] = __uint_as_float(raw.x);
+            z[i * 4 + 1] = __uint_as_float(raw.y);
+            z[i * 4 + 2] = __uint_as_float(raw.z);
+            z[i * 4 + 3] = __uint_as_float(raw.w);
+          }
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            zmax = fmaxf(zmax, z[i * VEC + j]);
+            if (v * VEC + j == y) zy = z[i * VEC + j];
           }
         } else {
-          const uint4 raw = ldg_stream(reinterpret_cast<const float*>(logits_) + row * ldl + v * 4);
-          z[it * 4 + 0] = __uint_as_float(raw.x);
-          z[it * 4 + 1] = __uint_as_float(raw.y);
-          z[it * 4 + 2] = __uint_as_float(raw.z);
-          z[it * 4 + 3] = __uint_as_float(raw.w);
-        }
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          zmax = fmaxf(zmax, z[it * VEC + j]);
-          if (v * VEC + j == y) zy = z[it * VEC + j];
+          for (int j = 0; j < VEC; ++j) z[i * VEC + j] = -INFINITY;
         }
+      }
+      zmax = warp_max(zmax);
+      zy = warp_sum(zy);
+      float sum = 0.f;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        z[i] = __expf(z[i] - zmax);  // FMUL + MUFU.EX2 (rel. error ~1e-6, far inside the 1e-5 loss bar); exp(-inf) = 0
+        sum += z[i];
+      }
+      sum = warp_sum(sum);
+      loss_acc += (zmax + logf(sum)) - zy;  // identical in every lane
+      const float inv = 1.0f / sum;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const int v = lane + 32 * i;
+        if (v < nvec) {
+          float d[VEC];
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            const float pj = z[i * VEC + j] * inv;
+            d[j] = (pj - ((v * VEC + j == y) ? 1.f : 0.f)) * scale;
+          }
+          if constexpr (kBf16) {
+            const uint32_t w[4] = {pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),
+                                   pack_bf16x2(d[6], d[7])};
+            st_shared_v4(srow + v * 16, w[0], w[1], w[2], w[3]);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {  // bias gradient sums what is stored (bf16-rounded)
+              dbacc[i * 8 + 2 * t] += bf16_lo(w[t]);
+              dbacc[i * 8 + 2 * t + 1] += bf16_hi(w[t]);
+            }
+          } else {
+            st_shared_v4(srow + v * 16, __float_as_uint(d[0]), __float_as_uint(d[1]), __float_as_uint(d[2]),
+                         __float_as_uint(d[3]));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dbacc[i * 4 + j] += d[j];
+          }
+        }
+      }
+    }
+    fence_proxy_async_smem();  // in-place gradient rows -> visible to the bulk store
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint8_t* src = ce_smem + (size_t)b * buf_bytes;
+      if (lddl == C) {
+        bulk_store_1d(gout + r0 * lddl * ES, src, rows * row_bytes);
       } else {
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) z[it * VEC + j] = -INFINITY;
+        for (int r = 0; r < rows; ++r) bulk_store_1d(gout + (r0 + r) * lddl * ES, src + r * row_bytes, row_bytes);
       }
-    }
-    zmax = warp_max(zmax);
-    zy = warp_sum(zy);
-    float sum = 0.f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      z[i] = expf(z[i] - zmax);  // exp(-inf) = 0 for the tail
-      sum += z[i];
-    }
-    sum = warp_sum(sum);
-    loss_acc += (zmax + logf(sum)) - zy;  // identical in every lane
-    const float inv = 1.0f / sum;
-#pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-      const int v = lane + 32 * it;
-      if (v < nvec) {
-        float d[VEC];
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          const float pj = z[it * VEC + j] * inv;
-          d[j] = (pj - ((v * VEC + j == y) ? 1.f : 0.f)) * scale;
-        }
-        if constexpr (kBf16) {
-          uint4 o;
-          o.x = pack_bf16x2(d[0], d[1]);
-          o.y = pack_bf16x2(d[2], d[3]);
-          o.z = pack_bf16x2(d[4], d[5]);
-          o.w = pack_bf16x2(d[6], d[7]);
-          stg_stream(reinterpret_cast<uint16_t*>(dlogits_) + row * lddl + v * 8, o);
-          const uint32_t w[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-          for (int t = 0; t < 4; ++t) {  // bias gradient sums what was stored (bf16-rounded)
-            dbacc[it * 8 + 2 * t] += bf16_lo(w[t]);
-            dbacc[it * 8 + 2 * t + 1] += bf16_hi(w[t]);
-          }
-        } else {
-          stg_stream(reinterpret_cast<float*>(dlogits_) + row * lddl + v * 4,
-                     make_uint4(__float_as_uint(d[0]), __float_as_uint(d[1]), __float_as_uint(d[2]),
-                                __float_as_uint(d[3])));
-#pragma unroll
-          for (int j = 0; j < 4; ++j) dbacc[it * 4 + j] += d[j];
-        }
-      }
+      bulk_commit();
     }
   }
+  if (threadIdx.x == 0) bulk_wait_all();
+  __syncthreads();
 
-  // CTA-level reduction in a fixed order, then one partial row per CTA
+  // CTA-level reduction in a fixed order (buffer 0 is free again: 16 warps x C floats = 64*C bytes), then one
+  // partial row per CTA
+  float* red = reinterpret_cast<float*>(ce_smem);  // [CE_WARPS][C]
   float* prow = partials + (long long)blockIdx.x * (C + 1);
   if (want_dbias) {
 #pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-      const int v = lane + 32 * it;
+    for (int i = 0; i < ITERS; ++i) {
+      const int v = lane + 32 * i;
       if (v < nvec) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) red[warp][v * VEC + j] = dbacc[it * VEC + j];
+        for (int j = 0; j < VEC; ++j) red[warp * C + v * VEC + j] = dbacc[i * VEC + j];
       }
     }
   }
@@ -130,7 +192,7 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
     for (int c = threadIdx.x; c < C; c += CE_THREADS) {
       float s = 0.f;
 #pragma unroll
-      for (int w = 0; w < CE_WARPS; ++w) s += red[w][c];
+      for (int w = 0; w < CE_WARPS; ++w) s += red[w * C + c];
       prow[c] = s;
     }
   }
@@ -158,11 +220,13 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
   if (live) {
     const float* col = partials + c;
     int r = warp;
-    for (; r + 24 < nrows; r += 32) {
-      s0 += col[(long long)(r + 0) * row_stride];
-      s1 += col[(long long)(r + 8) * row_stride];
-      s2 += col[(long long)(r + 16) * row_stride];
-      s3 += col[(long long)(r + 24) * row_stride];
+    for (; r + 56 < nrows; r += 64) {  // eight independent loads in flight per lane
+      const float a0 = col[(long long)(r + 0) * row_stride], a1 = col[(long long)(r + 8) * row_stride];
+      const float a2 = col[(long long)(r + 16) * row_stride], a3 = col[(long long)(r + 24) * row_stride];
+      const float a4 = col[(long long)(r + 32) * row_stride], a5 = col[(long long)(r + 40) * row_stride];
+      const float a6 = col[(long long)(r + 48) * row_stride], a7 = col[(long long)(r + 56) * row_stride];
+      s0 += a0; s1 += a1; s2 += a2; s3 += a3;
+      s0 += a4; s1 += a5; s2 += a6; s3 += a7;
     }
     for (; r < nrows; r += 8) s0 += col[(long long)r * row_stride];
   }
@@ -277,19 +341,34 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
   B200_REQUIRE(ldl % vec == 0 && lddl % vec == 0, "logit row strides must keep rows 16-byte aligned");
   B200_REQUIRE(batch > 0, "batch must be positive");
   B200_REQUIRE(scratch != nullptr, "scratch must not be NULL");
-  int grid = (int)((batch + CE_WARPS - 1) / CE_WARPS);
-  const int cap = sm_count() * 4 < CE_MAX_BLOCKS ? sm_count() * 4 : CE_MAX_BLOCKS;
-  if (grid > cap) grid = cap;
+  const int tile_rows = dtype == B200_BF16 ? 32 : 16;
+  const long long num_tiles = (batch + tile_rows - 1) / tile_rows;
+  int grid = (int)(num_tiles < sm_count() ? num_tiles : sm_count());
+  B200_REQUIRE(grid <= CE_MAX_BLOCKS, "device has more SMs than the scratch sizing assumes");
   B200_REQUIRE(scratch_floats >= (int64_t)grid * (num_classes + 1),
                "scratch too small: %lld floats, need %lld", (long long)scratch_floats,
                (long long)grid * (num_classes + 1));
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15) == 0,
+               "logits / dlogits must be 16-byte aligned");
+  const size_t smem = (size_t)CE_BUFS * 64 * num_classes;  // 3 tiles of 64*C bytes
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (dtype == B200_BF16)
-    ce_loss_grad_kernel<true><<<grid, CE_THREADS, 0, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                           num_classes, grad_scale, dbias != nullptr);
-  else
-    ce_loss_grad_kernel<false><<<grid, CE_THREADS, 0, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                            num_classes, grad_scale, dbias != nullptr);
+  if (dtype == B200_BF16) {
+    static bool cfg = false;
+    if (!cfg) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
+      cfg = true;
+    }
+    ce_loss_grad_kernel<true><<<grid, CE_THREADS, smem, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
+                                                              num_classes, grad_scale, dbias != nullptr);
+  } else {
+    static bool cfg = false;
+    if (!cfg) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
+      cfg = true;
+    }
+    ce_loss_grad_kernel<false><<<grid, CE_THREADS, smem, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
+                                                               num_classes, grad_scale, dbias != nullptr);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
   reduce_partials_kernel<<<(stride + 31) / 32, RED_THREADS, 0, st>>>(scratch, grid, stride, num_classes, dbias,

@@ -5,17 +5,18 @@
 // embedding lookup + concat at the front of the tabular model.  Results are bit-exact
 // with the CPU oracle: IEEE subtract then divide (no FMA contraction, no reciprocal), RNE to bf16.
 //
-// Layout: one CTA assembles up to 32 consecutive output rows in shared memory (embedding columns start at
-// element num_dense, which is not 16-byte aligned, so the row is built with scalar shared stores), then the
-// whole tile — a contiguous TILE*ldx block of x_out — leaves through one 1-D TMA bulk store.  Table rows are
-// read with 128-bit streaming loads, one float4 per lane.
+// Layout: persistent warps, one sample per warp at a time.  The per-sample work is a chain of three dependent
+// gathers (sampler index -> dataset row -> 26 table rows); the chain of sample k+1 is started before sample k is
+// finished (software pipelining in registers), so a warp pays one gather latency per sample instead of three.
+// The output row is assembled in a warp-private shared-memory row (embedding columns start at element
+// num_dense, which is not 16-byte aligned, so it is built with scalar shared stores) and leaves with
+// coalesced 128-bit stores.  Table rows are read with 128-bit streaming loads, one float4 per lane.
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int PRE_THREADS = 256;
-constexpr int PRE_MAX_TILE = 32;           // samples per CTA (fewer when rows are wide)
-constexpr int PRE_SMEM_TARGET = 96 * 1024;  // keeps >= 2 CTAs per SM resident
+constexpr int PRE_WARPS = PRE_THREADS / 32;
 
 template <typename OutT>
 __device__ __forceinline__ OutT cvt_out(float v);
@@ -25,44 +26,66 @@ template <>
 __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 
 template <typename OutT>
-__global__ void __launch_bounds__(PRE_THREADS)
+__global__ void __launch_bounds__(PRE_THREADS, 4)
 preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict__ ds_cat,
                   const int64_t* __restrict__ ds_label, const int64_t* __restrict__ row_idx,
                   const int32_t* __restrict__ cursor, const float* __restrict__ mean,
                   const float* __restrict__ stdv, const float* __restrict__ tables,
                   OutT* __restrict__ x_out, int64_t* __restrict__ y_out, int32_t* __restrict__ idx_out,
                   long long batch, int num_dense, int num_cat, long long table_rows, int embed_dim,
-                  long long ldx, int tile_rows) {
+                  long long ldx) {
   extern __shared__ __align__(128) uint8_t pre_smem[];
-  OutT* tile = reinterpret_cast<OutT*>(pre_smem);  // [tile_rows][ldx]
-
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long b0 = (long long)blockIdx.x * tile_rows;
+  OutT* xr = reinterpret_cast<OutT*>(pre_smem) + (long long)warp * ldx;  // this warp's row
+  const uint32_t xr_s = smem_u32(xr);
   const long long cur = cursor ? (long long)(*cursor) : 0;
-  const int rows_here = (int)min((long long)tile_rows, batch - b0);
-  const int vec_per_row = embed_dim >> 2;           // float4 chunks per table row
-  const int vec_total = num_cat * vec_per_row;      // float4 chunks per sample
-  const int used = num_dense + num_cat * embed_dim; // first padding column
+  const int64_t* ridx = row_idx + cur * batch;
+  const int vec_per_row = embed_dim >> 2;            // float4 chunks per table row
+  const int used = num_dense + num_cat * embed_dim;  // first padding column
+  const int row_vecs = (int)(ldx * sizeof(OutT) / 16);
+  const long long stride = (long long)gridDim.x * PRE_WARPS;
+  const float mu = lane < num_dense ? __ldg(mean + lane) : 0.f;     // num_dense <= 32 on the fast path
+  const float sd = lane < num_dense ? __ldg(stdv + lane) : 1.f;
 
-  for (int s = warp; s < rows_here; s += PRE_THREADS / 32) {
-    const long long b = b0 + s;
-    const long long r = __ldg(row_idx + cur * batch + b);
-    OutT* xr = tile + (long long)s * ldx;
-    // dense columns: (x - mean) / std, IEEE fp32
-    for (int j = lane; j < num_dense; j += 32) {
-      const float x = __ldg(ds_dense + r * num_dense + j);
-      xr[j] = cvt_out<OutT>(__fdiv_rn(__fsub_rn(x, __ldg(mean + j)), __ldg(stdv + j)));
+  // K padding never changes: write it once
+  for (int j = used + lane; j < ldx; j += 32) xr[j] = cvt_out<OutT>(0.0f);
+
+  long long b = (long long)blockIdx.x * PRE_WARPS + warp;
+  // pipeline registers: stage A = sampler index, stage B = that row's dense value / first-32 categorical ids / label
+  long long r_b = b < batch ? __ldg(ridx + b) : 0;
+  long long r_a = b + stride < batch ? __ldg(ridx + b + stride) : 0;
+  float dense_b = 0.f;
+  long long id_b = 0, label_b = 0;
+  if (b < batch) {
+    if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
+    if (lane < num_cat) id_b = __ldg(ds_cat + r_b * num_cat + lane);
+    if (lane == 0) label_b = __ldg(ds_label + r_b);
+  }
+  for (; b < batch; b += stride) {
+    // start the next sample's stage B (its index arrived during the previous iteration) and stage A of the one after
+    const long long bn = b + stride;
+    const long long r_cur = r_b;
+    const float dense_cur = dense_b;
+    const long long id_cur = id_b, label_cur = label_b;
+    r_b = r_a;
+    if (bn < batch) {
+      if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
+      if (lane < num_cat) id_b = __ldg(ds_cat + r_b * num_cat + lane);
+      if (lane == 0) label_b = __ldg(ds_label + r_b);
     }
-    // K padding
-    for (int j = used + lane; j < ldx; j += 32) xr[j] = cvt_out<OutT>(0.0f);
-    // categorical ids: lane t holds id of table t (+32, +64 ... for > 32 tables handled by the loop below)
+    r_a = bn + stride < batch ? __ldg(ridx + bn + stride) : 0;
+
+    // dense columns: (x - mean) / std, IEEE fp32
+    if (lane < num_dense) xr[lane] = cvt_out<OutT>(__fdiv_rn(__fsub_rn(dense_cur, mu), sd));
+    for (int j = 32 + lane; j < num_dense; j += 32)  // > 32 dense columns: plain path
+      xr[j] = cvt_out<OutT>(__fdiv_rn(__fsub_rn(__ldg(ds_dense + r_cur * num_dense + j), __ldg(mean + j)),
+                                      __ldg(stdv + j)));
+    // categorical ids: lane t holds the id of table tb + t
     for (int tb = 0; tb < num_cat; tb += 32) {
       const int t = tb + lane;
-      long long id = 0;
-      if (t < num_cat) {
-        id = __ldg(ds_cat + r * num_cat + t);
-        idx_out[b * num_cat + t] = (int32_t)id;
-      }
+      long long id = id_cur;
+      if (tb > 0) id = t < num_cat ? __ldg(ds_cat + r_cur * num_cat + t) : 0;
+      if (t < num_cat) idx_out[b * num_cat + t] = (int32_t)id;
       const int tcount = min(32, num_cat - tb);
       // gather: chunk i -> table tb + i / vec_per_row, float4 i % vec_per_row of that row
       for (int i0 = 0; i0 < tcount * vec_per_row; i0 += 32) {
@@ -81,16 +104,12 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
         }
       }
     }
-    if (lane == 0) y_out[b] = __ldg(ds_label + r);
-  }
-  (void)vec_total;
-  // hand the finished tile to the TMA engine: generic-proxy writes -> async-proxy read
-  fence_proxy_async_smem();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    bulk_store_1d(x_out + b0 * ldx, tile, (uint32_t)(rows_here * ldx * sizeof(OutT)));
-    bulk_commit();
-    bulk_wait_read0();  // shared memory must outlive the read
+    if (lane == 0) y_out[b] = label_cur;
+    __syncwarp();
+    // the finished row leaves with coalesced 16-byte stores (512 contiguous bytes per warp instruction)
+    uint8_t* orow = reinterpret_cast<uint8_t*>(x_out + b * ldx);
+    for (int c = lane; c < row_vecs; c += 32) stg_stream(orow + c * 16, ld_shared_v4(xr_s + c * 16));
+    __syncwarp();  // the row buffer is rewritten by the next sample
   }
 }
 
@@ -116,12 +135,11 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   B200_REQUIRE((reinterpret_cast<uintptr_t>(x_out) & 15) == 0 && (reinterpret_cast<uintptr_t>(tables) & 15) == 0,
                "x_out and tables must be 16-byte aligned");
   const size_t row_bytes = (size_t)ldx * es;
-  B200_REQUIRE(row_bytes <= 200 * 1024, "row of %lld elements does not fit in shared memory", (long long)ldx);
-  int tile_rows = (int)(PRE_SMEM_TARGET / row_bytes);
-  if (tile_rows > PRE_MAX_TILE) tile_rows = PRE_MAX_TILE;
-  if (tile_rows < 1) tile_rows = 1;
-  const size_t smem = (size_t)tile_rows * row_bytes;
-  const unsigned grid = (unsigned)((batch + tile_rows - 1) / tile_rows);
+  const size_t smem = PRE_WARPS * row_bytes;  // one output row per warp
+  B200_REQUIRE(smem <= 200 * 1024, "row of %lld elements does not fit in shared memory", (long long)ldx);
+  long long blocks = (batch + PRE_WARPS - 1) / PRE_WARPS;
+  const long long cap = (long long)sm_count() * 8;
+  const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (x_dtype == B200_F32) {
     static bool cfg = false;
@@ -131,7 +149,7 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
     }
     preprocess_kernel<float><<<grid, PRE_THREADS, smem, st>>>(
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables, static_cast<float*>(x_out), y_out,
-        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, ldx, tile_rows);
+        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, ldx);
   } else {
     static bool cfg = false;
     if (!cfg) {
@@ -141,7 +159,7 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
     preprocess_kernel<__nv_bfloat16><<<grid, PRE_THREADS, smem, st>>>(
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables,
         static_cast<__nv_bfloat16*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,
-        embed_dim, ldx, tile_rows);
+        embed_dim, ldx);
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
