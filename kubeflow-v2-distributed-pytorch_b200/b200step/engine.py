@@ -335,25 +335,70 @@ class TrainStep:
         self._enqueue(self.tail, None, self.row_idx[off:], None, False)
         self.host_steps += 1
 
-    def step_from_host(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> None:
-        """One step on a batch that lives in (pinned) HOST memory: the reference's per-step H2D copies
-        (task.py:305,307) followed by the same device step.  Used for the end-to-end measurement."""
+    def _init_host_path(self) -> None:
+        bs, dev, spec = self.cfg.batch_size, self.dev, self.spec
+        self.identity_idx = torch.arange(bs, dtype=torch.int64, device=dev)
+        self._stages = [TabularDataset(torch.empty(bs, spec.num_dense, dtype=torch.float32, device=dev),
+                                       torch.empty(bs, spec.num_cat, dtype=torch.int64, device=dev),
+                                       torch.empty(bs, dtype=torch.int64, device=dev), self.ds.mean, self.ds.std)
+                        for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._stage_ready = [torch.cuda.Event() for _ in range(2)]
+        self._stage_free = [torch.cuda.Event() for _ in range(2)]
+        self._loss_ev = [torch.cuda.Event() for _ in range(2)]
+        self._loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self._host_graphs = [None, None]
+        self._host_k = 0
+        torch.cuda.synchronize(dev)
+
+    def step_from_host(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> int:
+        """One step on a batch that lives in pinned HOST memory: the reference's per-step H2D copies
+        (task.py:305,307) followed by the same device step, then an asynchronous device->host copy of the step's
+        loss.  Two staging buffers alternate, so the copy of batch i+1 overlaps the compute of batch i (the
+        reference gets the same overlap from its DataLoader workers + non_blocking copies).
+        Returns a ticket for `host_loss(ticket)`."""
         B = dense.shape[0]
         if B > self.cfg.batch_size:
             raise ValueError("host batch larger than the configured batch size")
         if self.identity_idx is None:
-            self.identity_idx = torch.arange(self.cfg.batch_size, dtype=torch.int64, device=self.dev)
-            bs = self.cfg.batch_size
-            self._stage = TabularDataset(
-                torch.empty(bs, self.spec.num_dense, dtype=torch.float32, device=self.dev),
-                torch.empty(bs, self.spec.num_cat, dtype=torch.int64, device=self.dev),
-                torch.empty(bs, dtype=torch.int64, device=self.dev), self.ds.mean, self.ds.std)
+            self._init_host_path()
+        k = self._host_k
+        self._host_k ^= 1
+        stage = self._stages[k]
+        self.copy_stream.wait_event(self._stage_free[k])      # the step that last read this stage is done
+        with torch.cuda.stream(self.copy_stream):
+            stage.dense[:B].copy_(dense, non_blocking=True)
+            stage.cat[:B].copy_(cat, non_blocking=True)
+            stage.label[:B].copy_(label, non_blocking=True)
+        self._stage_ready[k].record(self.copy_stream)
+        self.main.wait_event(self._stage_ready[k])
+        if B == self.cfg.batch_size and self.cfg.use_graph and self.host_steps > 0:
+            if self._host_graphs[k] is None:
+                import ctypes as C
+
+                self.main.synchronize()
+                self.comm_stream.synchronize()
+                self.lib.graph_begin(self.main.cuda_stream)
+                try:
+                    self._enqueue(B, stage, self.identity_idx, None, False)
+                finally:
+                    out = C.c_void_p()
+                    self.lib.graph_end(self.main.cuda_stream, C.byref(out))
+                self._host_graphs[k] = out
+            self.lib.graph_launch(self._host_graphs[k], self.main.cuda_stream)
+        else:
+            self._enqueue(B, stage, self.identity_idx, None, False)
+        self._stage_free[k].record(self.main)
         with torch.cuda.stream(self.main):
-            self._stage.dense[:B].copy_(dense, non_blocking=True)
-            self._stage.cat[:B].copy_(cat, non_blocking=True)
-            self._stage.label[:B].copy_(label, non_blocking=True)
-        self._enqueue(B, self._stage, self.identity_idx, None, False)
+            self._loss_host[k].copy_(self.loss, non_blocking=True)
+        self._loss_ev[k].record(self.main)
         self.host_steps += 1
+        return k
+
+    def host_loss(self, ticket: int) -> float:
+        """Loss of the host-fed step that returned `ticket` (blocks until that step's D2H copy has landed)."""
+        self._loss_ev[ticket].synchronize()
+        return float(self._loss_host[ticket].item())
 
     def loss_value(self) -> float:
         """Blocking read of the last step's local mean loss (what `loss` holds at task.py:310)."""
@@ -378,3 +423,7 @@ class TrainStep:
         if self.graph is not None:
             self.lib.graph_destroy(self.graph)
             self.graph = None
+        for g in getattr(self, "_host_graphs", []):
+            if g is not None:
+                self.lib.graph_destroy(g)
+        self._host_graphs = [None, None]

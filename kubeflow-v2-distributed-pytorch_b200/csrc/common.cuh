@@ -136,6 +136,21 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t saddr) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
   return r;
 }
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t saddr) {
+  uint32_t r;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ uint16_t ld_shared_u16(uint32_t saddr) {
+  uint16_t r;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 // 1-D bulk store shared -> global (bytes % 16 == 0, both 16-byte aligned)
 __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),

@@ -88,8 +88,9 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
       const long long row = r0 + rr;
       const uint32_t srow = sbuf + rr * row_bytes;
       const int y = (int)__ldg(labels + row);
+      const int vy = y / VEC, jy = y - vy * VEC;  // 16-byte vector / slot that holds the label's logit
       float z[32];
-      float zmax = -INFINITY, zy = 0.f;
+      float zmax = -INFINITY;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
         const int v = lane + 32 * i;
@@ -109,35 +110,41 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
             z[i * 4 + 3] = __uint_as_float(raw.w);
           }
 #pragma unroll
-          for (int j = 0; j < VEC; ++j) {
-            zmax = fmaxf(zmax, z[i * VEC + j]);
-            if (v * VEC + j == y) zy = z[i * VEC + j];
-          }
+          for (int j = 0; j < VEC; ++j) zmax = fmaxf(zmax, z[i * VEC + j]);
         } else {
 #pragma unroll
           for (int j = 0; j < VEC; ++j) z[i * VEC + j] = -INFINITY;
         }
       }
+      // the label's logit: one scalar shared-memory read instead of a compare per element
+      float zy;
+      if constexpr (kBf16) zy = __uint_as_float((uint32_t)ld_shared_u16(srow + y * 2) << 16);
+      else zy = __uint_as_float(ld_shared_u32(srow + y * 4));
       zmax = warp_max(zmax);
-      zy = warp_sum(zy);
+      const float zmax_l2 = zmax * 1.4426950408889634f;
       float sum = 0.f;
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        z[i] = __expf(z[i] - zmax);  // FMUL + MUFU.EX2 (rel. error ~1e-6, far inside the 1e-5 loss bar); exp(-inf) = 0
+        // exp(z - zmax) = 2^(z*log2e - zmax*log2e): one FFMA + MUFU.EX2 (rel. error ~1e-6, inside the 1e-5 loss
+        // bar); the -inf tail gives 0
+        z[i] = ex2_approx(fmaf(z[i], 1.4426950408889634f, -zmax_l2));
         sum += z[i];
       }
       sum = warp_sum(sum);
       loss_acc += (zmax + logf(sum)) - zy;  // identical in every lane
       const float inv = 1.0f / sum;
+      const float inv_scale = inv * scale;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
         const int v = lane + 32 * i;
         if (v < nvec) {
           float d[VEC];
 #pragma unroll
-          for (int j = 0; j < VEC; ++j) {
-            const float pj = z[i * VEC + j] * inv;
-            d[j] = (pj - ((v * VEC + j == y) ? 1.f : 0.f)) * scale;
+          for (int j = 0; j < VEC; ++j) d[j] = z[i * VEC + j] * inv_scale;  // softmax * grad_scale
+          if (v == vy) {  // exactly one lane, once per row: subtract the one-hot
+#pragma unroll
+            for (int j = 0; j < VEC; ++j)
+              if (j == jy) d[j] = (z[i * VEC + j] * inv - 1.0f) * scale;
           }
           if constexpr (kBf16) {
             const uint32_t w[4] = {pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),

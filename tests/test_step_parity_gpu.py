@@ -143,13 +143,13 @@ def test_host_fed_step_matches_resident_step():
     rows, batch = 1024, 256
     ds = make_synthetic(rows, spec)
     idx = rank_indices(rows, 1, 0)
-    a = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16", use_graph=False))
-    b = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16", use_graph=False))
-    for s in range(3):
+    a = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16"))
+    b = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16"))
+    for s in range(4):   # eager, then graph capture + replay on both staging buffers
         r = idx[s * batch:(s + 1) * batch]
         a.step()
-        b.step_from_host(ds.dense[r].pin_memory(), ds.cat[r].pin_memory(), ds.label[r].pin_memory())
-        assert abs(a.loss_value() - b.loss_value()) <= 1e-5 * max(1.0, abs(a.loss_value()))
+        ticket = b.step_from_host(ds.dense[r].pin_memory(), ds.cat[r].pin_memory(), ds.label[r].pin_memory())
+        assert abs(a.loss_value() - b.host_loss(ticket)) <= 1e-5 * max(1.0, abs(a.loss_value()))
 
 
 def test_no_cpu_fallback():
