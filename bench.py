@@ -232,22 +232,22 @@ def run_b200(args, rank, local_rank, world):
 
     # ---- end-to-end measurement: host batches, H2D inside the timed region, loss read back every step --------
     nb = min(BATCHES_PER_RANK, 4)
-    host = [(host_local.dense[i * B:(i + 1) * B].pin_memory(), host_local.cat[i * B:(i + 1) * B].pin_memory(),
-             host_local.label[i * B:(i + 1) * B].pin_memory()) for i in range(nb)]
+    host = [eng.pack_host_batch(host_local.dense[i * B:(i + 1) * B], host_local.cat[i * B:(i + 1) * B],
+                                host_local.label[i * B:(i + 1) * B]) for i in range(nb)]
     e2e_steps = max(3, min(args.steps, 50))
-    for i in range(4):                      # warm-up: eager step, then graph capture for both staging buffers
-        eng.host_loss(eng.step_from_host(*host[i % nb]))
+    for i in range(5):                      # warm-up: eager step, then graph capture for every staging buffer
+        eng.host_loss(eng.step_from_host(host[i % nb]))
     eng.synchronize()
     barrier()
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     g0.record(eng.main)
-    prev = None
+    pending = []
     for i in range(e2e_steps):
-        ticket = eng.step_from_host(*host[i % nb])     # H2D of this step's batch, then the step, then loss D2H
-        if prev is not None:
-            _ = eng.host_loss(prev)                    # every step's loss is read on the host, one step behind
-        prev = ticket
-    _ = eng.host_loss(prev)
+        pending.append(eng.step_from_host(host[i % nb]))   # H2D of this step's batch, then the step, then loss D2H
+        if len(pending) > 2:
+            _ = eng.host_loss(pending.pop(0))              # every step's loss is read on the host, two steps behind
+    while pending:
+        _ = eng.host_loss(pending.pop(0))
     g1.record(eng.main)
     eng.synchronize()
     barrier()

@@ -335,44 +335,66 @@ class TrainStep:
         self._enqueue(self.tail, None, self.row_idx[off:], None, False)
         self.host_steps += 1
 
+    HOST_STAGES = 3  # staging buffers of the host-fed path: the host can run two steps ahead of the GPU
+
+    def host_batch_bytes(self, rows: int) -> int:
+        spec = self.spec
+        return rows * (4 * spec.num_dense + 8 * spec.num_cat + 8)
+
+    def pack_host_batch(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> torch.Tensor:
+        """Lay one raw batch out as ONE pinned host buffer [dense fp32 | cat int64 | label int64] so that it crosses
+        PCIe in a single cudaMemcpyAsync (what a data-loader thread would hand to the training loop)."""
+        B = dense.shape[0]
+        buf = torch.empty(self.host_batch_bytes(B), dtype=torch.uint8).pin_memory()
+        o1 = 4 * self.spec.num_dense * B
+        o2 = o1 + 8 * self.spec.num_cat * B
+        buf[:o1].view(torch.float32).view(B, -1).copy_(dense)
+        if self.spec.num_cat:
+            buf[o1:o2].view(torch.int64).view(B, -1).copy_(cat)
+        buf[o2:].view(torch.int64).copy_(label)
+        return buf
+
+    def _stage_views(self, raw: torch.Tensor, B: int) -> TabularDataset:
+        o1 = 4 * self.spec.num_dense * B
+        o2 = o1 + 8 * self.spec.num_cat * B
+        return TabularDataset(raw[:o1].view(torch.float32).view(B, self.spec.num_dense),
+                              raw[o1:o2].view(torch.int64).view(B, self.spec.num_cat),
+                              raw[o2: o2 + 8 * B].view(torch.int64), self.ds.mean, self.ds.std)
+
     def _init_host_path(self) -> None:
-        bs, dev, spec = self.cfg.batch_size, self.dev, self.spec
+        bs, dev, n = self.cfg.batch_size, self.dev, self.HOST_STAGES
         self.identity_idx = torch.arange(bs, dtype=torch.int64, device=dev)
-        self._stages = [TabularDataset(torch.empty(bs, spec.num_dense, dtype=torch.float32, device=dev),
-                                       torch.empty(bs, spec.num_cat, dtype=torch.int64, device=dev),
-                                       torch.empty(bs, dtype=torch.int64, device=dev), self.ds.mean, self.ds.std)
-                        for _ in range(2)]
+        self._stage_raw = [torch.empty(self.host_batch_bytes(bs), dtype=torch.uint8, device=dev) for _ in range(n)]
+        self._stages = [self._stage_views(r, bs) for r in self._stage_raw]
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self._stage_ready = [torch.cuda.Event() for _ in range(2)]
-        self._stage_free = [torch.cuda.Event() for _ in range(2)]
-        self._loss_ev = [torch.cuda.Event() for _ in range(2)]
-        self._loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
-        self._host_graphs = [None, None]
+        self._stage_ready = [torch.cuda.Event() for _ in range(n)]
+        self._stage_free = [torch.cuda.Event() for _ in range(n)]
+        self._loss_ev = [torch.cuda.Event() for _ in range(n)]
+        self._loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(n)]
+        self._host_graphs = [None] * n
         self._host_k = 0
         torch.cuda.synchronize(dev)
 
-    def step_from_host(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> int:
-        """One step on a batch that lives in pinned HOST memory: the reference's per-step H2D copies
-        (task.py:305,307) followed by the same device step, then an asynchronous device->host copy of the step's
-        loss.  Two staging buffers alternate, so the copy of batch i+1 overlaps the compute of batch i (the
-        reference gets the same overlap from its DataLoader workers + non_blocking copies).
-        Returns a ticket for `host_loss(ticket)`."""
-        B = dense.shape[0]
-        if B > self.cfg.batch_size:
-            raise ValueError("host batch larger than the configured batch size")
+    def step_from_host(self, packed: torch.Tensor, rows: Optional[int] = None) -> int:
+        """One step on a batch that lives in pinned HOST memory (`pack_host_batch`): the reference's per-step H2D
+        copies (task.py:305,307) followed by the same device step, then an asynchronous device->host copy of the
+        step's loss.  Three staging buffers rotate, so the copies of the next batches overlap the compute of this one
+        (the reference gets the same overlap from its DataLoader workers + non_blocking copies).
+        Returns a ticket for `host_loss(ticket)`; a ticket is valid until HOST_STAGES further steps were issued."""
+        bs = self.cfg.batch_size
+        B = bs if rows is None else rows
+        if B > bs or packed.numel() != self.host_batch_bytes(B):
+            raise ValueError("host batch does not match the configured batch size / layout")
         if self.identity_idx is None:
             self._init_host_path()
         k = self._host_k
-        self._host_k ^= 1
-        stage = self._stages[k]
+        self._host_k = (k + 1) % self.HOST_STAGES
         self.copy_stream.wait_event(self._stage_free[k])      # the step that last read this stage is done
         with torch.cuda.stream(self.copy_stream):
-            stage.dense[:B].copy_(dense, non_blocking=True)
-            stage.cat[:B].copy_(cat, non_blocking=True)
-            stage.label[:B].copy_(label, non_blocking=True)
+            self._stage_raw[k][: packed.numel()].copy_(packed, non_blocking=True)
         self._stage_ready[k].record(self.copy_stream)
         self.main.wait_event(self._stage_ready[k])
-        if B == self.cfg.batch_size and self.cfg.use_graph and self.host_steps > 0:
+        if B == bs and self.cfg.use_graph and self.host_steps > 0:
             if self._host_graphs[k] is None:
                 import ctypes as C
 
@@ -380,13 +402,14 @@ class TrainStep:
                 self.comm_stream.synchronize()
                 self.lib.graph_begin(self.main.cuda_stream)
                 try:
-                    self._enqueue(B, stage, self.identity_idx, None, False)
+                    self._enqueue(B, self._stages[k], self.identity_idx, None, False)
                 finally:
                     out = C.c_void_p()
                     self.lib.graph_end(self.main.cuda_stream, C.byref(out))
                 self._host_graphs[k] = out
             self.lib.graph_launch(self._host_graphs[k], self.main.cuda_stream)
         else:
+            stage = self._stages[k] if B == bs else self._stage_views(self._stage_raw[k], B)
             self._enqueue(B, stage, self.identity_idx, None, False)
         self._stage_free[k].record(self.main)
         with torch.cuda.stream(self.main):
@@ -426,4 +449,4 @@ class TrainStep:
         for g in getattr(self, "_host_graphs", []):
             if g is not None:
                 self.lib.graph_destroy(g)
-        self._host_graphs = [None, None]
+        self._host_graphs = [None] * self.HOST_STAGES

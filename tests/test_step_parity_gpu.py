@@ -145,10 +145,10 @@ def test_host_fed_step_matches_resident_step():
     idx = rank_indices(rows, 1, 0)
     a = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16"))
     b = TrainStep(spec, init_parameters(spec, 0), ds, idx, StepConfig(batch_size=batch, precision="bf16"))
-    for s in range(4):   # eager, then graph capture + replay on both staging buffers
+    for s in range(4):   # eager, then graph capture + replay on the staging buffers
         r = idx[s * batch:(s + 1) * batch]
         a.step()
-        ticket = b.step_from_host(ds.dense[r].pin_memory(), ds.cat[r].pin_memory(), ds.label[r].pin_memory())
+        ticket = b.step_from_host(b.pack_host_batch(ds.dense[r], ds.cat[r], ds.label[r]))
         assert abs(a.loss_value() - b.host_loss(ticket)) <= 1e-5 * max(1.0, abs(a.loss_value()))
 
 
