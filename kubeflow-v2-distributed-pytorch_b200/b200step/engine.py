@@ -125,7 +125,8 @@ class TrainStep:
         self.acts = [torch.zeros(B, o, dtype=self.dt, device=dev) for (_, o) in dims]  # acts[-1] = logits
         self.dlogits = torch.zeros_like(self.acts[-1]) if cfg.keep_logits else self.acts[-1]
         wmax = (max([o for (_, o) in dims[:-1]] + [8]) + 7) // 8 * 8
-        self.dh = [torch.zeros(B, wmax, dtype=self.dt, device=dev) for _ in range(2)]  # ping-pong hidden grads
+        # gradient wrt each hidden activation; all stay alive until the wgrad phase
+        self.dh = [torch.zeros(B, wmax, dtype=self.dt, device=dev) for _ in range(max(self.L - 1, 1))]
         self.dx0 = torch.zeros(B, self.k0, dtype=self.dt, device=dev)
         self.y = torch.zeros(B, dtype=torch.int64, device=dev)
         self.idx = torch.zeros(B, max(spec.num_cat, 1), dtype=torch.int32, device=dev)
@@ -227,51 +228,62 @@ class TrainStep:
                          grad_scale=1.0 / (batch * cfg.world), stream=st)
         n += 2
         # backward ---------------------------------------------------------------------------------------
+        # Phase 1 walks the dgrad chain down to the embedding gradient, phase 2 runs the wgrad GEMMs.  The table
+        # gradients (the largest bucket, and in torch's autograd order the LAST one to become ready) are therefore
+        # finished first and their all-reduce hides under all the wgrad GEMMs.
         inv_keep = 1.0 / (1.0 - spec.dropout) if spec.dropout > 0 else 1.0
         bucket_of = {ready: bi for bi, (_, _, ready) in enumerate(self.buckets)}
-        dy = self.dlogits
+        dys = [None] * L
+        dys[L - 1] = self.dlogits
+        for li in range(L - 1, 0, -1):
+            k, o = dims[li]
+            dx = self.dh[li - 1][:, :k]
+            # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums = bias gradient of layer l-1
+            ops.linear_dgrad(dys[li], self._w(li), None, dx, M=batch, N=o, K=k, relu=True, dscale=inv_keep,
+                             relu_mask=self.masks[li - 1], dbias=self._b(li - 1, grad=True),
+                             scratch=self.dg_scratch, stream=st)
+            n += 2
+            dys[li - 1] = dx
+        if spec.num_cat:
+            ops.linear_dgrad(dys[0], self._w(0), None, self.dx0, M=batch, N=dims[0][1], K=self.k0, relu=False,
+                             stream=st)
+            ops.zero(self.gtables, stream=st)
+            ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, num_dense=spec.num_dense,
+                        num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
+            n += 3
+            if -1 in bucket_of:
+                n += self._reduce_bucket(bucket_of[-1])
         for li in range(L - 1, -1, -1):
             k, o = dims[li]
             kk = self.k0 if li == 0 else k
             x_in = self.x0 if li == 0 else self.acts[li - 1]
-            if li > 0:
-                dx = self.dh[li % 2][:, :kk]
-                # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums = bias gradient of layer l-1
-                ops.linear_dgrad(dy, self._w(li), None, dx, M=batch, N=o, K=kk, relu=True, dscale=inv_keep,
-                                 relu_mask=self.masks[li - 1], dbias=self._b(li - 1, grad=True),
-                                 scratch=self.dg_scratch, stream=st)
-                n += 2
-            elif spec.num_cat:
-                dx = self.dx0
-                ops.linear_dgrad(dy, self._w(li), None, dx, M=batch, N=o, K=kk, relu=False, stream=st)
-                n += 1
-            else:
-                dx = None
-            ops.linear_wgrad(dy, x_in, self._gw(li), M=batch, N=o, K=kk, stream=st)
+            ops.linear_wgrad(dys[li], x_in, self._gw(li), M=batch, N=o, K=kk, stream=st)
             n += 2  # memset (split-K) + GEMM
             if li in bucket_of:
                 n += self._reduce_bucket(bucket_of[li])
-            dy = dx
-        if spec.num_cat:
-            ops.zero(self.gtables, stream=st)
-            ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, num_dense=spec.num_dense,
-                        num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
-            n += 2
-            if -1 in bucket_of:
-                n += self._reduce_bucket(bucket_of[-1])
-        # join the comm stream, then the optimizer ----------------------------------------------------------
-        if cfg.world > 1 and cfg.overlap_comm:
-            for ev in self._ev_done:
-                st.wait_event(ev)
+        # optimizer ----------------------------------------------------------------------------------------
+        # world > 1: one launch per bucket, each gated only by that bucket's all-reduce, so the update of the early
+        # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer.
         n_shadow = lay.n_shadow if self.shadow is not None else 0
-        if cfg.optimizer == "sgd":
-            ops.sgd_step(self.p, self.g, self.s1, self.shadow, n_shadow=n_shadow, lr=cfg.lr,
-                         momentum=cfg.momentum, weight_decay=cfg.weight_decay, stream=st)
+        if cfg.world > 1 and cfg.overlap_comm:
+            ranges = [(self._ev_done[bi], s_, e_) for bi, (s_, e_, _) in enumerate(self.buckets)]
+            order = sorted(range(len(ranges)), key=lambda bi: -1 if self.buckets[bi][2] == -1 else L - self.buckets[bi][2])
+            ranges = [ranges[bi] for bi in order]   # in the order their all-reduces were issued
         else:
-            ops.adam_step(self.p, self.g, self.s1, self.s2, self.shadow, self.step_ctr, n_shadow=n_shadow,
-                          lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                          weight_decay=cfg.weight_decay, stream=st)
-        n += 1
+            ranges = [(None, 0, lay.total)]
+        for ev, s_, e_ in ranges:
+            if ev is not None:
+                st.wait_event(ev)
+            ns = max(0, min(n_shadow, e_) - s_)
+            sh = self.shadow[s_:] if (self.shadow is not None and ns > 0) else None
+            if cfg.optimizer == "sgd":
+                ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
+                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, stream=st)
+            else:
+                ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, self.step_ctr,
+                              n_shadow=ns, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
+                              weight_decay=cfg.weight_decay, stream=st)
+            n += 1
         if advance:
             ops.advance_step(self.cursor, self.step_ctr, max(self.steps_per_epoch_full, 1), stream=st)
         else:
