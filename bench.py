@@ -268,16 +268,25 @@ def run_b200(args, rank, local_rank, world):
             dist.destroy_process_group()
         return
     peaks = _peaks()
+    # the dominant kernel = the single launch with the largest share of the step (ms x launches per step)
+    total_ms = sum(r["ms"] * r["per_step"] for r in prof)
+    for r in prof:
+        r["share"] = r["ms"] * r["per_step"] / total_ms
     top = max(prof, key=lambda r: r["ms"])
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")  # dram bytes per launch from `ncu --set full` captures
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            traffic = json.load(fh).get(args.workload, {}).get(top["name"])
     if top["bound"] == "tensor":
         peak = peaks["bf16_tflops"] if wl["precision"] == "bf16" else peaks["bf16_tflops"] / 2.0
         roof = {"bound": "tensor", "kernel": top["name"], "achieved": top["tflops"], "peak": peak, "unit": "TFLOP/s",
-                "frac": top["tflops"] / peak, "traffic": None,
+                "frac": top["tflops"] / peak, "traffic": traffic, "share_of_step": top["share"],
                 "peak_source": peaks["source"] + (" bf16 burst" if wl["precision"] == "bf16"
                                                   else " bf16 burst / 2 (tf32 runs at half the bf16 rate)")}
     else:
         roof = {"bound": "hbm", "kernel": top["name"], "achieved": top["gbs"], "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": top["gbs"] / peaks["hbm_gbs"], "traffic": None,
+                "unit": "GB/s", "frac": top["gbs"] / peaks["hbm_gbs"], "traffic": traffic, "share_of_step": top["share"],
                 "peak_source": peaks["source"] + " copy bandwidth"}
     flops = spec.flops_per_sample()["total"]
     step_tflops = flops * B / (ms / args.steps / 1e3) / 1e12
@@ -343,9 +352,9 @@ def profile_kernels(eng, spec, B, world):
             elif name == "zero":
                 work = {"bytes": a[0].numel() * a[0].element_size()}
             elif name == "sgd_step":
-                work = {"bytes": a[0].numel() * 20 + 2 * k.get("n_shadow", 0)}
+                work = {"bytes": a[0].numel() * (24 if k.get("zero_grad") else 20) + 2 * k.get("n_shadow", 0)}
             elif name == "adam_step":
-                work = {"bytes": a[0].numel() * 28 + 2 * k.get("n_shadow", 0)}
+                work = {"bytes": a[0].numel() * (32 if k.get("zero_grad") else 28) + 2 * k.get("n_shadow", 0)}
             records.append((label, a0, a1, work))
             return r
         return inner

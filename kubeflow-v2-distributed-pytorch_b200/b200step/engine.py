@@ -247,18 +247,19 @@ class TrainStep:
         if spec.num_cat:
             ops.linear_dgrad(dys[0], self._w(0), None, self.dx0, M=batch, N=dims[0][1], K=self.k0, relu=False,
                              stream=st)
-            ops.zero(self.gtables, stream=st)
+            # (the table gradients were zeroed by the previous optimizer pass / at allocation)
             ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, num_dense=spec.num_dense,
                         num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
-            n += 3
+            n += 2
             if -1 in bucket_of:
                 n += self._reduce_bucket(bucket_of[-1])
         for li in range(L - 1, -1, -1):
             k, o = dims[li]
             kk = self.k0 if li == 0 else k
             x_in = self.x0 if li == 0 else self.acts[li - 1]
-            ops.linear_wgrad(dys[li], x_in, self._gw(li), M=batch, N=o, K=kk, stream=st)
-            n += 2  # memset (split-K) + GEMM
+            # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
+            ops.linear_wgrad(dys[li], x_in, self._gw(li), M=batch, N=o, K=kk, accumulate=True, stream=st)
+            n += 1
             if li in bucket_of:
                 n += self._reduce_bucket(bucket_of[li])
         # optimizer ----------------------------------------------------------------------------------------
@@ -278,11 +279,11 @@ class TrainStep:
             sh = self.shadow[s_:] if (self.shadow is not None and ns > 0) else None
             if cfg.optimizer == "sgd":
                 ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
-                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, stream=st)
+                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True, stream=st)
             else:
                 ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, self.step_ctr,
                               n_shadow=ns, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                              weight_decay=cfg.weight_decay, stream=st)
+                              weight_decay=cfg.weight_decay, zero_grad=True, stream=st)
             n += 1
         if advance:
             ops.advance_step(self.cursor, self.step_ctr, max(self.steps_per_epoch_full, 1), stream=st)
@@ -449,9 +450,6 @@ class TrainStep:
         self.synchronize()
         return self.layout.unflatten(self.p)
 
-    def grads(self) -> Dict[str, torch.Tensor]:
-        self.synchronize()
-        return self.layout.unflatten(self.g, prefix="")
 
     def close(self) -> None:
         self.synchronize()

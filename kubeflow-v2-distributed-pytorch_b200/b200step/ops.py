@@ -108,17 +108,18 @@ def emb_bwd(dx, idx, dtables, *, batch: int, num_dense: int, num_cat: int, table
                       embed_dim, dtype_code(dx.dtype), _stream(stream))
 
 
-def sgd_step(p, g, buf, shadow, *, n_shadow: int, lr: float, momentum: float, weight_decay: float, stream=None):
+def sgd_step(p, g, buf, shadow, *, n_shadow: int, lr: float, momentum: float, weight_decay: float,
+             zero_grad: bool = False, stream=None):
     _cuda(p, g, buf, shadow)
     get_lib().sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), p.numel(), n_shadow, lr, momentum, weight_decay,
-                       _stream(stream))
+                       int(zero_grad), _stream(stream))
 
 
 def adam_step(p, g, m, v, shadow, step, *, n_shadow: int, lr: float, beta1: float, beta2: float, eps: float,
-              weight_decay: float, stream=None):
+              weight_decay: float, zero_grad: bool = False, stream=None):
     _cuda(p, g, m, v, shadow, step)
     get_lib().adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), n_shadow, lr, beta1, beta2,
-                        eps, weight_decay, ptr(step), _stream(stream))
+                        eps, weight_decay, ptr(step), int(zero_grad), _stream(stream))
 
 
 def cast_bf16(src, dst, stream=None):

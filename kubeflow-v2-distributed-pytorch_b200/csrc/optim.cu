@@ -18,8 +18,8 @@ __device__ __forceinline__ void store_shadow4(void* shadow, long long i, float a
 }
 
 __global__ void __launch_bounds__(OPT_THREADS)
-sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf,
-           void* __restrict__ shadow, long long n, long long n_shadow, float lr, float mu, float wd) {
+sgd_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ buf,
+           void* __restrict__ shadow, long long n, long long n_shadow, float lr, float mu, float wd, int zero_grad) {
   const long long nv = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += stride) {
@@ -39,6 +39,7 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
     *reinterpret_cast<float4*>(buf + i) = bb;
     *reinterpret_cast<float4*>(p + i) = pp;
     if (i < n_shadow) store_shadow4(shadow, i, pp.x, pp.y, pp.z, pp.w);
+    if (zero_grad) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);  // optimizer.zero_grad()
   }
   // scalar tail (n % 4)
   for (long long i = (nv << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -48,6 +49,7 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
     buf[i] = bi;
     p[i] = pi;
     if (i < n_shadow) reinterpret_cast<__nv_bfloat16*>(shadow)[i] = __float2bfloat16_rn(pi);
+    if (zero_grad) g[i] = 0.f;
   }
 }
 
@@ -63,9 +65,9 @@ __device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v,
 }
 
 __global__ void __launch_bounds__(OPT_THREADS)
-adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             void* __restrict__ shadow, long long n, long long n_shadow, double lr, double b1, double b2, float eps,
-            float wd, const int* __restrict__ step) {
+            float wd, const int* __restrict__ step, int zero_grad) {
   // bias corrections in double like torch (python floats): 1 - beta**t, t = completed steps + 1
   const double t = (double)(*step) + 1.0;
   const float step_size = (float)(lr / (1.0 - pow(b1, t)));
@@ -87,12 +89,14 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     *reinterpret_cast<float4*>(v + i) = vv;
     *reinterpret_cast<float4*>(p + i) = pp;
     if (i < n_shadow) store_shadow4(shadow, i, pp.x, pp.y, pp.z, pp.w);
+    if (zero_grad) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   for (long long i = (nv << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     float pi = p[i], mi = m[i], vi = v[i];
     adam_one(pi, g[i], mi, vi, wd, w1, b2f, w2, eps, step_size, bc2_sqrt);
     p[i] = pi; m[i] = mi; v[i] = vi;
     if (i < n_shadow) reinterpret_cast<__nv_bfloat16*>(shadow)[i] = __float2bfloat16_rn(pi);
+    if (zero_grad) g[i] = 0.f;
   }
 }
 
@@ -166,8 +170,8 @@ static int stream_grid(long long work_items) {
 
 using namespace b200;
 
-extern "C" int b200_sgd_step(float* p, const float* g, float* momentum_buf, void* shadow_bf16, int64_t n,
-                             int64_t n_shadow, double lr, double momentum, double weight_decay,
+extern "C" int b200_sgd_step(float* p, float* g, float* momentum_buf, void* shadow_bf16, int64_t n,
+                             int64_t n_shadow, double lr, double momentum, double weight_decay, int zero_grad,
                              b200_stream_t stream) {
   B200_REQUIRE(n > 0 && n_shadow >= 0 && n_shadow <= n, "bad sizes n=%lld n_shadow=%lld", (long long)n, (long long)n_shadow);
   B200_REQUIRE(n_shadow % 4 == 0 || n_shadow == n, "n_shadow must be a multiple of 4");
@@ -175,14 +179,14 @@ extern "C" int b200_sgd_step(float* p, const float* g, float* momentum_buf, void
                  reinterpret_cast<uintptr_t>(momentum_buf)) & 15) == 0, "p/g/buf must be 16-byte aligned");
   if (!shadow_bf16) n_shadow = 0;
   sgd_kernel<<<stream_grid(n / 4 + 1), OPT_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay);
+      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay, zero_grad);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-extern "C" int b200_adam_step(float* p, const float* g, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+extern "C" int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
                               int64_t n, int64_t n_shadow, double lr, double beta1, double beta2, double eps,
-                              double weight_decay, const int32_t* step, b200_stream_t stream) {
+                              double weight_decay, const int32_t* step, int zero_grad, b200_stream_t stream) {
   B200_REQUIRE(n > 0 && n_shadow >= 0 && n_shadow <= n, "bad sizes n=%lld n_shadow=%lld", (long long)n, (long long)n_shadow);
   B200_REQUIRE(n_shadow % 4 == 0 || n_shadow == n, "n_shadow must be a multiple of 4");
   B200_REQUIRE(step != nullptr, "adam needs the device step counter");
@@ -190,7 +194,8 @@ extern "C" int b200_adam_step(float* p, const float* g, float* exp_avg, float* e
                  reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0, "p/g/m/v must be 16-byte aligned");
   if (!shadow_bf16) n_shadow = 0;
   adam_kernel<<<stream_grid(n / 4 + 1), OPT_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      p, g, exp_avg, exp_avg_sq, shadow_bf16, n, n_shadow, lr, beta1, beta2, (float)eps, (float)weight_decay, step);
+      p, g, exp_avg, exp_avg_sq, shadow_bf16, n, n_shadow, lr, beta1, beta2, (float)eps, (float)weight_decay, step,
+      zero_grad);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
