@@ -60,7 +60,9 @@ int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t*
  *        relu_mask (nullable, either side): 1 bit per element, word [row, col/32], row stride ldmask words; the
  *        forward writes (y > 0) and the backward of the NEXT layer reads it instead of re-reading `act`.
  *        dbias (nullable) [K] = column sums of the stored dx = bias gradient of the layer that produced `act`
- *        (addmm backward wrt bias), deterministic two-stage reduction through `scratch`.
+ *        (addmm backward wrt bias).  With `scratch` (b200_dgrad_scratch_floats): deterministic two-stage reduction,
+ *        dbias is overwritten.  With scratch == NULL: every CTA adds its column sums onto dbias with float
+ *        atomics — dbias must hold zeros (or a value to accumulate onto) and the sum order is not fixed.
  * wgrad (task.py:311, addmm backward wrt weight): dw[N,K] (+)= dy[M,N]^T · x[M,K], fp32 result.
  * K and ld* must make every row 16-byte aligned (K%4==0 for F32, K%8==0 for BF16; same for N where N is a row length).
  */

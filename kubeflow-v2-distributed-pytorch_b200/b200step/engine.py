@@ -48,6 +48,7 @@ class StepConfig:
     first_bucket_bytes: int = 1 << 20    # DDP defaults
     bucket_cap_bytes: int = 25 << 20
     keep_logits: bool = False            # keep logits and dlogits in separate buffers (tests)
+    deterministic_bias_grad: bool = False  # hidden-layer bias grads through a fixed-order reduction instead of atomics
 
 
 class Communicator:
@@ -241,8 +242,8 @@ class TrainStep:
             # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums = bias gradient of layer l-1
             ops.linear_dgrad(dys[li], self._w(li), None, dx, M=batch, N=o, K=k, relu=True, dscale=inv_keep,
                              relu_mask=self.masks[li - 1], dbias=self._b(li - 1, grad=True),
-                             scratch=self.dg_scratch, stream=st)
-            n += 2
+                             scratch=self.dg_scratch if cfg.deterministic_bias_grad else None, stream=st)
+            n += 2 if cfg.deterministic_bias_grad else 1
             dys[li - 1] = dx
         if spec.num_cat:
             ops.linear_dgrad(dys[0], self._w(0), None, self.dx0, M=batch, N=dims[0][1], K=self.k0, relu=False,

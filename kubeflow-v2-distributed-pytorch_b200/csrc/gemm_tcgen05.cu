@@ -42,7 +42,8 @@ struct GemmParams {
   uint32_t* mask_out;        // fwd: bit j of word [row, col/32] = (output[row, col] > 0)
   const uint32_t* mask_in;   // dgrad: same layout, replaces reading `act`
   long long ldmask;          // row stride of the bit mask in 32-bit words
-  float* cs_partials;        // dgrad: per (m_tile, warp) column sums of the stored output, [m_tiles*4, N]
+  float* cs_partials;        // dgrad: per (CTA, lane quarter) column sums of the stored output (deterministic mode)
+  float* cs_atomic;          // dgrad: or add each CTA's column sums straight onto this zeroed [N] vector
   float dscale;
   int flags;
   float dropout_p;
@@ -388,7 +389,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
             if constexpr (kEpi == EPI_DGRAD) {
-              if (p.cs_partials != nullptr) {
+              if (p.cs_partials != nullptr || p.cs_atomic != nullptr) {
                 // column sums over this warp's 32 rows of what is stored (rounded to the output dtype):
                 // halving butterfly, 31 shuffles, lane i ends with the sum of column col0 + i
                 float r[32];
@@ -459,6 +460,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                      (unit % p.n_tiles) * BLOCK_N + chalf * (BLOCK_N / 2) + lane;
 #pragma unroll
         for (int k = 0; k < 4; ++k) dst[k * 32] = csacc[k];
+      } else if (p.cs_atomic != nullptr) {
+        // one coalesced red.add per 32 columns and warp: ~300 adds per address over the whole kernel
+        const int c0 = (unit % p.n_tiles) * BLOCK_N + chalf * (BLOCK_N / 2) + lane;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (c0 + k * 32 < p.N) atomicAdd(p.cs_atomic + c0 + k * 32, csacc[k]);
       }
     }
     if (lane == 0) bulk_wait_all();  // all output writes issued by this warp have completed
@@ -640,7 +647,7 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
                                         (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
                "relu_mask needs a 16-byte aligned base and a row stride (%lld words) that is a multiple of 4 and covers K=%lld",
                (long long)ldmask, (long long)K);
-  B200_REQUIRE(dbias == nullptr || (scratch != nullptr && scratch_floats >= b200_dgrad_scratch_floats(M, K)),
+  B200_REQUIRE(dbias == nullptr || scratch == nullptr || scratch_floats >= b200_dgrad_scratch_floats(M, K),
                "dgrad bias-gradient scratch too small: need %lld floats", (long long)b200_dgrad_scratch_floats(M, K));
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64;   // contraction (over N) elements per stage
@@ -660,14 +667,16 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
   p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = dx; p.ldo = lddx; p.act = act; p.ldact = ldact; p.flags = flags; p.dscale = dscale;
-  p.mask_in = relu_mask; p.ldmask = ldmask; p.cs_partials = dbias ? scratch : nullptr;
+  p.mask_in = relu_mask; p.ldmask = ldmask;
+  p.cs_partials = dbias ? scratch : nullptr;
+  p.cs_atomic = (dbias && !scratch) ? dbias : nullptr;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // with bias-gradient accumulation every work unit must keep one n_tile: units = multiple of n_tiles
   int units = 0;
   if (int r = tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st, dbias ? p.n_tiles : 1, &units)
                    : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st, dbias ? p.n_tiles : 1, &units))
     return r;
-  if (dbias)
+  if (dbias && scratch)
     return launch_reduce_partials(scratch, (units / p.n_tiles) * gemm_ctas() * 4, p.n_tiles * BLOCK_N, (int)K,
                                   dbias, st);
   return 0;

@@ -126,6 +126,11 @@ def test_relu_bitmask_and_fused_bias_grad(ops, dtype, M, N, K):
     ops.linear_dgrad(dy2, w2, None, dx_mask, M=M, N=N2, K=N, relu=True, relu_mask=mask, dbias=db2, scratch=scratch)
     torch.cuda.synchronize()
     assert torch.equal(db, db2)                                  # deterministic reduction order
+    # without scratch: float atomics onto a zeroed vector (what the training step uses)
+    db3 = torch.zeros_like(db)
+    ops.linear_dgrad(dy2, w2, None, dx_mask, M=M, N=N2, K=N, relu=True, relu_mask=mask, dbias=db3)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(db3, db, rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
 
 
 def test_gemm_rejects_misaligned(ops):
