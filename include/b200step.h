@@ -38,9 +38,11 @@ int b200_device_sm_count(int* out_host);     /* SM count of the current device *
  *   DistributedSampler/DataLoader batching (task.py:260-263: batch b = rows row_idx[cursor*batch + b]),
  *   transforms.Normalize (task.py:250-251 -> tensor.sub_(mean).div_(std), IEEE fp32 subtract then divide),
  *   the two H2D copies (task.py:305,307), and the model's embedding lookup + concat.
- * x_out[b, 0:num_dense]                     = (dense[r] - mean) / std            (bit-exact fp32, RNE to bf16 if x_dtype=BF16)
- * x_out[b, num_dense + t*dim : +dim]        = tables[t][cat[r,t]]                (bit-exact copy / RNE to bf16)
- * x_out[b, num_dense + num_cat*dim : ldx]   = 0                                  (K padding for the GEMMs)
+ * Column order of x_out (embeddings first, so that every gathered float4 lands on an aligned chunk of the row;
+ * the host keeps the first Linear's weight columns in the same order, b200step/model.py):
+ * x_out[b, t*dim : (t+1)*dim]                          = tables[t][cat[r,t]]      (bit-exact copy / RNE to bf16)
+ * x_out[b, num_cat*dim : num_cat*dim + num_dense]      = (dense[r] - mean) / std  (bit-exact fp32, RNE to bf16 if x_dtype=BF16)
+ * x_out[b, num_cat*dim + num_dense : ldx]              = 0                        (K padding for the GEMMs)
  * y_out[b] = label[r];  idx_out[b,t] = (int32) cat[r,t]  (kept for the embedding backward)
  * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.
  */
@@ -117,9 +119,10 @@ int b200_colsum_static(const void* dy, int64_t lddy, float* out, int64_t M, int6
                        b200_stream_t stream);
 
 /* ---- K-embbwd: embedding gradient scatter-add (task.py:311; embedding_dense_backward) -------
- * dtables[t][idx[b,t]][:] += dx[b, num_dense + t*dim : +dim]   (fp32 atomics; dtables must be zeroed by the caller) */
+ * dtables[t][idx[b,t]][:] += dx[b, emb_col0 + t*dim : +dim]   (fp32 atomics; dtables must be zeroed by the caller;
+ * emb_col0 % 4 == 0 — it is 0 in the layout b200_preprocess writes) */
 int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, float* dtables,
-                 int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
+                 int64_t batch, int emb_col0, int num_cat, int64_t table_rows, int embed_dim,
                  int dtype, b200_stream_t stream);
 
 /* ---- K-opt: fused optimizer over the flat parameter buffer ----------------------------------

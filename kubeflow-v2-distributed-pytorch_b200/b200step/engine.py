@@ -249,7 +249,7 @@ class TrainStep:
             ops.linear_dgrad(dys[0], self._w(0), None, self.dx0, M=batch, N=dims[0][1], K=self.k0, relu=False,
                              stream=st)
             # (the table gradients were zeroed by the previous optimizer pass / at allocation)
-            ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, num_dense=spec.num_dense,
+            ops.emb_bwd(self.dx0, self.idx, self.gtables, batch=batch, emb_col0=0,
                         num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
             n += 2
             if -1 in bucket_of:

@@ -92,7 +92,8 @@ class FlatLayout:
 
     Order: Linear weights/biases first (they also get a bf16 operand copy: `n_shadow` elements), embedding
     tables last.  The first Linear's weight is stored with its K dimension padded to `in_features_padded`
-    (pad columns are zero and stay zero: their gradient is X_pad^T dY = 0 and weight decay of 0 is 0).
+    (pad columns are zero and stay zero: their gradient is X_pad^T dY = 0 and weight decay of 0 is 0) and with
+    its input columns in the order the preprocess kernel writes them (`input_perm`).
     """
 
     def __init__(self, spec: ModelSpec):
@@ -122,14 +123,24 @@ class FlatLayout:
         return self.by_key[f"layers.{li}.bias"]
 
     def view(self, flat: torch.Tensor, seg: Segment) -> torch.Tensor:
-        """[rows, cols] strided view of a segment (biases: [cols])."""
+        """[rows, cols] strided view of a segment in STORED column order (biases: [cols])."""
         v = flat[seg.offset: seg.offset + seg.numel_stored].view(seg.rows, seg.ld)[:, : seg.cols]
         return v[0] if seg.key.endswith(".bias") else v
+
+    def input_perm(self) -> torch.Tensor:
+        """perm[j] = model (oracle / state_dict) input column held at stored column j of the preprocessed row x0 and
+        of the first Linear's weight.  The model's order is [dense | embeddings] (torch.cat in TabularMLP.features);
+        the step stores [embeddings | dense | pad] so that every gathered float4 is an aligned chunk of the row."""
+        nd, ne = self.spec.num_dense, self.spec.num_cat * self.spec.embed_dim
+        return torch.cat([torch.arange(nd, nd + ne), torch.arange(0, nd)])
 
     def flatten(self, tensors: Dict[str, torch.Tensor]) -> torch.Tensor:
         flat = torch.zeros(self.total, dtype=torch.float32)
         for seg in self.segments:
-            self.view(flat, seg).copy_(tensors[seg.key])
+            t = tensors[seg.key]
+            if seg.key == "layers.0.weight":
+                t = t[:, self.input_perm()]
+            self.view(flat, seg).copy_(t)
         return flat
 
     def unflatten(self, flat: torch.Tensor, prefix: str = "module.") -> Dict[str, torch.Tensor]:
@@ -137,8 +148,12 @@ class FlatLayout:
         out: Dict[str, torch.Tensor] = {}
         order = [s for s in self.segments if s.key.startswith("emb.")] + \
                 [s for s in self.segments if s.key.startswith("layers.")]
+        inv = torch.argsort(self.input_perm())
         for seg in order:
-            out[prefix + seg.key] = self.view(flat, seg).detach().to("cpu").contiguous().clone()
+            t = self.view(flat, seg).detach().to("cpu")
+            if seg.key == "layers.0.weight":
+                t = t[:, inv]                      # back to the model's [dense | embeddings] column order
+            out[prefix + seg.key] = t.contiguous().clone()
         return out
 
     def buckets(self, first_cap_bytes: int = 1 << 20, cap_bytes: int = 25 << 20) -> List[Tuple[int, int, int]]:

@@ -101,10 +101,10 @@ def colsum(dy, out, scratch, *, M: int, N: int, stream=None):
                      dtype_code(dy.dtype), _stream(stream))
 
 
-def emb_bwd(dx, idx, dtables, *, batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int,
+def emb_bwd(dx, idx, dtables, *, batch: int, emb_col0: int = 0, num_cat: int, table_rows: int, embed_dim: int,
             stream=None):
     _cuda(dx, idx, dtables)
-    get_lib().emb_bwd(ptr(dx), dx.stride(0), ptr(idx), ptr(dtables), batch, num_dense, num_cat, table_rows,
+    get_lib().emb_bwd(ptr(dx), dx.stride(0), ptr(idx), ptr(dtables), batch, emb_col0, num_cat, table_rows,
                       embed_dim, dtype_code(dx.dtype), _stream(stream))
 
 

@@ -123,14 +123,15 @@ __global__ void advance_step_kernel(int* cursor, int* step, int steps_per_epoch)
 }
 
 // ---- K-embbwd ----------------------------------------------------------------------------------------
-// One thread per (sample, table, float4 of the embedding row): reads 4 gradient values of dX and issues
-// one 128-bit red.global.add.v4.f32 into the table gradient.  Consecutive lanes cover consecutive
-// columns of dX, so the gradient read is coalesced; the scatter side is index-driven by nature.
+// One thread per (sample, table, float4 of the embedding row): one aligned 8-byte (bf16) / 16-byte (fp32) load of
+// the gradient row (embedding columns start at emb_col0, a multiple of 4 — column 0 in the step's layout) and one
+// 128-bit red.global.add.v4.f32 into the table gradient.  Consecutive lanes read consecutive chunks (coalesced);
+// the scatter side is index-driven by nature and resolves in L2.
 template <bool kBf16>
 __global__ void __launch_bounds__(OPT_THREADS)
 emb_bwd_kernel(const void* __restrict__ dx_, long long lddx, const int32_t* __restrict__ idx,
-               float* __restrict__ dtables, long long batch, int num_dense, int num_cat, long long table_rows,
-               int embed_dim) {
+               float* __restrict__ dtables, long long batch, int emb_col0, int num_cat, long long table_rows,
+               int embed_dim, int vpr_shift) {
   const int vec_per_row = embed_dim >> 2;
   const int vec_per_sample = num_cat * vec_per_row;
   const long long total = batch * vec_per_sample;
@@ -138,21 +139,19 @@ emb_bwd_kernel(const void* __restrict__ dx_, long long lddx, const int32_t* __re
   for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += stride) {
     const long long b = w / vec_per_sample;
     const int rem = (int)(w - b * vec_per_sample);
-    const int t = rem / vec_per_row;
+    const int t = vpr_shift >= 0 ? (rem >> vpr_shift) : (rem / vec_per_row);
     const int qv = rem - t * vec_per_row;
-    const int col = num_dense + t * embed_dim + qv * 4;
     float d0, d1, d2, d3;
     if constexpr (kBf16) {
-      const uint16_t* src = reinterpret_cast<const uint16_t*>(dx_) + b * lddx + col;  // 2-byte aligned only
-      d0 = __uint_as_float((uint32_t)src[0] << 16);
-      d1 = __uint_as_float((uint32_t)src[1] << 16);
-      d2 = __uint_as_float((uint32_t)src[2] << 16);
-      d3 = __uint_as_float((uint32_t)src[3] << 16);
+      const uint2 raw = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const uint16_t*>(dx_) + b * lddx +
+                                                              emb_col0 + 4 * rem));
+      d0 = bf16_lo(raw.x); d1 = bf16_hi(raw.x); d2 = bf16_lo(raw.y); d3 = bf16_hi(raw.y);
     } else {
-      const float* src = reinterpret_cast<const float*>(dx_) + b * lddx + col;
-      d0 = src[0]; d1 = src[1]; d2 = src[2]; d3 = src[3];
+      const float4 raw = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(dx_) + b * lddx +
+                                                               emb_col0 + 4 * rem));
+      d0 = raw.x; d1 = raw.y; d2 = raw.z; d3 = raw.w;
     }
-    const long long id = idx[b * num_cat + t];
+    const long long id = __ldg(idx + b * num_cat + t);
     float* dst = dtables + ((long long)t * table_rows + id) * embed_dim + qv * 4;
     red_add_v4(dst, d0, d1, d2, d3);
   }
@@ -214,20 +213,28 @@ extern "C" int b200_advance_step(int32_t* cursor, int32_t* step, int32_t steps_p
 }
 
 extern "C" int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, float* dtables, int64_t batch,
-                            int num_dense, int num_cat, int64_t table_rows, int embed_dim, int dtype,
+                            int emb_col0, int num_cat, int64_t table_rows, int embed_dim, int dtype,
                             b200_stream_t stream) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   if (num_cat == 0) return 0;
   B200_REQUIRE(embed_dim > 0 && embed_dim % 4 == 0, "embed_dim=%d must be a positive multiple of 4", embed_dim);
   B200_REQUIRE((reinterpret_cast<uintptr_t>(dtables) & 15) == 0, "dtables must be 16-byte aligned");
+  B200_REQUIRE(emb_col0 >= 0 && emb_col0 % 4 == 0 && lddx % 4 == 0 && (reinterpret_cast<uintptr_t>(dx) & 15) == 0,
+               "emb_bwd: dx, lddx and emb_col0 must keep every 4-element chunk aligned");
+  const int vpr = embed_dim / 4;
+  int vpr_shift = -1;
+  if ((vpr & (vpr - 1)) == 0) {
+    vpr_shift = 0;
+    while ((1 << vpr_shift) < vpr) ++vpr_shift;
+  }
   const long long total = (long long)batch * num_cat * (embed_dim / 4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == B200_BF16)
-    emb_bwd_kernel<true><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, num_dense,
-                                                                     num_cat, table_rows, embed_dim);
+    emb_bwd_kernel<true><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, emb_col0,
+                                                                     num_cat, table_rows, embed_dim, vpr_shift);
   else
-    emb_bwd_kernel<false><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, num_dense,
-                                                                      num_cat, table_rows, embed_dim);
+    emb_bwd_kernel<false><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, emb_col0,
+                                                                      num_cat, table_rows, embed_dim, vpr_shift);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

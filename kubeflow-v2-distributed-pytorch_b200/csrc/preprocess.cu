@@ -5,12 +5,15 @@
 // embedding lookup + concat at the front of the tabular model.  Results are bit-exact
 // with the CPU oracle: IEEE subtract then divide (no FMA contraction, no reciprocal), RNE to bf16.
 //
-// Layout: persistent warps, one sample per warp at a time.  The per-sample work is a chain of three dependent
-// gathers (sampler index -> dataset row -> 26 table rows); the chain of sample k+1 is started before sample k is
+// Column layout of the output row (an internal choice; the first Linear's weight columns are stored in the
+// same order, see b200step/model.py):   [ 26 x dim embedding columns | num_dense standardised columns | zero pad ].
+// With the embeddings first, float4 k of a sample's gathered table rows lands at element 4k of the row: every lane
+// writes one aligned 8-byte (bf16) / 16-byte (fp32) chunk and a warp writes 256 / 512 contiguous bytes per
+// instruction — no shared-memory staging, and the embedding backward reads the gradient back the same way.
+//
+// Persistent warps, one sample per warp at a time.  The per-sample work is a chain of three dependent gathers
+// (sampler index -> dataset row -> 26 table rows); the chain of sample k+1 is started before sample k is
 // finished (software pipelining in registers), so a warp pays one gather latency per sample instead of three.
-// The output row is assembled in a warp-private shared-memory row (embedding columns start at element
-// num_dense, which is not 16-byte aligned, so it is built with scalar shared stores) and leaves with
-// coalesced 128-bit stores.  Table rows are read with 128-bit streaming loads, one float4 per lane.
 #include "common.cuh"
 
 namespace b200 {
@@ -18,12 +21,15 @@ namespace b200 {
 constexpr int PRE_THREADS = 256;
 constexpr int PRE_WARPS = PRE_THREADS / 32;
 
-template <typename OutT>
-__device__ __forceinline__ OutT cvt_out(float v);
-template <>
-__device__ __forceinline__ float cvt_out<float>(float v) { return v; }
-template <>
-__device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+// four fp32 values -> one aligned store in the output dtype
+__device__ __forceinline__ void store4(float* dst, uint4 raw) { stg_stream(dst, raw); }
+__device__ __forceinline__ void store4(__nv_bfloat16* dst, uint4 raw) {
+  const uint2 o = make_uint2(pack_bf16x2(__uint_as_float(raw.x), __uint_as_float(raw.y)),
+                             pack_bf16x2(__uint_as_float(raw.z), __uint_as_float(raw.w)));
+  asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(dst), "r"(o.x), "r"(o.y) : "memory");
+}
+__device__ __forceinline__ void store1(float* dst, float v) { *dst = v; }
+__device__ __forceinline__ void store1(__nv_bfloat16* dst, float v) { *dst = __float2bfloat16_rn(v); }
 
 template <typename OutT>
 __global__ void __launch_bounds__(PRE_THREADS, 4)
@@ -33,22 +39,16 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
                   const float* __restrict__ stdv, const float* __restrict__ tables,
                   OutT* __restrict__ x_out, int64_t* __restrict__ y_out, int32_t* __restrict__ idx_out,
                   long long batch, int num_dense, int num_cat, long long table_rows, int embed_dim,
-                  long long ldx) {
-  extern __shared__ __align__(128) uint8_t pre_smem[];
+                  int vpr_shift, long long ldx) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  OutT* xr = reinterpret_cast<OutT*>(pre_smem) + (long long)warp * ldx;  // this warp's row
-  const uint32_t xr_s = smem_u32(xr);
   const long long cur = cursor ? (long long)(*cursor) : 0;
   const int64_t* ridx = row_idx + cur * batch;
-  const int vec_per_row = embed_dim >> 2;            // float4 chunks per table row
-  const int used = num_dense + num_cat * embed_dim;  // first padding column
-  const int row_vecs = (int)(ldx * sizeof(OutT) / 16);
+  const int vec_per_row = embed_dim >> 2;        // float4 chunks per table row
+  const int emb_cols = num_cat * embed_dim;      // dense columns start here
+  const int tail = (int)ldx - emb_cols;          // dense + zero padding
   const long long stride = (long long)gridDim.x * PRE_WARPS;
-  const float mu = lane < num_dense ? __ldg(mean + lane) : 0.f;     // num_dense <= 32 on the fast path
+  const float mu = lane < num_dense ? __ldg(mean + lane) : 0.f;  // num_dense <= 32 on the fast path
   const float sd = lane < num_dense ? __ldg(stdv + lane) : 1.f;
-
-  // K padding never changes: write it once
-  for (int j = used + lane; j < ldx; j += 32) xr[j] = cvt_out<OutT>(0.0f);
 
   long long b = (long long)blockIdx.x * PRE_WARPS + warp;
   // pipeline registers: stage A = sampler index, stage B = that row's dense value / first-32 categorical ids / label
@@ -75,11 +75,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
     }
     r_a = bn + stride < batch ? __ldg(ridx + bn + stride) : 0;
 
-    // dense columns: (x - mean) / std, IEEE fp32
-    if (lane < num_dense) xr[lane] = cvt_out<OutT>(__fdiv_rn(__fsub_rn(dense_cur, mu), sd));
-    for (int j = 32 + lane; j < num_dense; j += 32)  // > 32 dense columns: plain path
-      xr[j] = cvt_out<OutT>(__fdiv_rn(__fsub_rn(__ldg(ds_dense + r_cur * num_dense + j), __ldg(mean + j)),
-                                      __ldg(stdv + j)));
+    OutT* xr = x_out + b * ldx;
     // categorical ids: lane t holds the id of table tb + t
     for (int tb = 0; tb < num_cat; tb += 32) {
       const int t = tb + lane;
@@ -87,29 +83,40 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
       if (tb > 0) id = t < num_cat ? __ldg(ds_cat + r_cur * num_cat + t) : 0;
       if (t < num_cat) idx_out[b * num_cat + t] = (int32_t)id;
       const int tcount = min(32, num_cat - tb);
-      // gather: chunk i -> table tb + i / vec_per_row, float4 i % vec_per_row of that row
-      for (int i0 = 0; i0 < tcount * vec_per_row; i0 += 32) {
-        const int i = i0 + lane;
-        const int tt = i / vec_per_row;
-        const int qv = i - tt * vec_per_row;
-        const long long idt = __shfl_sync(0xffffffffu, id, tt < tcount ? tt : 0);
-        if (i < tcount * vec_per_row) {
-          const float* src = tables + ((long long)(tb + tt) * table_rows + idt) * embed_dim + qv * 4;
-          const uint4 raw = ldg_stream(src);
-          OutT* dst = xr + num_dense + (tb + tt) * embed_dim + qv * 4;
-          dst[0] = cvt_out<OutT>(__uint_as_float(raw.x));
-          dst[1] = cvt_out<OutT>(__uint_as_float(raw.y));
-          dst[2] = cvt_out<OutT>(__uint_as_float(raw.z));
-          dst[3] = cvt_out<OutT>(__uint_as_float(raw.w));
+      const int nvec = tcount * vec_per_row;
+      // gather: chunk i -> table tb + i / vec_per_row, float4 i % vec_per_row of that row -> row elements 4i..4i+3.
+      // Four independent 16-byte loads per lane are issued before the first store, so one L2/HBM latency is paid
+      // per 128 chunks (a whole T0 sample: 26 x 16 floats = 104 chunks) instead of one per 32.
+      for (int i0 = 0; i0 < nvec; i0 += 128) {
+        uint4 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 32 + lane;
+          const int tt = vpr_shift >= 0 ? (i >> vpr_shift) : (i / vec_per_row);
+          const int qv = i - tt * vec_per_row;
+          const long long idt = __shfl_sync(0xffffffffu, id, tt < tcount ? tt : 0);
+          if (i < nvec)
+            raw[u] = ldg_stream(tables + ((long long)(tb + tt) * table_rows + idt) * embed_dim + qv * 4);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 32 + lane;
+          if (i < nvec) store4(xr + (long long)tb * embed_dim + 4 * i, raw[u]);
         }
       }
     }
+    // dense columns (x - mean) / std in IEEE fp32, then the zero K-padding: one contiguous tail
+    {
+      const float v = lane < num_dense ? __fdiv_rn(__fsub_rn(dense_cur, mu), sd) : 0.f;
+      if (lane < tail) store1(xr + emb_cols + lane, v);
+      for (int e = 32 + lane; e < tail; e += 32) {  // > 32 tail columns: plain path
+        float w = 0.f;
+        if (e < num_dense)
+          w = __fdiv_rn(__fsub_rn(__ldg(ds_dense + r_cur * num_dense + e), __ldg(mean + e)), __ldg(stdv + e));
+        store1(xr + emb_cols + e, w);
+      }
+    }
     if (lane == 0) y_out[b] = label_cur;
-    __syncwarp();
-    // the finished row leaves with coalesced 16-byte stores (512 contiguous bytes per warp instruction)
-    uint8_t* orow = reinterpret_cast<uint8_t*>(x_out + b * ldx);
-    for (int c = lane; c < row_vecs; c += 32) stg_stream(orow + c * 16, ld_shared_v4(xr_s + c * 16));
-    __syncwarp();  // the row buffer is rewritten by the next sample
   }
 }
 
@@ -134,32 +141,25 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   B200_REQUIRE((ldx * es) % 16 == 0, "ldx*elemsize must be a multiple of 16 bytes");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(x_out) & 15) == 0 && (reinterpret_cast<uintptr_t>(tables) & 15) == 0,
                "x_out and tables must be 16-byte aligned");
-  const size_t row_bytes = (size_t)ldx * es;
-  const size_t smem = PRE_WARPS * row_bytes;  // one output row per warp
-  B200_REQUIRE(smem <= 200 * 1024, "row of %lld elements does not fit in shared memory", (long long)ldx);
+  const int vpr = embed_dim / 4;
+  int vpr_shift = -1;  // log2(float4 chunks per table row) when that is a power of two
+  if (vpr > 0 && (vpr & (vpr - 1)) == 0) {
+    vpr_shift = 0;
+    while ((1 << vpr_shift) < vpr) ++vpr_shift;
+  }
   long long blocks = (batch + PRE_WARPS - 1) / PRE_WARPS;
   const long long cap = (long long)sm_count() * 8;
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (x_dtype == B200_F32) {
-    static bool cfg = false;
-    if (!cfg) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(preprocess_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      cfg = true;
-    }
-    preprocess_kernel<float><<<grid, PRE_THREADS, smem, st>>>(
+    preprocess_kernel<float><<<grid, PRE_THREADS, 0, st>>>(
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables, static_cast<float*>(x_out), y_out,
-        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, ldx);
+        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx);
   } else {
-    static bool cfg = false;
-    if (!cfg) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(preprocess_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      cfg = true;
-    }
-    preprocess_kernel<__nv_bfloat16><<<grid, PRE_THREADS, smem, st>>>(
+    preprocess_kernel<__nv_bfloat16><<<grid, PRE_THREADS, 0, st>>>(
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables,
         static_cast<__nv_bfloat16*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,
-        embed_dim, ldx);
+        embed_dim, vpr_shift, ldx);
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -191,11 +191,12 @@ def test_preprocess_bit_exact(ops, dtype, batch, nd, nc, rows, dim, ldx):
     torch.cuda.synchronize()
     r = row_idx[batch: 2 * batch]
     ref = torch.zeros(batch, ldx, dtype=torch.float32, device="cuda")
-    ref[:, :nd] = dense[r].sub(mean).div(std)  # reference rule: tensor.sub_(mean).div_(std)
+    # row layout: [embeddings | standardised dense | zero pad]
+    ref[:, nc * dim: nc * dim + nd] = dense[r].sub(mean).div(std)  # reference rule: tensor.sub_(mean).div_(std)
     if nc:
         tv = tables.view(nc, rows, dim)
         emb = torch.stack([tv[t][cat[r, t]] for t in range(nc)], 1).reshape(batch, nc * dim)
-        ref[:, nd: nd + nc * dim] = emb
+        ref[:, : nc * dim] = emb
         assert torch.equal(idx[:, :nc].long(), cat[r])
     ref = ref.to(dtype)
     assert torch.equal(x.view(torch.int16 if dtype == torch.bfloat16 else torch.int32),
@@ -255,11 +256,12 @@ def test_emb_bwd(ops, dtype):
     dx = _rand((batch, ldx), dtype, 41, 0.01)
     idx = torch.randint(0, rows, (batch, nc), generator=torch.Generator().manual_seed(42)).int().cuda()
     dt = torch.zeros(nc * rows * dim, device="cuda")
-    ops.emb_bwd(dx, idx, dt, batch=batch, num_dense=nd, num_cat=nc, table_rows=rows, embed_dim=dim)
+    col0 = 16  # embedding columns may start at any multiple of 4 (0 in the training step)
+    ops.emb_bwd(dx, idx, dt, batch=batch, emb_col0=col0, num_cat=nc, table_rows=rows, embed_dim=dim)
     torch.cuda.synchronize()
     ref = torch.zeros(nc, rows, dim, dtype=torch.float64, device="cuda")
     for t in range(nc):
-        ref[t].index_add_(0, idx[:, t].long(), dx[:, nd + t * dim: nd + (t + 1) * dim].double())
+        ref[t].index_add_(0, idx[:, t].long(), dx[:, col0 + t * dim: col0 + (t + 1) * dim].double())
     # fp32 atomics in arbitrary order: |err| <= n_adds * eps * max|term|
     torch.testing.assert_close(dt.view(nc, rows, dim).double(), ref, rtol=1e-5, atol=1e-6)
 

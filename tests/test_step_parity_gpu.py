@@ -73,7 +73,9 @@ def test_preprocess_bit_exact_vs_oracle(precision):
     emb = [init[f"emb.{t}.weight"][ds.cat[r, t]] for t in range(spec.num_cat)]
     ref = torch.cat([dense_std] + emb, 1)
     ref = ref.to(eng.dt)
-    got = eng.x0[:, : spec.in_features].cpu()
+    # the step stores the row as [embeddings | dense | pad]; input_perm maps stored columns to the model's order
+    got = torch.empty_like(ref)
+    got[:, eng.layout.input_perm()] = eng.x0[:, : spec.in_features].cpu()
     view = torch.int16 if eng.dt == torch.bfloat16 else torch.int32
     assert torch.equal(got.view(view), ref.view(view))
     assert torch.count_nonzero(eng.x0[:, spec.in_features:]).item() == 0
