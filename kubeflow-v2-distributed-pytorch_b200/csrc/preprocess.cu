@@ -50,43 +50,53 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
   const float mu = lane < num_dense ? __ldg(mean + lane) : 0.f;  // num_dense <= 32 on the fast path
   const float sd = lane < num_dense ? __ldg(stdv + lane) : 1.f;
 
-  long long b = (long long)blockIdx.x * PRE_WARPS + warp;
-  // pipeline registers: stage A = sampler index, stage B = that row's dense value / first-32 categorical ids / label
-  long long r_b = b < batch ? __ldg(ridx + b) : 0;
-  long long r_a = b + stride < batch ? __ldg(ridx + b + stride) : 0;
+  const long long b_first = (long long)blockIdx.x * PRE_WARPS + warp;
+  // The sampler indices of this warp's next 32 samples are fetched with ONE load (lane l holds the index of the
+  // l-th upcoming sample) and handed out by shuffles; the dataset row of sample k+1 (its dense value, its first 32
+  // categorical ids, its label) is requested while sample k is being gathered.
+  long long b = b_first;
+  int k = 0;  // position inside the current group of 32 samples
+  long long rgrp = (b + (long long)lane * stride) < batch ? __ldg(ridx + b + (long long)lane * stride) : 0;
+  long long r_b = __shfl_sync(0xffffffffu, rgrp, 0);
   float dense_b = 0.f;
-  long long id_b = 0, label_b = 0;
+  int id_b = 0;
+  long long label_b = 0;
   if (b < batch) {
     if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
-    if (lane < num_cat) id_b = __ldg(ds_cat + r_b * num_cat + lane);
+    if (lane < num_cat) id_b = (int)__ldg(ds_cat + r_b * num_cat + lane);
     if (lane == 0) label_b = __ldg(ds_label + r_b);
   }
   for (; b < batch; b += stride) {
-    // start the next sample's stage B (its index arrived during the previous iteration) and stage A of the one after
     const long long bn = b + stride;
     const long long r_cur = r_b;
     const float dense_cur = dense_b;
-    const long long id_cur = id_b, label_cur = label_b;
-    r_b = r_a;
+    const int id_cur = id_b;
+    const long long label_cur = label_b;
+    if (++k == 32) {  // next group of sampler indices (warp-uniform branch)
+      k = 0;
+      rgrp = (bn + (long long)lane * stride) < batch ? __ldg(ridx + bn + (long long)lane * stride) : 0;
+    }
+    r_b = __shfl_sync(0xffffffffu, rgrp, k);
     if (bn < batch) {
       if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
-      if (lane < num_cat) id_b = __ldg(ds_cat + r_b * num_cat + lane);
+      if (lane < num_cat) id_b = (int)__ldg(ds_cat + r_b * num_cat + lane);
       if (lane == 0) label_b = __ldg(ds_label + r_b);
     }
-    r_a = bn + stride < batch ? __ldg(ridx + bn + stride) : 0;
 
     OutT* xr = x_out + b * ldx;
     // categorical ids: lane t holds the id of table tb + t
     for (int tb = 0; tb < num_cat; tb += 32) {
       const int t = tb + lane;
-      long long id = id_cur;
-      if (tb > 0) id = t < num_cat ? __ldg(ds_cat + r_cur * num_cat + t) : 0;
-      if (t < num_cat) idx_out[b * num_cat + t] = (int32_t)id;
+      int id = id_cur;
+      if (tb > 0) id = t < num_cat ? (int)__ldg(ds_cat + r_cur * num_cat + t) : 0;
+      if (t < num_cat) idx_out[b * num_cat + t] = id;
       const int tcount = min(32, num_cat - tb);
       const int nvec = tcount * vec_per_row;
+      OutT* xe = xr + tb * embed_dim;
       // gather: chunk i -> table tb + i / vec_per_row, float4 i % vec_per_row of that row -> row elements 4i..4i+3.
       // Four independent 16-byte loads per lane are issued before the first store, so one L2/HBM latency is paid
-      // per 128 chunks (a whole T0 sample: 26 x 16 floats = 104 chunks) instead of one per 32.
+      // per 128 chunks (a whole T0 sample: 26 x 16 floats = 104 chunks) instead of one per 32.  32-bit offsets:
+      // the host checks that the tables hold fewer than 2^31 elements.
       for (int i0 = 0; i0 < nvec; i0 += 128) {
         uint4 raw[4];
 #pragma unroll
@@ -94,14 +104,16 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
           const int i = i0 + u * 32 + lane;
           const int tt = vpr_shift >= 0 ? (i >> vpr_shift) : (i / vec_per_row);
           const int qv = i - tt * vec_per_row;
-          const long long idt = __shfl_sync(0xffffffffu, id, tt < tcount ? tt : 0);
-          if (i < nvec)
-            raw[u] = ldg_stream(tables + ((long long)(tb + tt) * table_rows + idt) * embed_dim + qv * 4);
+          const uint32_t idt = (uint32_t)__shfl_sync(0xffffffffu, id, tt & 31);
+          if (i < nvec) {
+            const uint32_t off = ((uint32_t)(tb + tt) * (uint32_t)table_rows + idt) * (uint32_t)embed_dim + qv * 4;
+            raw[u] = ldg_stream(tables + off);
+          }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int i = i0 + u * 32 + lane;
-          if (i < nvec) store4(xr + (long long)tb * embed_dim + 4 * i, raw[u]);
+          if (i < nvec) store4(xe + 4 * i, raw[u]);
         }
       }
     }
@@ -141,6 +153,8 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   B200_REQUIRE((ldx * es) % 16 == 0, "ldx*elemsize must be a multiple of 16 bytes");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(x_out) & 15) == 0 && (reinterpret_cast<uintptr_t>(tables) & 15) == 0,
                "x_out and tables must be 16-byte aligned");
+  B200_REQUIRE((int64_t)num_cat * table_rows * embed_dim < (1ll << 31),
+               "embedding tables hold 2^31 or more elements: 32-bit gather offsets would overflow");
   const int vpr = embed_dim / 4;
   int vpr_shift = -1;  // log2(float4 chunks per table row) when that is a power of two
   if (vpr > 0 && (vpr & (vpr - 1)) == 0) {
