@@ -31,8 +31,31 @@ void set_error(const char* fmt, ...);
   } while (0)
 
 int sm_count();  // cached per process (current device at first call)
+bool pdl_enabled();  // programmatic dependent launch (B200STEP_PDL=0 turns it off)
 // out[c] = sum_r partials[r * row_stride + c] for c < ncols, fixed order (defined in loss.cu)
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out, cudaStream_t st);
+
+// ---- kernel launch with programmatic dependent launch -------------------------------------------------
+// Every kernel of the step starts with pdl_launch_dependents() + pdl_wait(): the next kernel in the stream may be
+// scheduled (and run its prologue: barrier init, TMEM allocation, descriptor prefetch) while this one is still
+// draining, but touches global memory only after griddepcontrol.wait, i.e. after this grid has completed and
+// flushed.  That removes most of the launch latency between the ~15 dependent kernels of a step.
+template <typename Kern, typename... Args>
+inline cudaError_t launch_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<Args&&>(args)...);
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // ---- small device helpers -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

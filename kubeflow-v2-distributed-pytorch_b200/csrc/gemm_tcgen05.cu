@@ -107,6 +107,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int rank = kCtas == 2 ? (int)cluster_ctarank() : 0;   // 0 = leader of the pair
   const int unit = blockIdx.x / kCtas, nunits = gridDim.x / kCtas;
 
+  pdl_launch_dependents();  // the next kernel may start its own prologue
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -132,6 +133,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // barriers, TMEM and descriptors are set up; operands come from the previous kernel
 
   const int tiles = p.m_tiles * p.n_tiles;
   const int total = tiles * p.splits;
@@ -562,13 +564,15 @@ static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUt
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = GEMM_SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kCtas;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, p));
   return 0;
 }

@@ -45,11 +45,13 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
   const uint8_t* gin = reinterpret_cast<const uint8_t*>(logits_);
   uint8_t* gout = reinterpret_cast<uint8_t*>(dlogits_);
 
+  pdl_launch_dependents();
   if (threadIdx.x == 0) {
     for (int i = 0; i < CE_BUFS; ++i) mbar_init(&full_bar[i], 1);
     fence_mbar_init();
   }
   __syncthreads();
+  pdl_wait();  // the logits come from the previous kernel
 
   auto issue_load = [&](long long tile, int buf) {  // one thread
     const long long r0 = tile * TILE_ROWS;
@@ -218,6 +220,8 @@ constexpr int RED_THREADS = 256;
 __global__ void __launch_bounds__(RED_THREADS)
 reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
                        float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float part[RED_THREADS / 32][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = blockIdx.x * 32 + lane;
@@ -253,8 +257,8 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
 
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out,
                            cudaStream_t st) {
-  reduce_partials_kernel<<<(row_stride + 31) / 32, RED_THREADS, 0, st>>>(partials, nrows, row_stride, ncols, out, -1, 0.f,
-                                                                 nullptr);
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials, nrows, row_stride, ncols, out, -1, 0.f,
+                                                                 nullptr));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -269,6 +273,8 @@ template <bool kBf16>
 __global__ void __launch_bounds__(CS_THREADS)
 colsum_kernel(const void* __restrict__ dy_, long long ld, float* __restrict__ partials, long long M, int N,
               int rows_per_block, int panels) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int VEC = kBf16 ? 8 : 4;
   const int panel = blockIdx.x % panels;
   const int slab = blockIdx.x / panels;
@@ -365,21 +371,21 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
       B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
       cfg = true;
     }
-    ce_loss_grad_kernel<true><<<grid, CE_THREADS, smem, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                              num_classes, grad_scale, dbias != nullptr);
+    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<true>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels, dlogits, lddl, scratch, batch,
+                                                              num_classes, grad_scale, dbias != nullptr));
   } else {
     static bool cfg = false;
     if (!cfg) {
       B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
       cfg = true;
     }
-    ce_loss_grad_kernel<false><<<grid, CE_THREADS, smem, st>>>(logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                               num_classes, grad_scale, dbias != nullptr);
+    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<false>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels, dlogits, lddl, scratch, batch,
+                                                               num_classes, grad_scale, dbias != nullptr));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
-  reduce_partials_kernel<<<(stride + 31) / 32, RED_THREADS, 0, st>>>(scratch, grid, stride, num_classes, dbias,
-                                                             num_classes, 1.0f / (float)batch, loss_out);
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((stride + 31) / 32), dim3(RED_THREADS), 0, st, scratch, grid, stride, num_classes, dbias,
+                                                             num_classes, 1.0f / (float)batch, loss_out));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -403,11 +409,11 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   B200_REQUIRE(scratch != nullptr && scratch_floats >= (int64_t)slabs * N, "colsum scratch too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == B200_BF16)
-    colsum_kernel<true><<<slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+    B200_CHECK_CUDA(launch_pdl(colsum_kernel<true>, dim3(slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   else
-    colsum_kernel<false><<<slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+    B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3(slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  reduce_partials_kernel<<<(int)((N + 31) / 32), RED_THREADS, 0, st>>>(scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -465,11 +471,11 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   // every partial row that the second kernel reads is written by the first one in this same call, so nothing
   // in the shared array has to start at zero
   if (dtype == B200_BF16)
-    colsum_kernel<true><<<(int)slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+    B200_CHECK_CUDA(launch_pdl(colsum_kernel<true>, dim3((int)slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   else
-    colsum_kernel<false><<<(int)slabs * panels, CS_THREADS, 0, st>>>(dy, lddy, scratch, M, (int)N, rows_per_block, panels);
+    B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3((int)slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  reduce_partials_kernel<<<(int)((N + 31) / 32), RED_THREADS, 0, st>>>(scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr);
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

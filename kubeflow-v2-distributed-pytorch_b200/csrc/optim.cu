@@ -20,6 +20,8 @@ __device__ __forceinline__ void store_shadow4(void* shadow, long long i, float a
 __global__ void __launch_bounds__(OPT_THREADS)
 sgd_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ buf,
            void* __restrict__ shadow, long long n, long long n_shadow, float lr, float mu, float wd, int zero_grad) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long nv = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += stride) {
@@ -68,6 +70,8 @@ __global__ void __launch_bounds__(OPT_THREADS)
 adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             void* __restrict__ shadow, long long n, long long n_shadow, double lr, double b1, double b2, float eps,
             float wd, const int* __restrict__ step, int zero_grad) {
+  pdl_launch_dependents();
+  pdl_wait();
   // bias corrections in double like torch (python floats): 1 - beta**t, t = completed steps + 1
   const double t = (double)(*step) + 1.0;
   const float step_size = (float)(lr / (1.0 - pow(b1, t)));
@@ -102,6 +106,8 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
 
 __global__ void __launch_bounds__(OPT_THREADS)
 cast_bf16_kernel(const float* __restrict__ src, void* __restrict__ dst, long long n) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long nv = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nv; q += stride) {
@@ -113,6 +119,8 @@ cast_bf16_kernel(const float* __restrict__ src, void* __restrict__ dst, long lon
 }
 
 __global__ void advance_step_kernel(int* cursor, int* step, int steps_per_epoch) {
+  pdl_launch_dependents();
+  pdl_wait();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     if (cursor) {
       const int c = *cursor + 1;
@@ -132,6 +140,8 @@ __global__ void __launch_bounds__(OPT_THREADS)
 emb_bwd_kernel(const void* __restrict__ dx_, long long lddx, const int32_t* __restrict__ idx,
                float* __restrict__ dtables, long long batch, int emb_col0, int num_cat, long long table_rows,
                int embed_dim, int vpr_shift) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int vec_per_row = embed_dim >> 2;
   const int vec_per_sample = num_cat * vec_per_row;
   const long long total = batch * vec_per_sample;
@@ -177,8 +187,8 @@ extern "C" int b200_sgd_step(float* p, float* g, float* momentum_buf, void* shad
   B200_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
                  reinterpret_cast<uintptr_t>(momentum_buf)) & 15) == 0, "p/g/buf must be 16-byte aligned");
   if (!shadow_bf16) n_shadow = 0;
-  sgd_kernel<<<stream_grid(n / 4 + 1), OPT_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay, zero_grad);
+  B200_CHECK_CUDA(launch_pdl(sgd_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), 
+      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay, zero_grad));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -192,22 +202,22 @@ extern "C" int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg
   B200_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(exp_avg) |
                  reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0, "p/g/m/v must be 16-byte aligned");
   if (!shadow_bf16) n_shadow = 0;
-  adam_kernel<<<stream_grid(n / 4 + 1), OPT_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  B200_CHECK_CUDA(launch_pdl(adam_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), 
       p, g, exp_avg, exp_avg_sq, shadow_bf16, n, n_shadow, lr, beta1, beta2, (float)eps, (float)weight_decay, step,
-      zero_grad);
+      zero_grad));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_cast_bf16(const float* src, void* dst_bf16, int64_t n, b200_stream_t stream) {
   B200_REQUIRE(n > 0, "n must be positive");
-  cast_bf16_kernel<<<stream_grid(n / 4 + 1), OPT_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(src, dst_bf16, n);
+  B200_CHECK_CUDA(launch_pdl(cast_bf16_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), src, dst_bf16, n));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_advance_step(int32_t* cursor, int32_t* step, int32_t steps_per_epoch, b200_stream_t stream) {
-  advance_step_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(cursor, step, steps_per_epoch);
+  B200_CHECK_CUDA(launch_pdl(advance_step_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(stream), cursor, step, steps_per_epoch));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -230,11 +240,11 @@ extern "C" int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, fl
   const long long total = (long long)batch * num_cat * (embed_dim / 4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == B200_BF16)
-    emb_bwd_kernel<true><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, emb_col0,
-                                                                     num_cat, table_rows, embed_dim, vpr_shift);
+    B200_CHECK_CUDA(launch_pdl(emb_bwd_kernel<true>, dim3(stream_grid(total)), dim3(OPT_THREADS), 0, st, dx, lddx, idx, dtables, batch, emb_col0,
+                                                                     num_cat, table_rows, embed_dim, vpr_shift));
   else
-    emb_bwd_kernel<false><<<stream_grid(total), OPT_THREADS, 0, st>>>(dx, lddx, idx, dtables, batch, emb_col0,
-                                                                      num_cat, table_rows, embed_dim, vpr_shift);
+    B200_CHECK_CUDA(launch_pdl(emb_bwd_kernel<false>, dim3(stream_grid(total)), dim3(OPT_THREADS), 0, st, dx, lddx, idx, dtables, batch, emb_col0,
+                                                                      num_cat, table_rows, embed_dim, vpr_shift));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

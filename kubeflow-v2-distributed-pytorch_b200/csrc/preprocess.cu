@@ -40,6 +40,8 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
                   OutT* __restrict__ x_out, int64_t* __restrict__ y_out, int32_t* __restrict__ idx_out,
                   long long batch, int num_dense, int num_cat, long long table_rows, int embed_dim,
                   int vpr_shift, long long ldx) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long cur = cursor ? (long long)(*cursor) : 0;
   const int64_t* ridx = row_idx + cur * batch;
@@ -166,14 +168,14 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (x_dtype == B200_F32) {
-    preprocess_kernel<float><<<grid, PRE_THREADS, 0, st>>>(
+    B200_CHECK_CUDA(launch_pdl(preprocess_kernel<float>, dim3(grid), dim3(PRE_THREADS), 0, st, 
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables, static_cast<float*>(x_out), y_out,
-        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx);
+        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx));
   } else {
-    preprocess_kernel<__nv_bfloat16><<<grid, PRE_THREADS, 0, st>>>(
+    B200_CHECK_CUDA(launch_pdl(preprocess_kernel<__nv_bfloat16>, dim3(grid), dim3(PRE_THREADS), 0, st, 
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables,
         static_cast<__nv_bfloat16*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,
-        embed_dim, vpr_shift, ldx);
+        embed_dim, vpr_shift, ldx));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
