@@ -220,6 +220,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                      : make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t bd = kBMN ? make_smem_desc(sb + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT)
                                      : make_smem_desc(sb + k * 32, 16, 1024);
+            if (p.flags & 0x800) continue;  // timing experiment: stream the operands, skip the MMAs
             if constexpr (kCtas == 2) umma_ss_pair<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
             else umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
@@ -578,7 +579,7 @@ static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUt
 }
 
 // timing experiments only (results are wrong): bit 8 = do not issue the output TMA stores, bit 9 = skip the
-// epilogue math and staging, bit 10 = skip the ReLU bit-mask store
+// epilogue math and staging, bit 10 = skip the ReLU bit-mask store, bit 11 = skip the MMAs (operand streaming only)
 static int gemm_debug_flags() {
   static int v = -1;
   if (v < 0) v = getenv("B200STEP_GEMM_DEBUG") ? (atoi(getenv("B200STEP_GEMM_DEBUG")) << 8) : 0;
