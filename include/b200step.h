@@ -44,19 +44,23 @@ int b200_device_sm_count(int* out_host);     /* SM count of the current device *
  * x_out[b, num_cat*dim : num_cat*dim + num_dense]      = (dense[r] - mean) / std  (bit-exact fp32, RNE to bf16 if x_dtype=BF16)
  * x_out[b, num_cat*dim + num_dense : ldx]              = 0                        (K padding for the GEMMs)
  * y_out[b] = label[r];  idx_out[b,t] = (int32) cat[r,t]  (kept for the embedding backward)
- * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.
+ * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.  The batch is
+ * rows row_idx[*cursor * cursor_stride + b], b < batch; cursor_stride <= 0 means `batch` (a step may be processed
+ * in several row chunks: each call then gets row_idx advanced by its chunk offset and cursor_stride = full batch).
  */
 int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t* ds_label,
                     const int64_t* row_idx, const int32_t* cursor,
                     const float* mean, const float* std, const float* tables,
                     void* x_out, int64_t* y_out, int32_t* idx_out,
                     int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
-                    int64_t ldx, int x_dtype, b200_stream_t stream);
+                    int64_t ldx, int x_dtype, int64_t cursor_stride, b200_stream_t stream);
 
 /* ---- K-gemm: tcgen05/TMEM linear layers ----------------------------------------------------
  * M = batch rows, N = out_features, K = in_features for all three.
  * fwd   (task.py:309, nn.Linear inside model(inputs)):  y[M,N] = act(x[M,K] · w[N,K]^T + bias[N])
- *        with optional inverted dropout after the activation: keep iff philox(seed,*step,layer,elem) >= p.
+ *        with optional inverted dropout after the activation: keep iff philox(seed,*step,layer,elem) >= p, where
+ *        elem = (dropout_row0 + m) * N + n (dropout_row0 = index of x's first row inside the whole batch when a
+ *        batch is processed in row chunks).
  * dgrad (task.py:311 loss.backward, addmm backward wrt input):
  *        dx[M,K] = (dy[M,N] · w[N,K]) * (act[M,K] > 0 if RELU) * dscale     (act = the stored layer input)
  *        relu_mask (nullable, either side): 1 bit per element, word [row, col/32], row stride ldmask words; the
@@ -71,7 +75,7 @@ int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t*
 int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
                     void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
                     float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
-                    uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream);
+                    int64_t dropout_row0, uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream);
 int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw,
                       const void* act, int64_t ldact, void* dx, int64_t lddx,
                       int64_t M, int64_t N, int64_t K, int dtype, int flags, float dscale,
@@ -89,13 +93,15 @@ int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx,
  * dlogits[b,c] = (softmax(z_b)[c] - [c==y_b]) * grad_scale   (grad_scale = 1/(batch*world): DDP's mean, task.py:189)
  * dbias (nullable) [C] = sum_b dlogits[b,:] as stored (after rounding to dtype), fp32.
  * scratch: b200_ce_scratch_floats(C) floats of device memory, contents need not be initialised.
+ * loss_scale <= 0 means 1/batch; accumulate != 0 adds loss and dbias onto the existing values (a batch processed in
+ * row chunks: grad_scale = 1/(full batch * world), loss_scale = 1/full batch, accumulate on every chunk but the first).
  */
 int64_t b200_ce_scratch_floats(int num_classes);
 int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels,
                       void* dlogits, int64_t lddl, float* loss_out, float* dbias,
                       float* scratch, int64_t scratch_floats,
-                      int64_t batch, int num_classes, float grad_scale, int dtype,
-                      b200_stream_t stream);
+                      int64_t batch, int num_classes, float grad_scale, float loss_scale, int accumulate,
+                      int dtype, b200_stream_t stream);
 
 /* ---- column sum: bias gradients of the hidden layers (task.py:311, addmm backward wrt bias) -
  * out[N] = sum_m dy[m, :]  (fp32, deterministic two-stage reduction through scratch) */

@@ -42,20 +42,21 @@ def _cuda(*ts):
 
 
 def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x_out, y_out, idx_out, *,
-               batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, stream=None):
+               batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, cursor_stride: int = 0,
+               stream=None):
     _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out)
     get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
                          ptr(std), ptr(tables), ptr(x_out), ptr(y_out), ptr(idx_out), batch, num_dense,
                          num_cat, table_rows, embed_dim, x_out.stride(0), dtype_code(x_out.dtype),
-                         _stream(stream))
+                         cursor_stride, _stream(stream))
 
 
 def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,
-               step=None, layer_id: int = 0, relu_mask=None, stream=None):
+               step=None, layer_id: int = 0, row0: int = 0, relu_mask=None, stream=None):
     _cuda(x, w, bias, y, relu_mask)
     get_lib().linear_fwd(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(y), y.stride(0), M, N, K,
                          dtype_code(x.dtype), FLAG_RELU if relu else 0, float(dropout_p), int(seed),
-                         ptr(step), layer_id, ptr(relu_mask),
+                         ptr(step), layer_id, int(row0), ptr(relu_mask),
                          relu_mask.stride(0) if relu_mask is not None else 0, _stream(stream))
 
 
@@ -84,11 +85,12 @@ def ce_scratch_floats(num_classes: int) -> int:
 
 
 def ce_loss_grad(logits, labels, dlogits, loss_out, dbias, scratch, *, batch: int, num_classes: int,
-                 grad_scale: float, stream=None):
+                 grad_scale: float, loss_scale: float = 0.0, accumulate: bool = False, stream=None):
     _cuda(logits, labels, dlogits, loss_out, dbias, scratch)
     get_lib().ce_loss_grad(ptr(logits), logits.stride(0), ptr(labels), ptr(dlogits), dlogits.stride(0),
                            ptr(loss_out), ptr(dbias), ptr(scratch), scratch.numel(), batch, num_classes,
-                           float(grad_scale), dtype_code(logits.dtype), _stream(stream))
+                           float(grad_scale), float(loss_scale), int(accumulate), dtype_code(logits.dtype),
+                           _stream(stream))
 
 
 def colsum_scratch_floats(n: int) -> int:
@@ -130,6 +132,14 @@ def cast_bf16(src, dst, stream=None):
 def advance_step(cursor, step, steps_per_epoch: int, stream=None):
     _cuda(cursor, step)
     get_lib().advance_step(ptr(cursor), ptr(step), steps_per_epoch, _stream(stream))
+
+
+def sm_count() -> int:
+    import ctypes as C
+
+    n = C.c_int(0)
+    get_lib().device_sm_count(C.byref(n))
+    return int(n.value)
 
 
 def zero(t, stream=None):

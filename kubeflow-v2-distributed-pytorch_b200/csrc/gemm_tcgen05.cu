@@ -50,6 +50,7 @@ struct GemmParams {
   unsigned long long seed;
   const int* step;
   int layer_id;
+  long long row0;            // fwd dropout: row index of this call's first row inside the whole batch
 };
 
 // ---- UMMA descriptors (bit layout: PTX ISA "tcgen05 matrix/instruction descriptor") ------------
@@ -337,7 +338,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32) ^ stepv);
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
-                  const unsigned long long e = (unsigned long long)row * (unsigned long long)p.N + (col0 + j);
+                  const unsigned long long e = (unsigned long long)(row + p.row0) * (unsigned long long)p.N + (col0 + j);
                   const uint4 r = philox4x32_10(
                       make_uint4((uint32_t)(e >> 2), (uint32_t)(e >> 34), (uint32_t)p.layer_id, 0u), key);
                   f[j + 0] = (r.x >= thresh) ? f[j + 0] * inv_keep : 0.0f;
@@ -614,7 +615,7 @@ using namespace b200;
 extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
                                void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int dtype, int flags,
                                float dropout_p, uint64_t seed, const int32_t* step, int layer_id,
-                               uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream) {
+                               int64_t dropout_row0, uint32_t* relu_mask, int64_t ldmask, b200_stream_t stream) {
   if (int r = check_dims(M, N, K, dtype)) return r;
   B200_REQUIRE(relu_mask == nullptr || (ldmask * 32 >= N && ldmask % 4 == 0 &&
                                         (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
@@ -637,7 +638,7 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f;
   p.dropout_p = dropout_p; p.seed = seed; p.step = step; p.layer_id = layer_id;
-  p.mask_out = relu_mask; p.ldmask = ldmask;
+  p.mask_out = relu_mask; p.ldmask = ldmask; p.row0 = dropout_row0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, tc, p, st)
               : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);

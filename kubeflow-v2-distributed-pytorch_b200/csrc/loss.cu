@@ -213,13 +213,14 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
   }
 }
 
-// out[c] = sum over partial rows in a fixed order; column `loss_col` (if >= 0) is scaled and written to loss_out.
+// out[c] (+)= sum over partial rows in a fixed order; column `loss_col` (if >= 0) is scaled and written/added to loss_out.
 // One CTA per 32 columns: warp w walks rows w, w+8, ... (128 contiguous bytes per warp and row, four
 // independent loads in flight), then the 8 per-warp sums are combined in a fixed order -> deterministic.
 constexpr int RED_THREADS = 256;
 __global__ void __launch_bounds__(RED_THREADS)
 reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
-                       float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out) {
+                       float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out,
+                       int accumulate) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float part[RED_THREADS / 32][33];
@@ -248,9 +249,9 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
 #pragma unroll
     for (int w = 0; w < RED_THREADS / 32; ++w) s += part[w][lane];
     if (is_loss) {
-      if (loss_out) loss_out[0] = s * loss_scale;
+      if (loss_out) loss_out[0] = (accumulate ? loss_out[0] : 0.f) + s * loss_scale;
     } else {
-      out[c] = s;
+      out[c] = (accumulate ? out[c] : 0.f) + s;
     }
   }
 }
@@ -258,7 +259,7 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out,
                            cudaStream_t st) {
   B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials, nrows, row_stride, ncols, out, -1, 0.f,
-                                                                 nullptr));
+                                                                 nullptr, 0));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -346,7 +347,7 @@ extern "C" int64_t b200_ce_scratch_floats(int num_classes) {
 extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels, void* dlogits,
                                  int64_t lddl, float* loss_out, float* dbias, float* scratch,
                                  int64_t scratch_floats, int64_t batch, int num_classes, float grad_scale,
-                                 int dtype, b200_stream_t stream) {
+                                 float loss_scale, int accumulate, int dtype, b200_stream_t stream) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   const int vec = dtype == B200_F32 ? 4 : 8;
   B200_REQUIRE(num_classes > 0 && num_classes <= CE_MAX_CLASSES && num_classes % vec == 0,
@@ -385,7 +386,7 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
   B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((stride + 31) / 32), dim3(RED_THREADS), 0, st, scratch, grid, stride, num_classes, dbias,
-                                                             num_classes, 1.0f / (float)batch, loss_out));
+                                                             num_classes, loss_scale > 0.f ? loss_scale : 1.0f / (float)batch, loss_out, accumulate));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -413,7 +414,7 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3(slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr, 0));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -475,7 +476,7 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3((int)slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr, 0));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

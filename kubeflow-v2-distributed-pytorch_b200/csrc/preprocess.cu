@@ -39,12 +39,12 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
                   const float* __restrict__ stdv, const float* __restrict__ tables,
                   OutT* __restrict__ x_out, int64_t* __restrict__ y_out, int32_t* __restrict__ idx_out,
                   long long batch, int num_dense, int num_cat, long long table_rows, int embed_dim,
-                  int vpr_shift, long long ldx) {
+                  int vpr_shift, long long ldx, long long cursor_stride) {
   pdl_launch_dependents();
   pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long cur = cursor ? (long long)(*cursor) : 0;
-  const int64_t* ridx = row_idx + cur * batch;
+  const int64_t* ridx = row_idx + cur * cursor_stride;
   const int vec_per_row = embed_dim >> 2;        // float4 chunks per table row
   const int emb_cols = num_cat * embed_dim;      // dense columns start here
   const int tail = (int)ldx - emb_cols;          // dense + zero padding
@@ -143,7 +143,8 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
                                const float* stdv, const float* tables, void* x_out, int64_t* y_out,
                                int32_t* idx_out, int64_t batch, int num_dense, int num_cat,
                                int64_t table_rows, int embed_dim, int64_t ldx, int x_dtype,
-                               b200_stream_t stream) {
+                               int64_t cursor_stride, b200_stream_t stream) {
+  if (cursor_stride <= 0) cursor_stride = batch;
   B200_REQUIRE(x_dtype == B200_F32 || x_dtype == B200_BF16, "unknown dtype code %d", x_dtype);
   B200_REQUIRE(batch > 0, "batch must be positive");
   B200_REQUIRE(num_dense >= 0 && num_cat >= 0 && embed_dim >= 0, "negative feature counts");
@@ -170,12 +171,12 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   if (x_dtype == B200_F32) {
     B200_CHECK_CUDA(launch_pdl(preprocess_kernel<float>, dim3(grid), dim3(PRE_THREADS), 0, st, 
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables, static_cast<float*>(x_out), y_out,
-        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx));
+        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx, (long long)cursor_stride));
   } else {
     B200_CHECK_CUDA(launch_pdl(preprocess_kernel<__nv_bfloat16>, dim3(grid), dim3(PRE_THREADS), 0, st, 
         ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables,
         static_cast<__nv_bfloat16*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,
-        embed_dim, vpr_shift, ldx));
+        embed_dim, vpr_shift, ldx, (long long)cursor_stride));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -21,5 +21,7 @@ def run(steps=200, **kw):
         out.append(e0.elapsed_time(e1) / steps)
     eng.close()
     return out
-for name, kw in [("atomic dbias", {}), ("deterministic dbias", {"deterministic_bias_grad": True}), ("atomic dbias again", {})]:
-    print(name, ["%.4f" % x for x in run(**kw)])
+import json
+variants = json.loads(os.environ.get("AB_VARIANTS", '[["default", {}]]'))
+for name, kw in variants:
+    print(name, ["%.4f" % x for x in run(steps=int(os.environ.get("AB_STEPS", "50")), **kw)], flush=True)

@@ -29,12 +29,13 @@ def _spec_dict(spec):
 SMALL = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=50, hidden=(64, 32), num_classes=40)
 
 
-def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True):
+def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True,
+              micro_rows=0):
     ds = make_synthetic(rows, spec)
     oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, seed=seed, optimizer=optimizer,
                            precision=precision, lr=lr)
     cfg = StepConfig(batch_size=batch, precision=precision, optimizer=optimizer, lr=lr, use_graph=use_graph,
-                     keep_logits=True)
+                     keep_logits=True, micro_rows=micro_rows)
     eng = TrainStep(spec, init_parameters(spec, seed), ds, rank_indices(rows, 1, 0), cfg)
     o_losses, g_losses = [], []
     for _ in range(steps):
@@ -106,6 +107,17 @@ def test_t0_batch4096(precision):
     for a, b in zip(lo, lg):
         assert abs(a - b) <= 2e-3 * max(1.0, abs(a)), (lo, lg)
     assert _param_err(oracle, eng) <= 5e-3
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_row_chunked_step_matches_oracle(precision):
+    """A step processed in row chunks (3 chunks of 96 + 64 rows): loss and gradients accumulate across chunks,
+    the dropout mask is indexed by the row inside the whole batch."""
+    spec = dataclasses.replace(SMALL, dropout=0.25)
+    ds, oracle, eng, lo, lg = _run_pair(spec, rows=1024, batch=256, steps=8, precision=precision, micro_rows=96)
+    for a, b in zip(lo, lg):
+        assert abs(a - b) <= 5e-3 * max(1.0, abs(a)), (lo, lg)
+    assert _param_err(oracle, eng) <= 2e-2
 
 
 def test_graph_replay_equals_eager():
