@@ -256,9 +256,8 @@ def run_b200(args, rank, local_rank, world):
         t = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    raw_bytes = 4 * spec.num_dense + 8 * spec.num_cat + 8
     e2e = {"value": world * B * e2e_steps / (e2e_ms / 1e3), "unit": "samples/s",
-           "h2d_bytes_per_step": B * raw_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps}
+           "h2d_bytes_per_step": int(host[0].numel()), "d2h_bytes_per_step": 4, "steps": e2e_steps}
 
     # ---- per-kernel timing of one eager step (CUDA events around each launch) -> roofline --------------------
     prof = profile_kernels(eng, spec, B, world)

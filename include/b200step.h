@@ -44,11 +44,13 @@ int b200_device_sm_count(int* out_host);     /* SM count of the current device *
  * x_out[b, num_cat*dim : num_cat*dim + num_dense]      = (dense[r] - mean) / std  (bit-exact fp32, RNE to bf16 if x_dtype=BF16)
  * x_out[b, num_cat*dim + num_dense : ldx]              = 0                        (K padding for the GEMMs)
  * y_out[b] = label[r];  idx_out[b,t] = (int32) cat[r,t]  (kept for the embedding backward)
+ * ds_cat holds int64 ids (cat_id_bytes = 8, torch's index dtype) or int32 ids (cat_id_bytes = 4, the narrowed form
+ * the host-fed path sends over PCIe).
  * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.  The batch is
  * rows row_idx[*cursor * cursor_stride + b], b < batch; cursor_stride <= 0 means `batch` (a step may be processed
  * in several row chunks: each call then gets row_idx advanced by its chunk offset and cursor_stride = full batch).
  */
-int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t* ds_label,
+int b200_preprocess(const float* ds_dense, const void* ds_cat, int cat_id_bytes, const int64_t* ds_label,
                     const int64_t* row_idx, const int32_t* cursor,
                     const float* mean, const float* std, const float* tables,
                     void* x_out, int64_t* y_out, int32_t* idx_out,

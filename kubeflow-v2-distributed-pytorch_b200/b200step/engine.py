@@ -375,29 +375,33 @@ class TrainStep:
 
     HOST_STAGES = 3  # staging buffers of the host-fed path: the host can run two steps ahead of the GPU
 
+    HOST_ID_BYTES = 4   # categorical ids cross PCIe as int32 (lossless: cardinality < 2^31), 39 % fewer bytes per batch
+
     def host_batch_bytes(self, rows: int) -> int:
         spec = self.spec
-        return rows * (4 * spec.num_dense + 8 * spec.num_cat + 8)
+        return rows * (4 * spec.num_dense + self.HOST_ID_BYTES * spec.num_cat + 8)
 
     def pack_host_batch(self, dense: torch.Tensor, cat: torch.Tensor, label: torch.Tensor) -> torch.Tensor:
-        """Lay one raw batch out as ONE pinned host buffer [dense fp32 | cat int64 | label int64] so that it crosses
-        PCIe in a single cudaMemcpyAsync (what a data-loader thread would hand to the training loop)."""
+        """Lay one raw batch out as ONE pinned host buffer [label int64 | dense fp32 | cat int32] so that it crosses
+        PCIe in a single cudaMemcpyAsync (what a data-loader thread would hand to the training loop).  The ids are
+        narrowed from torch's int64 to int32 on the way (lossless)."""
         B = dense.shape[0]
         buf = torch.empty(self.host_batch_bytes(B), dtype=torch.uint8).pin_memory()
-        o1 = 4 * self.spec.num_dense * B
-        o2 = o1 + 8 * self.spec.num_cat * B
-        buf[:o1].view(torch.float32).view(B, -1).copy_(dense)
+        o1 = 8 * B
+        o2 = o1 + 4 * self.spec.num_dense * B
+        buf[:o1].view(torch.int64).copy_(label)
+        buf[o1:o2].view(torch.float32).view(B, -1).copy_(dense)
         if self.spec.num_cat:
-            buf[o1:o2].view(torch.int64).view(B, -1).copy_(cat)
-        buf[o2:].view(torch.int64).copy_(label)
+            buf[o2:].view(torch.int32).view(B, -1).copy_(cat)
         return buf
 
     def _stage_views(self, raw: torch.Tensor, B: int) -> TabularDataset:
-        o1 = 4 * self.spec.num_dense * B
-        o2 = o1 + 8 * self.spec.num_cat * B
-        return TabularDataset(raw[:o1].view(torch.float32).view(B, self.spec.num_dense),
-                              raw[o1:o2].view(torch.int64).view(B, self.spec.num_cat),
-                              raw[o2: o2 + 8 * B].view(torch.int64), self.ds.mean, self.ds.std)
+        o1 = 8 * B
+        o2 = o1 + 4 * self.spec.num_dense * B
+        o3 = o2 + self.HOST_ID_BYTES * self.spec.num_cat * B
+        return TabularDataset(raw[o1:o2].view(torch.float32).view(B, self.spec.num_dense),
+                              raw[o2:o3].view(torch.int32).view(B, self.spec.num_cat),
+                              raw[:o1].view(torch.int64), self.ds.mean, self.ds.std)
 
     def _init_host_path(self) -> None:
         bs, dev, n = self.cfg.batch_size, self.dev, self.HOST_STAGES

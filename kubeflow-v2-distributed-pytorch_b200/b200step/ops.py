@@ -45,7 +45,8 @@ def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x
                batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, cursor_stride: int = 0,
                stream=None):
     _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out)
-    get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
+    get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ds_cat.element_size() if ds_cat is not None else 8,
+                         ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
                          ptr(std), ptr(tables), ptr(x_out), ptr(y_out), ptr(idx_out), batch, num_dense,
                          num_cat, table_rows, embed_dim, x_out.stride(0), dtype_code(x_out.dtype),
                          cursor_stride, _stream(stream))

@@ -31,9 +31,9 @@ __device__ __forceinline__ void store4(__nv_bfloat16* dst, uint4 raw) {
 __device__ __forceinline__ void store1(float* dst, float v) { *dst = v; }
 __device__ __forceinline__ void store1(__nv_bfloat16* dst, float v) { *dst = __float2bfloat16_rn(v); }
 
-template <typename OutT>
+template <typename OutT, typename IdT>
 __global__ void __launch_bounds__(PRE_THREADS, 4)
-preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict__ ds_cat,
+preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds_cat,
                   const int64_t* __restrict__ ds_label, const int64_t* __restrict__ row_idx,
                   const int32_t* __restrict__ cursor, const float* __restrict__ mean,
                   const float* __restrict__ stdv, const float* __restrict__ tables,
@@ -138,7 +138,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const int64_t* __restrict_
 
 using namespace b200;
 
-extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, const int64_t* ds_label,
+extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int cat_id_bytes, const int64_t* ds_label,
                                const int64_t* row_idx, const int32_t* cursor, const float* mean,
                                const float* stdv, const float* tables, void* x_out, int64_t* y_out,
                                int32_t* idx_out, int64_t batch, int num_dense, int num_cat,
@@ -168,16 +168,21 @@ extern "C" int b200_preprocess(const float* ds_dense, const int64_t* ds_cat, con
   const long long cap = (long long)sm_count() * 8;
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  B200_REQUIRE(cat_id_bytes == 8 || cat_id_bytes == 4, "categorical ids must be int64 or int32 (cat_id_bytes=%d)",
+               cat_id_bytes);
+#define B200_PRE_LAUNCH(OUT_T, ID_T)                                                                              \
+  B200_CHECK_CUDA(launch_pdl(preprocess_kernel<OUT_T, ID_T>, dim3(grid), dim3(PRE_THREADS), 0, st, ds_dense,     \
+                             static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor, mean, stdv, tables,    \
+                             static_cast<OUT_T*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,  \
+                             embed_dim, vpr_shift, ldx, (long long)cursor_stride))
   if (x_dtype == B200_F32) {
-    B200_CHECK_CUDA(launch_pdl(preprocess_kernel<float>, dim3(grid), dim3(PRE_THREADS), 0, st, 
-        ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables, static_cast<float*>(x_out), y_out,
-        idx_out, batch, num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx, (long long)cursor_stride));
+    if (cat_id_bytes == 8) B200_PRE_LAUNCH(float, int64_t);
+    else B200_PRE_LAUNCH(float, int32_t);
   } else {
-    B200_CHECK_CUDA(launch_pdl(preprocess_kernel<__nv_bfloat16>, dim3(grid), dim3(PRE_THREADS), 0, st, 
-        ds_dense, ds_cat, ds_label, row_idx, cursor, mean, stdv, tables,
-        static_cast<__nv_bfloat16*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,
-        embed_dim, vpr_shift, ldx, (long long)cursor_stride));
+    if (cat_id_bytes == 8) B200_PRE_LAUNCH(__nv_bfloat16, int64_t);
+    else B200_PRE_LAUNCH(__nv_bfloat16, int32_t);
   }
+#undef B200_PRE_LAUNCH
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
