@@ -83,6 +83,12 @@ int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw,
                       int64_t M, int64_t N, int64_t K, int dtype, int flags, float dscale,
                       const uint32_t* relu_mask, int64_t ldmask,
                       float* dbias, float* scratch, int64_t scratch_floats, b200_stream_t stream);
+/* wgrad of `count` (<= 8) layers that share the batch dimension M, in ONE launch: dw[j] += dy[j]^T . x[j].  All
+ * arrays are HOST arrays of length count.  Results are accumulated with red.add: every dw[j] must hold zeros (or the
+ * value to add onto).  One launch instead of `count`, and the epilogue of one work unit overlaps the MMAs of the next. */
+int b200_linear_wgrad_grouped(int count, const void* const* dy, const int64_t* lddy, const void* const* x,
+                              const int64_t* ldx, float* const* dw, const int64_t* lddw, int64_t M,
+                              const int64_t* N, const int64_t* K, int dtype, b200_stream_t stream);
 /* scratch floats b200_linear_dgrad needs when dbias != NULL */
 int64_t b200_dgrad_scratch_floats(int64_t M, int64_t K);
 int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx,

@@ -50,6 +50,8 @@ class StepConfig:
     keep_logits: bool = False            # keep logits and dlogits in separate buffers (tests)
     deterministic_bias_grad: bool = False  # hidden-layer bias grads through a fixed-order reduction instead of atomics
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
+    grouped_wgrad: bool = False          # all layers' wgrad GEMMs in one launch (measured equal on T0; per-layer
+                                         # launches let each bucket's all-reduce start earlier when world > 1)
 
 
 class Communicator:
@@ -278,15 +280,29 @@ class TrainStep:
                 n += 2
                 if last_chunk and -1 in bucket_of:
                     n += self._reduce_bucket(bucket_of[-1])
-            for li in range(L - 1, -1, -1):
-                k, o = dims[li]
-                kk = self.k0 if li == 0 else k
-                x_in = self.x0[sl] if li == 0 else self.acts[li - 1][sl]
-                # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
-                ops.linear_wgrad(dys[li], x_in, self._gw(li), M=rows, N=o, K=kk, accumulate=True, stream=st)
+            grouped = bool(cfg.grouped_wgrad)
+            xs = [self.x0[sl] if li == 0 else self.acts[li - 1][sl] for li in range(L)]
+            # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
+            if grouped:
+                # one launch for every layer's weight gradient (largest layer first)
+                order = list(range(L - 1, -1, -1))
+                ops.linear_wgrad_grouped([dys[li] for li in order], [xs[li] for li in order],
+                                         [self._gw(li) for li in order], M=rows,
+                                         Ns=[dims[li][1] for li in order],
+                                         Ks=[self.k0 if li == 0 else dims[li][0] for li in order], stream=st)
                 n += 1
-                if last_chunk and li in bucket_of:
-                    n += self._reduce_bucket(bucket_of[li])
+                if last_chunk:
+                    for li in order:
+                        if li in bucket_of:
+                            n += self._reduce_bucket(bucket_of[li])
+            else:
+                for li in range(L - 1, -1, -1):
+                    k, o = dims[li]
+                    kk = self.k0 if li == 0 else k
+                    ops.linear_wgrad(dys[li], xs[li], self._gw(li), M=rows, N=o, K=kk, accumulate=True, stream=st)
+                    n += 1
+                    if last_chunk and li in bucket_of:
+                        n += self._reduce_bucket(bucket_of[li])
         # optimizer ----------------------------------------------------------------------------------------
         # world > 1: one launch per bucket, each gated only by that bucket's all-reduce, so the update of the early
         # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer.

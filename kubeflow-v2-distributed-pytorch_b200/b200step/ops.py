@@ -81,6 +81,19 @@ def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False,
                            dtype_code(dy.dtype), FLAG_ACCUMULATE if accumulate else 0, _stream(stream))
 
 
+def linear_wgrad_grouped(dys, xs, dws, *, M: int, Ns, Ks, stream=None):
+    """dws[j] += dys[j]^T @ xs[j] for all j in one launch (outputs must be zeroed / hold the value to add onto)."""
+    import ctypes as C
+
+    n = len(dys)
+    _cuda(*dys, *xs, *dws)
+    vp = lambda ts: (C.c_void_p * n)(*[t.data_ptr() for t in ts])
+    i64 = lambda vs: (C.c_int64 * n)(*[int(v) for v in vs])
+    get_lib().linear_wgrad_grouped(n, vp(dys), i64([t.stride(0) for t in dys]), vp(xs),
+                                   i64([t.stride(0) for t in xs]), vp(dws), i64([t.stride(0) for t in dws]), M,
+                                   i64(Ns), i64(Ks), dtype_code(dys[0].dtype), _stream(stream))
+
+
 def ce_scratch_floats(num_classes: int) -> int:
     return int(get_lib().ce_scratch_floats(num_classes))
 

@@ -485,6 +485,199 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
+// ---- grouped wgrad: the weight gradients of ALL layers in one launch -----------------------------------------
+// The per-layer wgrad launches each give a CTA pair exactly one work unit (one output tile x one slice of the
+// batch), so prologue, pipeline fill, the red.add epilogue and the ~6 us fixed cost of a launch are paid per
+// layer and nothing overlaps them.  Here the units of every layer form one list; a pair walks its share of it
+// (unit, unit + npairs, ...), so the epilogue of one unit drains under the MMAs of the next and there is one
+// launch for the whole wgrad phase.  Same tiles, same pipeline, same epilogue as gemm_kernel<MN, MN, WGRAD, 2>.
+constexpr int WG_MAX_PROBLEMS = 8;
+
+struct WgradProblem {
+  int M, N;             // dW is M x N (= out_features x in_features)
+  int k_blocks;         // ceil(batch / BLOCK_K)
+  int m_tiles, n_tiles, splits, kb_per_split;
+  int unit_begin;       // first unit of this problem in the global unit list
+  float* out;
+  long long ldo;
+};
+
+struct WgradGroup {
+  CUtensorMap tmA[WG_MAX_PROBLEMS];  // dY^T (MN-major)
+  CUtensorMap tmB[WG_MAX_PROBLEMS];  // X^T  (MN-major)
+  WgradProblem prob[WG_MAX_PROBLEMS];
+  int count;
+  int total_units;
+};
+
+template <int kTf32>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+wgrad_grouped_kernel(const __grid_constant__ WgradGroup g) {
+  constexpr int ESIZE = kTf32 ? 4 : 2;
+  constexpr int BLOCK_K = 128 / ESIZE;
+  constexpr int UMMA_K = 32 / ESIZE;
+  constexpr int EPR = 128 / ESIZE;
+  constexpr int MN_BOX_BYTES = BLOCK_K * 128;
+  constexpr uint32_t MN_SBO = kTf32 ? 512 : 1024;
+  constexpr uint32_t MN_LAYOUT = kTf32 ? 1 : 2;
+  constexpr uint32_t IDESC = make_idesc(kTf32 ? 2 : 1, 1, 1, BLOCK_M * 2, BLOCK_N);
+  constexpr int B_ROWS = BLOCK_N / 2;
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_ROWS * 128;
+  constexpr int NUM_STAGES = PIPE_BYTES / STAGE_BYTES;
+  constexpr int TILE_M = BLOCK_M * 2;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + PIPE_BYTES + EPI_STAGING_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + NUM_STAGES;
+  uint64_t* acc_full = bars + 2 * NUM_STAGES;
+  uint64_t* acc_empty = acc_full + NUM_ACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + NUM_ACC);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  const int unit0 = blockIdx.x / 2, nunits = gridDim.x / 2;
+
+  pdl_launch_dependents();
+  if (warp == 0 && lane == 0) {
+    for (int j = 0; j < g.count; ++j) {
+      tma_prefetch_desc(&g.tmA[j]);
+      tma_prefetch_desc(&g.tmB[j]);
+    }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < NUM_STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < NUM_ACC; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], EPI_WARPS * 2);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_pair(tmem_slot, NUM_ACC * BLOCK_N);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  // unit -> (problem, tile, split): problems are few, a linear scan is cheapest
+  auto locate = [&](int w, int& j, int& m0, int& n0, int& kb0, int& kb1) {
+    j = 0;
+    while (j + 1 < g.count && w >= g.prob[j + 1].unit_begin) ++j;
+    const WgradProblem& q = g.prob[j];
+    const int lw = w - q.unit_begin;
+    const int tiles = q.m_tiles * q.n_tiles;
+    const int tile = lw % tiles, split = lw / tiles;
+    m0 = (tile / q.n_tiles) * TILE_M;
+    n0 = (tile % q.n_tiles) * BLOCK_N;
+    kb0 = split * q.kb_per_split;
+    kb1 = min(kb0 + q.kb_per_split, q.k_blocks);
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {  // ---- TMA producer
+      int s = 0;
+      uint32_t ph = 0;
+      for (int w = unit0; w < g.total_units; w += nunits) {
+        int j, m0, n0, kb0, kb1;
+        locate(w, j, m0, n0, kb0, kb1);
+        m0 += rank * BLOCK_M;
+        n0 += rank * B_ROWS;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_TILE_BYTES;
+          if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+          const uint32_t fb = smem_u32(&full_bar[s]) & 0xFEFFFFFFu;
+#pragma unroll
+          for (int i = 0; i < BLOCK_M / EPR; ++i)
+            tma_load_2d_pair(sa + i * MN_BOX_BYTES, &g.tmA[j], fb, m0 + i * EPR, kb * BLOCK_K);
+#pragma unroll
+          for (int i = 0; i < B_ROWS / EPR; ++i)
+            tma_load_2d_pair(sb + i * MN_BOX_BYTES, &g.tmB[j], fb, n0 + i * EPR, kb * BLOCK_K);
+          if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && rank == 0) {  // ---- MMA issuer
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int w = unit0; w < g.total_units; w += nunits, ++it) {
+        int j, m0, n0, kb0, kb1;
+        locate(w, j, m0, n0, kb0, kb1);
+        const int a = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&acc_empty[a], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * BLOCK_N;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          const uint32_t sb = sa + A_TILE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint64_t ad = make_smem_desc(sa + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT);
+            const uint64_t bd = make_smem_desc(sb + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT);
+            umma_ss_pair<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[s], 3);
+          if (++s == NUM_STAGES) { s = 0; ph ^= 1; }
+        }
+        umma_commit_pair(&acc_full[a], 3);
+      }
+    }
+  } else if (warp >= 4) {  // ---- epilogue: TMEM -> registers -> red.add onto the (zeroed) gradient
+    const int q4 = warp & 3;
+    const int chalf = (warp - 4) >> 2;
+    int it = 0;
+    for (int w = unit0; w < g.total_units; w += nunits, ++it) {
+      int j, m0, n0, kb0, kb1;
+      locate(w, j, m0, n0, kb0, kb1);
+      const WgradProblem& q = g.prob[j];
+      const int a = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      const int row = m0 + rank * BLOCK_M + q4 * 32 + lane;
+      const bool row_ok = row < q.M;
+      mbar_wait(&acc_full[a], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + a * BLOCK_N;
+#pragma unroll 1
+      for (int c = chalf * (BLOCK_N / 64); c < (chalf + 1) * (BLOCK_N / 64); ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= q.N) break;  // warp-uniform
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        float* o = q.out + (long long)row * q.ldo + col0;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+          if (col0 + i < q.N)
+            red_add_v4(o + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
+                       __uint_as_float(v[i + 3]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&acc_empty[a], 0);
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, NUM_ACC * BLOCK_N);
+  }
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -730,4 +923,71 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
   }
   return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
               : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st);
+}
+
+// All layers' weight gradients in one launch: dw[j][N_j, K_j] += dy[j][M, N_j]^T . x[j][M, K_j]  (fp32, red.add: the
+// outputs must hold zeros or the value to accumulate onto).
+extern "C" int b200_linear_wgrad_grouped(int count, const void* const* dy, const int64_t* lddy, const void* const* x,
+                                         const int64_t* ldx, float* const* dw, const int64_t* lddw, int64_t M,
+                                         const int64_t* N, const int64_t* K, int dtype, b200_stream_t stream) {
+  B200_REQUIRE(count >= 1 && count <= WG_MAX_PROBLEMS, "grouped wgrad takes 1..%d problems, got %d", WG_MAX_PROBLEMS,
+               count);
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;
+  const int epr = tf32 ? 32 : 64;
+  static WgradGroup g;  // host staging copy (one caller thread per process, see b200step.h)
+  g.count = count;
+  const int k_blocks = (int)((M + bk - 1) / bk);
+  int total_tiles = 0;
+  for (int j = 0; j < count; ++j) {
+    if (int r = check_dims(M, N[j], K[j], dtype)) return r;
+    B200_REQUIRE(lddw[j] % 4 == 0 && (reinterpret_cast<uintptr_t>(dw[j]) & 15) == 0,
+                 "wgrad output %d must be 16-byte aligned with lddw %% 4 == 0", j);
+    if (int r = make_tmap(&g.tmA[j], tf32, dy[j], N[j], M, lddy[j], epr, bk, true)) return r;
+    if (int r = make_tmap(&g.tmB[j], tf32, x[j], K[j], M, ldx[j], epr, bk, true)) return r;
+    WgradProblem& q = g.prob[j];
+    q.M = (int)N[j]; q.N = (int)K[j];
+    q.k_blocks = k_blocks;
+    q.m_tiles = (int)((N[j] + 2 * BLOCK_M - 1) / (2 * BLOCK_M));
+    q.n_tiles = (int)((K[j] + BLOCK_N - 1) / BLOCK_N);
+    q.out = dw[j]; q.ldo = lddw[j];
+    total_tiles += q.m_tiles * q.n_tiles;
+  }
+  // every tile is cut into the same number of batch slices, sized so that each CTA pair gets ~4 units
+  const int pairs = sm_count() / 2;
+  static const int rounds = getenv("B200STEP_WGRAD_ROUNDS") ? atoi(getenv("B200STEP_WGRAD_ROUNDS")) : 4;
+  int splits = rounds * pairs / total_tiles;
+  if (splits < 1) splits = 1;
+  if (splits > k_blocks) splits = k_blocks;
+  const int kbps = (k_blocks + splits - 1) / splits;
+  splits = (k_blocks + kbps - 1) / kbps;
+  int units = 0;
+  for (int j = 0; j < count; ++j) {
+    WgradProblem& q = g.prob[j];
+    q.splits = splits; q.kb_per_split = kbps;
+    q.unit_begin = units;
+    units += q.m_tiles * q.n_tiles * splits;
+  }
+  g.total_units = units;
+  auto launch = [&](auto kern) -> int {
+    static bool configured[2] = {false, false};
+    if (!configured[tf32]) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+      configured[tf32] = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((units < pairs ? units : pairs) * 2);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = GEMM_SMEM_BYTES;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 2;
+    B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, g));
+    return 0;
+  };
+  return tf32 ? launch(wgrad_grouped_kernel<1>) : launch(wgrad_grouped_kernel<0>);
 }

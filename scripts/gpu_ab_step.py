@@ -8,20 +8,22 @@ from b200step.engine import StepConfig, TrainStep
 from b200step.model import ARCHS, init_parameters
 spec = ARCHS["tabular_mlp"]; B = 65536
 ds = make_synthetic(B * 8, spec)
-def run(steps=200, **kw):
+import json, statistics
+variants = json.loads(os.environ.get("AB_VARIANTS", '[["default", {}]]'))
+steps = int(os.environ.get("AB_STEPS", "40"))
+reps = int(os.environ.get("AB_REPS", "8"))
+engs = []
+for name, kw in variants:
     eng = TrainStep(spec, init_parameters(spec, 0), ds, torch.arange(B * 8), StepConfig(batch_size=B, **kw))
     for _ in range(5): eng.step()
     eng.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    out = []
-    for rep in range(3):
+    engs.append((name, eng, []))
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+for rep in range(reps):            # interleaved, so clock / thermal drift hits every variant alike
+    for name, eng, out in engs:
         e0.record(eng.main)
         for _ in range(steps): eng.step()
         e1.record(eng.main); eng.synchronize()
         out.append(e0.elapsed_time(e1) / steps)
-    eng.close()
-    return out
-import json
-variants = json.loads(os.environ.get("AB_VARIANTS", '[["default", {}]]'))
-for name, kw in variants:
-    print(name, ["%.4f" % x for x in run(steps=int(os.environ.get("AB_STEPS", "50")), **kw)], flush=True)
+for name, eng, out in engs:
+    print("%-28s median %.4f  min %.4f  max %.4f ms" % (name, statistics.median(out), min(out), max(out)), flush=True)

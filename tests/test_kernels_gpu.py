@@ -133,6 +133,28 @@ def test_relu_bitmask_and_fused_bias_grad(ops, dtype, M, N, K):
     torch.testing.assert_close(db3, db, rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M", [4096, 65536, 1000])
+def test_linear_wgrad_grouped(ops, dtype, M):
+    """All layers' weight gradients in one launch == the per-layer kernel (same tiles, same arithmetic)."""
+    shapes = [(1000, 512), (512, 512), (512, 448)]   # (N, K) of T0's three Linear layers
+    dys = [_rand((M, n), dtype, 70 + i, 0.1) for i, (n, k) in enumerate(shapes)]
+    xs = [_rand((M, k), dtype, 80 + i) for i, (n, k) in enumerate(shapes)]
+    dws = [torch.zeros((n, k), dtype=torch.float32, device="cuda") for (n, k) in shapes]
+    ops.linear_wgrad_grouped(dys, xs, dws, M=M, Ns=[n for n, _ in shapes], Ks=[k for _, k in shapes])
+    torch.cuda.synchronize()
+    for dy, x, dw, (n, k) in zip(dys, xs, dws, shapes):
+        ref = dy.double().t() @ x.double()
+        scale = (M ** 0.5) * 0.1
+        tol = (1e-5 if dtype == torch.bfloat16 else 2e-3) * scale + 1e-5
+        assert (dw.double() - ref).abs().max().item() <= tol * 4
+    # accumulates onto what is there
+    ops.linear_wgrad_grouped(dys, xs, dws, M=M, Ns=[n for n, _ in shapes], Ks=[k for _, k in shapes])
+    torch.cuda.synchronize()
+    ref = dys[0].double().t() @ xs[0].double()
+    assert (dws[0].double() - 2 * ref).abs().max().item() <= tol * 8 * 10
+
+
 def test_gemm_rejects_misaligned(ops):
     from b200step.lib import B200Error
 

@@ -120,6 +120,19 @@ def test_row_chunked_step_matches_oracle(precision):
     assert _param_err(oracle, eng) <= 2e-2
 
 
+def test_grouped_wgrad_step_matches_oracle():
+    spec = SMALL
+    ds = make_synthetic(1024, spec)
+    oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=256, precision="bf16")
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(1024, 1, 0),
+                    StepConfig(batch_size=256, precision="bf16", grouped_wgrad=True))
+    for _ in range(8):
+        lo = oracle.step()[0]
+        eng.step()
+        assert abs(lo - eng.loss_value()) <= 2e-3 * max(1.0, abs(lo))
+    assert _param_err(oracle, eng) <= 1e-2
+
+
 def test_graph_replay_equals_eager():
     a = _run_pair(SMALL, rows=2048, batch=256, steps=10, precision="bf16", use_graph=True)
     b = _run_pair(SMALL, rows=2048, batch=256, steps=10, precision="bf16", use_graph=False)
