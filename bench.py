@@ -195,6 +195,9 @@ def run_b200(args, rank, local_rank, world):
     rows = world * B * BATCHES_PER_RANK
     ds = make_synthetic(rows, spec)
     cfg = StepConfig(batch_size=B, world=world, rank=rank, precision=wl["precision"], optimizer=wl["optimizer"])
+    if os.environ.get("B200STEP_BUCKET_CAP_BYTES"):      # experiments with the DDP-style bucket cap
+        cfg.bucket_cap_bytes = int(os.environ["B200STEP_BUCKET_CAP_BYTES"])
+        cfg.first_bucket_bytes = min(cfg.first_bucket_bytes, cfg.bucket_cap_bytes)
     idx = rank_indices(rows, world, rank)
     # keep only this rank's rows resident (same values as the global dataset, re-indexed 0..n-1)
     local = dataclasses.replace(ds, dense=ds.dense[idx], cat=ds.cat[idx], label=ds.label[idx])
