@@ -40,7 +40,6 @@ WORKLOADS = {
     "t1_bf16_b65536_adam": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="adam"),
 }
 BATCHES_PER_RANK = 8          # distinct batches per rank, cycled (N = W*B*8 rows)
-RAW_BYTES_PER_SAMPLE = None   # filled from the spec: 4*num_dense + 8*num_cat + 8
 REF_SAMPLE_CAP = 65536        # rows per step of the CPU arms (bounded sample)
 
 

@@ -3,18 +3,20 @@
 This is the body of the reference's hot loop (task.py:303-312) re-laid for the GPU:
 
     task.py:305,307  H2D copies of the batch          -> none: the dataset is resident in HBM; K-pre gathers rows
-    task.py:308      optimizer.zero_grad()            -> none: every gradient is overwritten (or memset) below
-    task.py:309      outputs = model(inputs)          -> K-pre, then one tcgen05 GEMM per Linear (bias/ReLU/dropout fused)
+                                                         (`step_from_host` keeps the copies for host-fed batches)
+    task.py:308      optimizer.zero_grad()            -> folded into the optimizer pass (it leaves the gradients zeroed)
+    task.py:309      outputs = model(inputs)          -> K-pre, then one tcgen05 GEMM per Linear (bias/ReLU/dropout and
+                                                         the ReLU bit-mask for backward fused into the epilogue)
     task.py:310      loss = criterion(outputs, y)     -> K-loss (loss + dlogits + output-layer bias gradient)
-    task.py:311      loss.backward()  [+ DDP hooks]   -> per layer: dgrad GEMM (ReLU mask fused), wgrad GEMM (split-K, fp32
-                                                         into the flat gradient buffer), column-sum bias gradient, embedding
-                                                         scatter-add; each finished bucket is all-reduced by NCCL on a side
-                                                         stream while the rest of backward keeps running
-    task.py:312      optimizer.step()                 -> one fused SGD/Adam pass over the flat buffers
+    task.py:311      loss.backward()  [+ DDP hooks]   -> dgrad GEMM chain (ReLU mask and bias-gradient column sums fused),
+                                                         embedding scatter-add, then the wgrad GEMMs (split-K, fp32
+                                                         red.add into the flat gradient buffer); each finished bucket is
+                                                         all-reduced by NCCL on a side stream under the remaining wgrads
+    task.py:312      optimizer.step()                 -> fused SGD/Adam pass over the flat buffers, one launch per bucket
 
-All kernels are enqueued through the C ABI (libb200step.so).  The steady-state step (full batches) is captured
-once into a CUDA graph and replayed; the per-step variables (batch cursor, step count) live in device memory.
-PyTorch owns the memory and the streams and does nothing else here.
+All kernels are enqueued through the C ABI (libb200step.so) with programmatic dependent launch.  The steady-state
+step (full batches) is captured once into a CUDA graph and replayed; the per-step variables (batch cursor, step
+count) live in device memory.  PyTorch owns the memory and the streams and does nothing else here.
 """
 from __future__ import annotations
 
