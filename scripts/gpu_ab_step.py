@@ -6,7 +6,8 @@ import torch
 from b200step.data import make_synthetic
 from b200step.engine import StepConfig, TrainStep
 from b200step.model import ARCHS, init_parameters
-spec = ARCHS["tabular_mlp"]; B = 65536
+spec = ARCHS[os.environ.get("AB_ARCH", "tabular_mlp")]; B = int(os.environ.get("AB_BATCH", "65536"))
+PREC = os.environ.get("AB_PRECISION", "bf16")
 ds = make_synthetic(B * 8, spec)
 import json, statistics
 variants = json.loads(os.environ.get("AB_VARIANTS", '[["default", {}]]'))
@@ -14,7 +15,7 @@ steps = int(os.environ.get("AB_STEPS", "40"))
 reps = int(os.environ.get("AB_REPS", "8"))
 engs = []
 for name, kw in variants:
-    eng = TrainStep(spec, init_parameters(spec, 0), ds, torch.arange(B * 8), StepConfig(batch_size=B, **kw))
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, torch.arange(B * 8), StepConfig(batch_size=B, precision=PREC, **kw))
     for _ in range(5): eng.step()
     eng.synchronize()
     engs.append((name, eng, []))
