@@ -27,7 +27,9 @@ cnt = {"fwd": 0, "dgrad": 0, "wgrad": 0}
 out, traffic = [], {}
 for r in rows[start:]:
     n = r[ix["Kernel Name"]]
-    if "gemm_kernel" in n:
+    if "wgrad_grouped_kernel" in n:
+        label = "linear_wgrad_grouped[65536x3 layers]"
+    elif "gemm_kernel" in n:
         kind = "fwd" if ", 0, 2>" in n.replace("(int)", "").replace("(bool)", "") and False else None
         args = n.replace("(int)", "").replace("(bool)", "")
         epi = args.split("<")[1].split(">")[0].split(",")[3].strip()
