@@ -247,7 +247,9 @@ class TrainStep:
         L = self.L
         n = 0
         inv_keep = 1.0 / (1.0 - spec.dropout) if spec.dropout > 0 else 1.0
-        bucket_of = {ready: bi for bi, (_, _, ready) in enumerate(self.buckets)}
+        bucket_of: Dict[int, List[int]] = {}
+        for bi, (_, _, ready) in enumerate(self.buckets):
+            bucket_of.setdefault(ready, []).append(bi)
         chunks = self._chunks(batch)
         for ci, (r0, rows) in enumerate(chunks):
             sl = slice(r0, r0 + rows)
@@ -281,8 +283,9 @@ class TrainStep:
                 ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
                             num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
                 n += 2
-                if last_chunk and -1 in bucket_of:
-                    n += self._reduce_bucket(bucket_of[-1])
+                if last_chunk:
+                    for bi in bucket_of.get(-1, []):
+                        n += self._reduce_bucket(bi)
             grouped = cfg.grouped_wgrad if cfg.grouped_wgrad is not None else cfg.world == 1
             xs = [self.x0[sl] if li == 0 else self.acts[li - 1][sl] for li in range(L)]
             # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
@@ -296,23 +299,25 @@ class TrainStep:
                 n += 1
                 if last_chunk:
                     for li in order:
-                        if li in bucket_of:
-                            n += self._reduce_bucket(bucket_of[li])
+                        for bi in bucket_of.get(li, []):
+                            n += self._reduce_bucket(bi)
             else:
                 for li in range(L - 1, -1, -1):
                     k, o = dims[li]
                     kk = self.k0 if li == 0 else k
                     ops.linear_wgrad(dys[li], xs[li], self._gw(li), M=rows, N=o, K=kk, accumulate=True, stream=st)
                     n += 1
-                    if last_chunk and li in bucket_of:
-                        n += self._reduce_bucket(bucket_of[li])
+                    if last_chunk:
+                        for bi in bucket_of.get(li, []):
+                            n += self._reduce_bucket(bi)
         # optimizer ----------------------------------------------------------------------------------------
         # world > 1: one launch per bucket, each gated only by that bucket's all-reduce, so the update of the early
         # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer.
         n_shadow = lay.n_shadow if self.shadow is not None else 0
         if cfg.world > 1 and cfg.overlap_comm:
             ranges = [(self._ev_done[bi], s_, e_) for bi, (s_, e_, _) in enumerate(self.buckets)]
-            order = sorted(range(len(ranges)), key=lambda bi: -1 if self.buckets[bi][2] == -1 else L - self.buckets[bi][2])
+            order = sorted(range(len(ranges)),
+                           key=lambda bi: (-1 if self.buckets[bi][2] == -1 else L - self.buckets[bi][2], bi))
             ranges = [ranges[bi] for bi in order]   # in the order their all-reduces were issued
         else:
             ranges = [(None, 0, lay.total)]

@@ -187,6 +187,9 @@ class FlatLayout:
                 cur_start, cur_end, ready = s, e, li
         if cur_start is not None:
             out.append((cur_start, cur_end, ready))
+        # A single range above the cap (the wide model's 436 MB of embedding tables) is deliberately NOT cut into
+        # cap-sized pieces: measured on 8 GPUs, 17 all-reduces of 25 MiB made the T1 step 4.77 ms against 3.73 ms
+        # with one 436 MB all-reduce.
         return out
 
 

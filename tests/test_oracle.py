@@ -129,3 +129,19 @@ def test_golden_vectors(name):
     assert torch.equal(got["x0_bits"], blob["x0_bits"])           # preprocessing: bit-exact
     torch.testing.assert_close(got["losses"], blob["losses"], rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(got["param_checksums"], blob["param_checksums"], rtol=1e-4, atol=1e-5)
+
+
+def test_bucket_plan_covers_flat_buffer_and_respects_cap():
+    """DDP-style buckets (first 1 MiB, then 25 MiB): contiguous, disjoint, cover every parameter, in backward order;
+    the embedding tables stay one bucket (one large all-reduce measured faster than 17 capped ones)."""
+    for name, spec in ARCHS.items():
+        lay = FlatLayout(spec)
+        b = lay.buckets()
+        covered = sorted((s, e) for s, e, _ in b)
+        assert covered[0][0] == 0 and covered[-1][1] == lay.total
+        for (s0, e0), (s1, e1) in zip(covered, covered[1:]):
+            assert e0 == s1
+        assert all((e - s) * 4 <= (25 << 20) for s, e, r in b if r != -1)
+        readies = [r for _, _, r in b]
+        assert readies[0] == len(spec.layer_dims) - 1            # output layer first, like DDP's reverse order
+        assert readies.count(-1) == 1
