@@ -8,6 +8,9 @@
  *   - all pointers are DEVICE pointers unless the comment says "host";
  *   - the library never allocates the caller's data: the host (PyTorch) owns every buffer and
  *     passes tensor.data_ptr(); work is enqueued on the caller's stream and does not synchronise;
+ *   - kernels are launched with programmatic dependent launch (a kernel's prologue may overlap the tail of the
+ *     previous kernel on the stream; it touches global memory only after that kernel has completed);
+ *     B200STEP_PDL=0 in the environment turns this off;
  *   - matrices are row-major; `ld*` are row strides in ELEMENTS;
  *   - dtype codes: B200_F32 (fp32 storage, TF32 tensor-core math), B200_BF16 (bf16 storage, fp32 accumulate).
  */
