@@ -1,0 +1,52 @@
+"""The CUDA path against the COMMITTED golden fixtures (tests/golden/*.pt, produced by the CPU oracle with
+tests/golden/make_golden.py): sampler order, the bit pattern of the first preprocessed batch, the loss curve and
+the parameter checksums after 16 steps.  Nothing here runs the oracle."""
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from b200step.data import make_synthetic  # noqa: E402
+from b200step.engine import StepConfig, TrainStep  # noqa: E402
+from b200step.model import init_parameters  # noqa: E402
+from b200step.sampler import rank_indices  # noqa: E402
+from tests.golden.make_golden import CASES  # noqa: E402  (case definitions only)
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_cuda_path_reproduces_golden_vectors(name):
+    case = CASES[name]
+    blob = torch.load(os.path.join(GOLDEN, f"{name}.pt"))
+    spec = case["spec"]
+    ds = make_synthetic(case["rows"], spec)
+    idx = rank_indices(case["rows"], 1, 0)
+    assert torch.equal(idx, blob["row_idx"])                                   # sampler: index-exact
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, idx,
+                    StepConfig(batch_size=case["batch"], precision=case["precision"], optimizer=case["optimizer"],
+                               lr=case["lr"]))
+    losses = []
+    for s in range(case["steps"]):
+        eng.step()
+        losses.append(eng.loss_value())
+        if s == 0:                                                             # preprocessing: bit-exact
+            got = torch.empty(case["batch"], spec.in_features, dtype=eng.dt)
+            got[:, eng.layout.input_perm()] = eng.x0[:, : spec.in_features].cpu()
+            view = torch.int16 if eng.dt == torch.bfloat16 else torch.int32
+            assert torch.equal(got.view(view), blob["x0_bits"])
+    # per-step loss: rel 2e-3 (TF32 vs the fp32 fixture; bf16 vs the bf16-storage fixture)
+    ref = blob["losses"]
+    for a, b in zip(ref.tolist(), losses):
+        assert abs(a - b) <= 2e-3 * max(1.0, abs(a)), (name, ref.tolist(), losses)
+    # parameter checksums (sum, sum of squares per tensor) after the last step
+    sd = eng.state_dict()
+    assert list(sd.keys()) == blob["param_keys"]
+    chk = torch.tensor([[v.double().sum().item(), (v.double() ** 2).sum().item()] for v in sd.values()],
+                       dtype=torch.float64)
+    sq_ref, sq = blob["param_checksums"][:, 1], chk[:, 1]
+    assert ((sq - sq_ref).abs() / sq_ref.clamp_min(1e-12)).max().item() <= (2e-2 if case["optimizer"] == "sgd" else 5e-2)
+    scale = sq_ref.sqrt() * torch.tensor([float(v.numel()) ** 0.5 for v in sd.values()], dtype=torch.float64)
+    assert ((chk[:, 0] - blob["param_checksums"][:, 0]).abs() / scale.clamp_min(1e-9)).max().item() <= 2e-2
