@@ -152,14 +152,19 @@ int b200_emb_bwd(const void* dx, int64_t lddx, const int32_t* idx, float* dtable
  * zero_grad != 0: the consumed gradient is overwritten with zeros in the same pass (the reference's
  *      optimizer.zero_grad(), task.py:308, moved behind the update) so the next backward's split-K / scatter
  *      accumulations need no separate memset.
+ * adv_ticket (nullable): a zero-initialised device counter; when given, the last block of this launch to finish
+ *      does what b200_advance_step does (cursor = (cursor+1) mod steps_per_epoch, step += 1; either pointer may be
+ *      NULL) — pass it to the LAST optimizer launch of a step to save the separate bookkeeping kernel.
  * shadow_bf16 (nullable): bf16 copy of p refreshed for the first n_shadow elements (GEMM operand copy).
  */
 int b200_sgd_step(float* p, float* g, float* momentum_buf, void* shadow_bf16,
                   int64_t n, int64_t n_shadow, double lr, double momentum, double weight_decay,
-                  int zero_grad, b200_stream_t stream);
+                  int zero_grad, int32_t* adv_cursor, int32_t* adv_step, int32_t steps_per_epoch,
+                  uint32_t* adv_ticket, b200_stream_t stream);
 int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
                    int64_t n, int64_t n_shadow, double lr, double beta1, double beta2, double eps,
-                   double weight_decay, const int32_t* step, int zero_grad, b200_stream_t stream);
+                   double weight_decay, const int32_t* step, int zero_grad, int32_t* adv_cursor,
+                   int32_t* adv_step, int32_t steps_per_epoch, uint32_t* adv_ticket, b200_stream_t stream);
 /* fp32 -> bf16 RNE copy (initial shadow weights) */
 int b200_cast_bf16(const float* src, void* dst_bf16, int64_t n, b200_stream_t stream);
 /* zero `bytes` bytes of device memory on the stream (gradient regions that are accumulated with atomics) */

@@ -140,6 +140,7 @@ class TrainStep:
         self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)   # last-block detector of the optimizer launch
         self.ce_scratch = torch.empty(ops.ce_scratch_floats(spec.num_classes), dtype=torch.float32, device=dev)
         # 1 bit per hidden activation (ReLU/dropout mask for backward), row stride padded to 16 bytes
         self.masks = [torch.zeros(B, ((o + 31) // 32 + 3) // 4 * 4, dtype=torch.int32, device=dev)
@@ -321,24 +322,24 @@ class TrainStep:
             ranges = [ranges[bi] for bi in order]   # in the order their all-reduces were issued
         else:
             ranges = [(None, 0, lay.total)]
-        for ev, s_, e_ in ranges:
+        # the last optimizer launch also advances the device-side batch cursor / step count (its last block does)
+        adv = (self.cursor if advance else None, self.step_ctr, max(self.steps_per_epoch_full, 1), self.ticket)
+        for ri, (ev, s_, e_) in enumerate(ranges):
+            last_range = ri == len(ranges) - 1
             if ev is not None:
                 st.wait_event(ev)
             ns = max(0, min(n_shadow, e_) - s_)
             sh = self.shadow[s_:] if (self.shadow is not None and ns > 0) else None
             if cfg.optimizer == "sgd":
                 ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
-                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True, stream=st)
+                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True,
+                             advance=adv if last_range else None, stream=st)
             else:
                 ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, self.step_ctr,
                               n_shadow=ns, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                              weight_decay=cfg.weight_decay, zero_grad=True, stream=st)
+                              weight_decay=cfg.weight_decay, zero_grad=True,
+                              advance=adv if last_range else None, stream=st)
             n += 1
-        if advance:
-            ops.advance_step(self.cursor, self.step_ctr, max(self.steps_per_epoch_full, 1), stream=st)
-        else:
-            ops.advance_step(None, self.step_ctr, 1, stream=st)
-        n += 1
         return n
 
     def _reduce_bucket(self, bi: int) -> int:

@@ -125,17 +125,21 @@ def emb_bwd(dx, idx, dtables, *, batch: int, emb_col0: int = 0, num_cat: int, ta
 
 
 def sgd_step(p, g, buf, shadow, *, n_shadow: int, lr: float, momentum: float, weight_decay: float,
-             zero_grad: bool = False, stream=None):
+             zero_grad: bool = False, advance=None, stream=None):
+    """advance = (cursor, step, steps_per_epoch, ticket) folds the step bookkeeping into this launch."""
     _cuda(p, g, buf, shadow)
+    ac, as_, spe, tk = advance if advance is not None else (None, None, 1, None)
     get_lib().sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), p.numel(), n_shadow, lr, momentum, weight_decay,
-                       int(zero_grad), _stream(stream))
+                       int(zero_grad), ptr(ac), ptr(as_), spe, ptr(tk), _stream(stream))
 
 
 def adam_step(p, g, m, v, shadow, step, *, n_shadow: int, lr: float, beta1: float, beta2: float, eps: float,
-              weight_decay: float, zero_grad: bool = False, stream=None):
+              weight_decay: float, zero_grad: bool = False, advance=None, stream=None):
     _cuda(p, g, m, v, shadow, step)
+    ac, as_, spe, tk = advance if advance is not None else (None, None, 1, None)
     get_lib().adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), n_shadow, lr, beta1, beta2,
-                        eps, weight_decay, ptr(step), int(zero_grad), _stream(stream))
+                        eps, weight_decay, ptr(step), int(zero_grad), ptr(ac), ptr(as_), spe, ptr(tk),
+                        _stream(stream))
 
 
 def cast_bf16(src, dst, stream=None):

@@ -17,9 +17,36 @@ __device__ __forceinline__ void store_shadow4(void* shadow, long long i, float a
   *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(shadow) + i) = o;
 }
 
+// Folded step bookkeeping: the LAST block of the optimizer grid to finish (a ticket counter tells) advances the
+// device-side batch cursor and step count, so the step needs no separate 1-thread kernel.  Every other block has
+// finished — hence has read *step — before the last one takes its ticket.
+struct StepAdvance {
+  int* cursor;
+  int* step;
+  int steps_per_epoch;
+  unsigned* ticket;  // nullptr: no bookkeeping in this launch
+};
+__device__ __forceinline__ void advance_if_last_block(const StepAdvance& a) {
+  if (a.ticket == nullptr) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned t = atomicAdd(a.ticket, 1u);
+    if (t == gridDim.x - 1) {
+      *a.ticket = 0u;
+      if (a.cursor) {
+        const int c = *a.cursor + 1;
+        *a.cursor = (c >= a.steps_per_epoch) ? 0 : c;
+      }
+      if (a.step) *a.step = *a.step + 1;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(OPT_THREADS)
 sgd_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ buf,
-           void* __restrict__ shadow, long long n, long long n_shadow, float lr, float mu, float wd, int zero_grad) {
+           void* __restrict__ shadow, long long n, long long n_shadow, float lr, float mu, float wd, int zero_grad,
+           const StepAdvance adv) {
   pdl_launch_dependents();
   pdl_wait();
   const long long nv = n >> 2;
@@ -53,6 +80,7 @@ sgd_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ buf
     if (i < n_shadow) reinterpret_cast<__nv_bfloat16*>(shadow)[i] = __float2bfloat16_rn(pi);
     if (zero_grad) g[i] = 0.f;
   }
+  advance_if_last_block(adv);
 }
 
 // w1 = (float)(1-beta1), w2 = (float)(1-beta2): formed in double on the host like torch's python scalars
@@ -69,7 +97,7 @@ __device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v,
 __global__ void __launch_bounds__(OPT_THREADS)
 adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             void* __restrict__ shadow, long long n, long long n_shadow, double lr, double b1, double b2, float eps,
-            float wd, const int* __restrict__ step, int zero_grad) {
+            float wd, const int* __restrict__ step, int zero_grad, const StepAdvance adv) {
   pdl_launch_dependents();
   pdl_wait();
   // bias corrections in double like torch (python floats): 1 - beta**t, t = completed steps + 1
@@ -102,6 +130,7 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
     if (i < n_shadow) reinterpret_cast<__nv_bfloat16*>(shadow)[i] = __float2bfloat16_rn(pi);
     if (zero_grad) g[i] = 0.f;
   }
+  advance_if_last_block(adv);
 }
 
 __global__ void __launch_bounds__(OPT_THREADS)
@@ -181,21 +210,25 @@ using namespace b200;
 
 extern "C" int b200_sgd_step(float* p, float* g, float* momentum_buf, void* shadow_bf16, int64_t n,
                              int64_t n_shadow, double lr, double momentum, double weight_decay, int zero_grad,
+                             int32_t* adv_cursor, int32_t* adv_step, int32_t steps_per_epoch, uint32_t* adv_ticket,
                              b200_stream_t stream) {
+  const StepAdvance adv{adv_cursor, adv_step, steps_per_epoch, adv_ticket};
   B200_REQUIRE(n > 0 && n_shadow >= 0 && n_shadow <= n, "bad sizes n=%lld n_shadow=%lld", (long long)n, (long long)n_shadow);
   B200_REQUIRE(n_shadow % 4 == 0 || n_shadow == n, "n_shadow must be a multiple of 4");
   B200_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
                  reinterpret_cast<uintptr_t>(momentum_buf)) & 15) == 0, "p/g/buf must be 16-byte aligned");
   if (!shadow_bf16) n_shadow = 0;
   B200_CHECK_CUDA(launch_pdl(sgd_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), 
-      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay, zero_grad));
+      p, g, momentum_buf, shadow_bf16, n, n_shadow, (float)lr, (float)momentum, (float)weight_decay, zero_grad, adv));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
                               int64_t n, int64_t n_shadow, double lr, double beta1, double beta2, double eps,
-                              double weight_decay, const int32_t* step, int zero_grad, b200_stream_t stream) {
+                              double weight_decay, const int32_t* step, int zero_grad, int32_t* adv_cursor,
+                              int32_t* adv_step, int32_t steps_per_epoch, uint32_t* adv_ticket, b200_stream_t stream) {
+  const StepAdvance adv{adv_cursor, adv_step, steps_per_epoch, adv_ticket};
   B200_REQUIRE(n > 0 && n_shadow >= 0 && n_shadow <= n, "bad sizes n=%lld n_shadow=%lld", (long long)n, (long long)n_shadow);
   B200_REQUIRE(n_shadow % 4 == 0 || n_shadow == n, "n_shadow must be a multiple of 4");
   B200_REQUIRE(step != nullptr, "adam needs the device step counter");
@@ -204,7 +237,7 @@ extern "C" int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg
   if (!shadow_bf16) n_shadow = 0;
   B200_CHECK_CUDA(launch_pdl(adam_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), 
       p, g, exp_avg, exp_avg_sq, shadow_bf16, n, n_shadow, lr, beta1, beta2, (float)eps, (float)weight_decay, step,
-      zero_grad));
+      zero_grad, adv));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
