@@ -192,11 +192,17 @@ def run_b200(args, rank, local_rank, world):
         comm = Communicator(rank, world, uid[0])
 
     rows = world * B * BATCHES_PER_RANK
-    ds = make_synthetic(rows, spec)
+    ds = make_synthetic(rows, spec, zipf_alpha=args.zipf_alpha)
     cfg = StepConfig(batch_size=B, world=world, rank=rank, precision=wl["precision"], optimizer=wl["optimizer"])
     if os.environ.get("B200STEP_BUCKET_CAP_BYTES"):      # experiments with the DDP-style bucket cap
         cfg.bucket_cap_bytes = int(os.environ["B200STEP_BUCKET_CAP_BYTES"])
         cfg.first_bucket_bytes = min(cfg.first_bucket_bytes, cfg.bucket_cap_bytes)
+    if os.environ.get("B200STEP_SM_RESERVE"):             # experiments: SMs the wgrads leave to the all-reduce
+        cfg.comm_sm_reserve = int(os.environ["B200STEP_SM_RESERVE"])
+    if os.environ.get("B200STEP_PREFETCH_RESERVE"):
+        cfg.prefetch_sm_reserve = int(os.environ["B200STEP_PREFETCH_RESERVE"])
+    if os.environ.get("B200STEP_PREFETCH_PRE"):           # A/B: K-pre of the next batch under the last all-reduces
+        cfg.prefetch_pre = os.environ["B200STEP_PREFETCH_PRE"] != "0"
     idx = rank_indices(rows, world, rank)
     # keep only this rank's rows resident (same values as the global dataset, re-indexed 0..n-1)
     local = dataclasses.replace(ds, dense=ds.dense[idx], cat=ds.cat[idx], label=ds.label[idx])
@@ -308,7 +314,8 @@ def run_b200(args, rank, local_rank, world):
                    "optimizer": wl["optimizer"], "params": spec.num_params, "parallelism": f"dp{world}",
                    "l2": "per-step working set > 126 MB L2 (no flush needed)" if B >= 32768 else
                          "working set fits L2: dataset cycles 8 batches",
-                   "cuda_graph": True},
+                   "cuda_graph": True, "prefetch_pre": eng.prefetch,
+                   "categorical_ids": "uniform" if args.zipf_alpha is None else f"zipf(alpha={args.zipf_alpha})"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": eng.kernels_per_step * args.steps,
         "roofline": roof, "roofline_hbm": roof_hbm, "kernels": prof, "step_tflops_per_gpu": step_tflops,
         "final_loss": loss_after,
@@ -376,6 +383,7 @@ def profile_kernels(eng, spec, B, world):
     try:
         for n in names:
             setattr(ops, n, wrap(n, orig[n]))
+        eng._pre_ready = False      # the eager steps below run K-pre themselves and overwrite the prefetched batch
         for _ in range(reps):
             eng._enqueue(B, None, eng.row_idx, eng.cursor, True)
         eng.synchronize()
@@ -407,6 +415,8 @@ def main():
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="t0_bf16_b65536")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--zipf-alpha", dest="zipf_alpha", type=float, default=None,
+                    help="categorical ids ~ Zipf(alpha) instead of uniform (SURVEY.md §8d secondary dataset row)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -35,6 +35,12 @@ typedef void* b200_stream_t; /* a cudaStream_t */
 const char* b200_last_error(void);           /* host string, thread-local */
 int b200_abi_version(void);
 int b200_device_sm_count(int* out_host);     /* SM count of the current device */
+/* Size the persistent grids of every later launch (GEMMs, K-pre, K-loss, K-opt) for `sms` SMs instead of the whole
+ * device; 0 restores the default.  Host-side state read at launch (or graph-capture) time, one caller thread.
+ * No counterpart in the reference: DDP overlaps its all-reduce with cuBLAS/cuDNN kernels that are not persistent
+ * (task.py:189).  Here a collective on another stream needs free SMs, otherwise its CTAs wait for a grid boundary
+ * and then push part of the next persistent grid into a second wave.  Results do not depend on the budget. */
+int b200_set_sm_budget(int sms);
 
 /* ---- K-pre: fused batch load + standardise + categorical gather ---------------------------
  * Replaces the reference's host-side input pipeline for one batch:

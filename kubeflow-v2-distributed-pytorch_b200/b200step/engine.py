@@ -52,9 +52,21 @@ class StepConfig:
     keep_logits: bool = False            # keep logits and dlogits in separate buffers (tests)
     deterministic_bias_grad: bool = False  # hidden-layer bias grads through a fixed-order reduction instead of atomics
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
+    comm_sm_reserve: Optional[int] = None  # None = DEFAULT_COMM_SM_RESERVE when world > 1 and comm overlaps
+    prefetch_sm_reserve: int = 32        # SMs the prefetched K-pre leaves to the all-reduces it runs under
+    prefetch_pre: bool = False           # run K-pre of the NEXT batch inside this step, right after the embedding
+                                         # tables' optimizer launch, i.e. under the all-reduces still in flight
+                                         # (device-resident `step()` path only).  Off by default: measured on T0
+                                         # +0.6 % at 2 GPUs, -2 % at 8 GPUs (profiles/r01_comm_overlap_experiments.md)
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1
+
+
+# SMs the GEMMs that run while an all-reduce is in flight leave free (B200_FLAG_SM_RESERVE).  The GEMM grids are
+# persistent and sized for every SM: when NCCL's CTAs take some, the displaced GEMM CTAs become a second wave.
+# Measured with scripts/gpu_allreduce_sweep.py (profiles/r01_allreduce_reserve_matrix_w2.md).
+DEFAULT_COMM_SM_RESERVE = 0
 
 
 class Communicator:
@@ -97,6 +109,7 @@ class TrainStep:
         if cfg.world > 1 and comm is None:
             raise ValueError("world > 1 needs a Communicator")
         self.lib = get_lib()  # raises when libb200step.so is missing
+        self.sms = ops.sm_count()
         self.spec, self.cfg, self.comm = spec, cfg, comm
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         self.layout = FlatLayout(spec)
@@ -157,6 +170,8 @@ class TrainStep:
         self.graph = None
         self.kernels_per_step = 0
         self.host_steps = 0
+        self.prefetch = bool(cfg.prefetch_pre) and len(self._chunks(B)) == 1 and self.steps_per_epoch_full > 0
+        self._pre_ready = False   # x0 / y / idx already hold the batch at the current cursor (prefetch mode)
 
         torch.cuda.synchronize(dev)  # allocations/fills above ran on torch's default stream
         with torch.cuda.stream(self.main):
@@ -196,8 +211,21 @@ class TrainStep:
             r0 += rows
         return out
 
+    def _pre(self, batch: int, ds: TabularDataset, row_idx: torch.Tensor, cursor: Optional[torch.Tensor],
+             r0: int = 0, rows: Optional[int] = None) -> int:
+        """K-pre for rows [r0, r0 + rows) of the batch the cursor points at: x0, y, idx."""
+        spec = self.spec
+        rows = batch if rows is None else rows
+        sl = slice(r0, r0 + rows)
+        ops.preprocess(ds.dense, ds.cat, ds.label, row_idx[r0:], cursor, ds.mean, ds.std,
+                       self.tables if spec.num_cat else None, self.x0[sl], self.y[sl], self.idx[sl], batch=rows,
+                       num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
+                       embed_dim=spec.embed_dim, cursor_stride=batch, stream=self.main)
+        return 1
+
     def _forward(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
-                 cursor: Optional[torch.Tensor], training: bool, r0: int = 0, rows: Optional[int] = None) -> int:
+                 cursor: Optional[torch.Tensor], training: bool, r0: int = 0, rows: Optional[int] = None,
+                 skip_pre: bool = False) -> int:
         """K-pre + the Linear stack (task.py:309) for rows [r0, r0 + rows) of the batch; dropout only when training
         (model.train(), task.py:301)."""
         spec, cfg, st = self.spec, self.cfg, self.main
@@ -206,11 +234,8 @@ class TrainStep:
         rows = batch if rows is None else rows
         sl = slice(r0, r0 + rows)
         n = 0
-        ops.preprocess(ds.dense, ds.cat, ds.label, row_idx[r0:], cursor, ds.mean, ds.std,
-                       self.tables if spec.num_cat else None, self.x0[sl], self.y[sl], self.idx[sl], batch=rows,
-                       num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
-                       embed_dim=spec.embed_dim, cursor_stride=batch, stream=st)
-        n += 1
+        if not skip_pre:
+            n += self._pre(batch, ds, row_idx, cursor, r0, rows)
         inp = self.x0[sl]
         for li, (k, o) in enumerate(dims):
             kk = self.k0 if li == 0 else k
@@ -230,6 +255,7 @@ class TrainStep:
         order = torch.arange(n_rows, dtype=torch.int64, device=self.dev)
         correct = torch.zeros((), dtype=torch.int64, device=self.dev)
         torch.cuda.synchronize(self.dev)
+        self._pre_ready = False                                  # x0 / y / idx are overwritten below
         with torch.cuda.stream(self.main):
             for s in range(0, n_rows, B):
                 b = min(B, n_rows - s)
@@ -241,8 +267,10 @@ class TrainStep:
 
     # --------------------------------------------------------------------------------------- the schedule
     def _enqueue(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
-                 cursor: Optional[torch.Tensor], advance: bool) -> int:
-        """Enqueue one full step on self.main for `batch` rows; returns the number of kernels launched."""
+                 cursor: Optional[torch.Tensor], advance: bool, prefetch: bool = False) -> int:
+        """Enqueue one full step on self.main for `batch` rows; returns the number of kernels launched.
+        prefetch: x0 / y / idx already hold this batch; K-pre of the NEXT batch is launched after the first optimizer
+        range instead (needs `cursor` and `advance`)."""
         spec, cfg, lay, st = self.spec, self.cfg, self.layout, self.main
         dims = spec.layer_dims
         L = self.L
@@ -252,10 +280,14 @@ class TrainStep:
         for bi, (_, _, ready) in enumerate(self.buckets):
             bucket_of.setdefault(ready, []).append(bi)
         chunks = self._chunks(batch)
+        reserve = 0
+        if cfg.world > 1 and cfg.overlap_comm:
+            reserve = DEFAULT_COMM_SM_RESERVE if cfg.comm_sm_reserve is None else cfg.comm_sm_reserve
+        comm_live = False
         for ci, (r0, rows) in enumerate(chunks):
             sl = slice(r0, r0 + rows)
             last_chunk = ci == len(chunks) - 1
-            n += self._forward(batch, src, row_idx, cursor, training=True, r0=r0, rows=rows)
+            n += self._forward(batch, src, row_idx, cursor, training=True, r0=r0, rows=rows, skip_pre=prefetch)
             # loss + dlogits + db_L (summed over the chunks) ---------------------------------------------------
             ops.ce_loss_grad(self.acts[-1][sl], self.y[sl], self.dlogits[sl], self.loss, self._b(L - 1, grad=True),
                              self.ce_scratch, batch=rows, num_classes=spec.num_classes,
@@ -287,6 +319,7 @@ class TrainStep:
                 if last_chunk:
                     for bi in bucket_of.get(-1, []):
                         n += self._reduce_bucket(bi)
+                        comm_live = True
             grouped = cfg.grouped_wgrad if cfg.grouped_wgrad is not None else cfg.world == 1
             xs = [self.x0[sl] if li == 0 else self.acts[li - 1][sl] for li in range(L)]
             # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
@@ -306,11 +339,17 @@ class TrainStep:
                 for li in range(L - 1, -1, -1):
                     k, o = dims[li]
                     kk = self.k0 if li == 0 else k
+                    # while an all-reduce is in flight the persistent GEMM grid leaves `reserve` SMs to NCCL's CTAs
+                    if reserve and comm_live:
+                        ops.set_sm_budget(self.sms - reserve)
                     ops.linear_wgrad(dys[li], xs[li], self._gw(li), M=rows, N=o, K=kk, accumulate=True, stream=st)
+                    if reserve and comm_live:
+                        ops.set_sm_budget(0)
                     n += 1
                     if last_chunk:
                         for bi in bucket_of.get(li, []):
                             n += self._reduce_bucket(bi)
+                            comm_live = True
         # optimizer ----------------------------------------------------------------------------------------
         # world > 1: one launch per bucket, each gated only by that bucket's all-reduce, so the update of the early
         # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer.
@@ -323,9 +362,16 @@ class TrainStep:
         else:
             ranges = [(None, 0, lay.total)]
         # the last optimizer launch also advances the device-side batch cursor / step count (its last block does)
-        adv = (self.cursor if advance else None, self.step_ctr, max(self.steps_per_epoch_full, 1), self.ticket)
+        # With `prefetch` the batch cursor moves in the FIRST launch (the range that holds the embedding tables, whose
+        # all-reduce was issued first), K-pre of the next batch follows it and runs under the all-reduces that are
+        # still in flight; the step counter (dropout stream, Adam's t) still moves in the last launch.
+        spe = max(self.steps_per_epoch_full, 1)
+        cur = self.cursor if advance else None
         for ri, (ev, s_, e_) in enumerate(ranges):
-            last_range = ri == len(ranges) - 1
+            first_range, last_range = ri == 0, ri == len(ranges) - 1
+            adv_cursor = cur if (first_range if prefetch else last_range) else None
+            adv_step = self.step_ctr if last_range else None
+            adv = (adv_cursor, adv_step, spe, self.ticket) if (adv_cursor is not None or adv_step is not None) else None
             if ev is not None:
                 st.wait_event(ev)
             ns = max(0, min(n_shadow, e_) - s_)
@@ -333,13 +379,20 @@ class TrainStep:
             if cfg.optimizer == "sgd":
                 ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
                              momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True,
-                             advance=adv if last_range else None, stream=st)
+                             advance=adv, stream=st)
             else:
                 ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, self.step_ctr,
                               n_shadow=ns, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                              weight_decay=cfg.weight_decay, zero_grad=True,
-                              advance=adv if last_range else None, stream=st)
+                              weight_decay=cfg.weight_decay, zero_grad=True, advance=adv, stream=st)
             n += 1
+            if prefetch and first_range:
+                # K-pre is a persistent grid too: leave SMs to the all-reduces it is meant to run under
+                pre_reserve = cfg.prefetch_sm_reserve if not last_range else 0
+                if pre_reserve:
+                    ops.set_sm_budget(self.sms - pre_reserve)
+                n += self._pre(batch, src or self.ds, row_idx, cursor)
+                if pre_reserve:
+                    ops.set_sm_budget(0)
         return n
 
     def _reduce_bucket(self, bi: int) -> int:
@@ -368,7 +421,8 @@ class TrainStep:
         self.comm_stream.synchronize()
         self.lib.graph_begin(self.main.cuda_stream)
         try:
-            self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
+            self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True,
+                                                  prefetch=self.prefetch)
         finally:
             out = C.c_void_p()
             self.lib.graph_end(self.main.cuda_stream, C.byref(out))
@@ -378,15 +432,17 @@ class TrainStep:
         """One optimizer step on the next full batch of this rank (asynchronous; see `loss_value`)."""
         if self.steps_per_epoch_full == 0:
             raise B200Error("batch_size larger than this rank's sample count: use step_tail()")
-        if self.cfg.use_graph:
-            if self.host_steps == 0:
-                self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
-            else:
-                if self.graph is None:
-                    self.capture()
-                self.lib.graph_launch(self.graph, self.main.cuda_stream)
+        bs = self.cfg.batch_size
+        if self.prefetch and not self._pre_ready:
+            # first step, or x0 / y / idx were overwritten by a tail batch, an evaluation or a host-fed step
+            self._pre(bs, self.ds, self.row_idx, self.cursor)
+        if self.cfg.use_graph and self.host_steps > 0:
+            if self.graph is None:
+                self.capture()
+            self.lib.graph_launch(self.graph, self.main.cuda_stream)
         else:
-            self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True)
+            self.kernels_per_step = self._enqueue(bs, None, self.row_idx, self.cursor, True, prefetch=self.prefetch)
+        self._pre_ready = self.prefetch
         self.host_steps += 1
 
     def step_tail(self) -> None:
@@ -395,6 +451,7 @@ class TrainStep:
         if self.tail == 0:
             return
         off = self.steps_per_epoch_full * self.cfg.batch_size
+        self._pre_ready = False
         self._enqueue(self.tail, None, self.row_idx[off:], None, False)
         self.host_steps += 1
 
@@ -456,6 +513,7 @@ class TrainStep:
             self._init_host_path()
         k = self._host_k
         self._host_k = (k + 1) % self.HOST_STAGES
+        self._pre_ready = False
         self.copy_stream.wait_event(self._stage_free[k])      # the step that last read this stage is done
         with torch.cuda.stream(self.copy_stream):
             self._stage_raw[k][: packed.numel()].copy_(packed, non_blocking=True)

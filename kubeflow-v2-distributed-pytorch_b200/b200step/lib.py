@@ -28,6 +28,7 @@ SIGNATURES = {
     "b200_last_error": (C.c_char_p, []),
     "b200_abi_version": (_i, []),
     "b200_device_sm_count": (_i, [C.POINTER(_i)]),
+    "b200_set_sm_budget": (_i, [_i]),
     "b200_preprocess": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _i, _i, _i64, _i, _i64, _i, _i64, _p]),
     "b200_linear_fwd": (_i, [_p, _i64, _p, _i64, _p, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _u64, _p, _i, _i64, _p, _i64,
                              _p]),

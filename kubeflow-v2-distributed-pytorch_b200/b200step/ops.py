@@ -160,6 +160,11 @@ def sm_count() -> int:
     return int(n.value)
 
 
+def set_sm_budget(sms: int) -> None:
+    """Size the persistent grids of the launches that follow for `sms` SMs (0 = all of them)."""
+    get_lib().set_sm_budget(int(sms))
+
+
 def zero(t, stream=None):
     _cuda(t)
     get_lib().zero(ptr(t), t.numel() * t.element_size(), _stream(stream))

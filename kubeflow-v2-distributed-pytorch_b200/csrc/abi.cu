@@ -16,7 +16,7 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-int sm_count() {
+int sm_count_physical() {
   static int cached = 0;
   if (cached > 0) return cached;
   int dev = 0, n = 0;
@@ -24,6 +24,13 @@ int sm_count() {
   if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
   cached = n;
   return n;
+}
+
+// SMs the persistent grids are sized for: the physical count unless b200_set_sm_budget lowered it.
+static int g_sm_budget = 0;
+int sm_count() {
+  const int n = sm_count_physical();
+  return (g_sm_budget > 0 && g_sm_budget < n) ? g_sm_budget : n;
 }
 
 bool pdl_enabled() {
@@ -48,6 +55,12 @@ extern "C" int b200_device_sm_count(int* out_host) {
   B200_CHECK_CUDA(cudaGetDevice(&dev));
   B200_CHECK_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
   *out_host = n;
+  return 0;
+}
+
+extern "C" int b200_set_sm_budget(int sms) {
+  B200_REQUIRE(sms >= 0, "SM budget must be >= 0 (0 = every SM of the device)");
+  g_sm_budget = (sms > 0 && sms < 2) ? 2 : sms;  // a CTA pair needs two
   return 0;
 }
 

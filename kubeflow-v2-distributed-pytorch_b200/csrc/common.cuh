@@ -30,7 +30,8 @@ void set_error(const char* fmt, ...);
     }                                   \
   } while (0)
 
-int sm_count();  // cached per process (current device at first call)
+int sm_count();           // SMs the persistent grids are sized for (b200_set_sm_budget), <= sm_count_physical()
+int sm_count_physical();  // cached per process (current device at first call)
 bool pdl_enabled();  // programmatic dependent launch (B200STEP_PDL=0 turns it off)
 // out[c] = sum_r partials[r * row_stride + c] for c < ncols, fixed order (defined in loss.cu)
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out, cudaStream_t st);

@@ -885,7 +885,7 @@ extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, in
 extern "C" int64_t b200_dgrad_scratch_floats(int64_t M, int64_t K) {
   (void)M;
   (void)K;
-  return (int64_t)sm_count() * 4 * BLOCK_N;
+  return (int64_t)sm_count_physical() * 4 * BLOCK_N;
 }
 
 extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx, float* dw,

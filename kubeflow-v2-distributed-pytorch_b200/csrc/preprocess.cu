@@ -18,8 +18,12 @@
 
 namespace b200 {
 
-constexpr int PRE_THREADS = 256;
-constexpr int PRE_WARPS = PRE_THREADS / 32;
+constexpr int PRE_THREADS = 256;   // default shape: 256-thread CTAs, four resident per SM
+// Budgeted shape (b200_set_sm_budget below the device's SM count): ONE 1024-thread CTA per SM, pinned there by a
+// shared-memory request nothing else fits beside, on `budget` SMs only.  The other SMs stay empty for the collective
+// this launch is meant to run under; with the default shape the block scheduler would spread the CTAs over every SM.
+constexpr int PRE_FAT_THREADS = 1024;
+constexpr int PRE_FAT_SMEM = 160 * 1024;
 
 // four fp32 values -> one aligned store in the output dtype
 __device__ __forceinline__ void store4(float* dst, uint4 raw) { stg_stream(dst, raw); }
@@ -31,8 +35,8 @@ __device__ __forceinline__ void store4(__nv_bfloat16* dst, uint4 raw) {
 __device__ __forceinline__ void store1(float* dst, float v) { *dst = v; }
 __device__ __forceinline__ void store1(__nv_bfloat16* dst, float v) { *dst = __float2bfloat16_rn(v); }
 
-template <typename OutT, typename IdT>
-__global__ void __launch_bounds__(PRE_THREADS, 4)
+template <typename OutT, typename IdT, int kThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
 preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds_cat,
                   const int64_t* __restrict__ ds_label, const int64_t* __restrict__ row_idx,
                   const int32_t* __restrict__ cursor, const float* __restrict__ mean,
@@ -48,6 +52,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
   const int vec_per_row = embed_dim >> 2;        // float4 chunks per table row
   const int emb_cols = num_cat * embed_dim;      // dense columns start here
   const int tail = (int)ldx - emb_cols;          // dense + zero padding
+  constexpr int PRE_WARPS = kThreads / 32;
   const long long stride = (long long)gridDim.x * PRE_WARPS;
   const float mu = lane < num_dense ? __ldg(mean + lane) : 0.f;  // num_dense <= 32 on the fast path
   const float sd = lane < num_dense ? __ldg(stdv + lane) : 1.f;
@@ -164,17 +169,35 @@ extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int ca
     vpr_shift = 0;
     while ((1 << vpr_shift) < vpr) ++vpr_shift;
   }
-  long long blocks = (batch + PRE_WARPS - 1) / PRE_WARPS;
-  const long long cap = (long long)sm_count() * 8;
+  const bool fat = sm_count() < sm_count_physical();
+  const int warps = (fat ? PRE_FAT_THREADS : PRE_THREADS) / 32;
+  long long blocks = (batch + warps - 1) / warps;
+  const long long cap = fat ? (long long)sm_count() : (long long)sm_count() * 8;
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   B200_REQUIRE(cat_id_bytes == 8 || cat_id_bytes == 4, "categorical ids must be int64 or int32 (cat_id_bytes=%d)",
                cat_id_bytes);
 #define B200_PRE_LAUNCH(OUT_T, ID_T)                                                                              \
-  B200_CHECK_CUDA(launch_pdl(preprocess_kernel<OUT_T, ID_T>, dim3(grid), dim3(PRE_THREADS), 0, st, ds_dense,     \
-                             static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor, mean, stdv, tables,    \
-                             static_cast<OUT_T*>(x_out), y_out, idx_out, batch, num_dense, num_cat, table_rows,  \
-                             embed_dim, vpr_shift, ldx, (long long)cursor_stride))
+  do {                                                                                                            \
+    if (fat) {                                                                                                    \
+      auto kern = preprocess_kernel<OUT_T, ID_T, PRE_FAT_THREADS, 1>;                                             \
+      static bool configured = false;                                                                             \
+      if (!configured) {                                                                                          \
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_FAT_SMEM));   \
+        configured = true;                                                                                        \
+      }                                                                                                           \
+      B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(PRE_FAT_THREADS), PRE_FAT_SMEM, st, ds_dense,            \
+                                 static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor, mean, stdv, tables, \
+                                 static_cast<OUT_T*>(x_out), y_out, idx_out, batch, num_dense, num_cat,           \
+                                 table_rows, embed_dim, vpr_shift, ldx, (long long)cursor_stride));               \
+    } else {                                                                                                      \
+      B200_CHECK_CUDA(launch_pdl(preprocess_kernel<OUT_T, ID_T, PRE_THREADS, 4>, dim3(grid), dim3(PRE_THREADS),   \
+                                 0, st, ds_dense, static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor,    \
+                                 mean, stdv, tables, static_cast<OUT_T*>(x_out), y_out, idx_out, batch,           \
+                                 num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx,                       \
+                                 (long long)cursor_stride));                                                      \
+    }                                                                                                             \
+  } while (0)
   if (x_dtype == B200_F32) {
     if (cat_id_bytes == 8) B200_PRE_LAUNCH(float, int64_t);
     else B200_PRE_LAUNCH(float, int32_t);

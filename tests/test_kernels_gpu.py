@@ -226,6 +226,48 @@ def test_preprocess_bit_exact(ops, dtype, batch, nd, nc, rows, dim, ldx):
     assert torch.equal(y, label[r])
 
 
+@pytest.mark.parametrize("budget", [116, 8, 2])
+def test_sm_budget_changes_grids_not_results(ops, budget):
+    """b200_set_sm_budget: K-pre switches to one fat CTA per budgeted SM, the GEMMs to fewer CTA pairs; outputs are
+    bit-identical to the full-device launch (wgrad: same split-K sums up to float atomics order)."""
+    g = torch.Generator().manual_seed(11)
+    batch, nd, nc, rows, dim, ldx = 5000, 13, 26, 1000, 16, 448
+    dense = (torch.randn(batch, nd, generator=g) * 3 + 1).cuda()
+    cat = torch.randint(0, rows, (batch, nc), generator=g).cuda()
+    label = torch.randint(0, 10, (batch,), generator=g).cuda()
+    mean, std = dense.mean(0).contiguous(), dense.std(0).contiguous()
+    tables = torch.randn(nc * rows * dim, generator=g).cuda()
+    row_idx = torch.randperm(batch, generator=g).cuda()
+    w = _rand((512, ldx), torch.bfloat16, 3, 0.05)
+    bias = _rand((512,), torch.float32, 4, 0.1)
+
+    def run():
+        x = torch.full((batch, ldx), float("nan"), dtype=torch.bfloat16, device="cuda")
+        y = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        idx = torch.full((batch, nc), -1, dtype=torch.int32, device="cuda")
+        ops.preprocess(dense, cat, label, row_idx, None, mean, std, tables, x, y, idx, batch=batch, num_dense=nd,
+                       num_cat=nc, table_rows=rows, embed_dim=dim)
+        h = torch.empty(batch, 512, dtype=torch.bfloat16, device="cuda")
+        ops.linear_fwd(x, w, bias, h, M=batch, N=512, K=ldx, relu=True)
+        dw = torch.zeros(512, ldx, dtype=torch.float32, device="cuda")
+        ops.linear_wgrad(h, x, dw, M=batch, N=512, K=ldx, accumulate=True)
+        torch.cuda.synchronize()
+        return x, y, idx, h, dw
+
+    full = run()
+    ops.set_sm_budget(budget)
+    try:
+        part = run()
+    finally:
+        ops.set_sm_budget(0)
+    for a, b in zip(full[:4], part[:4]):
+        assert torch.equal(a.view(torch.int16) if a.dtype == torch.bfloat16 else a,
+                           b.view(torch.int16) if b.dtype == torch.bfloat16 else b)
+    assert (full[4] - part[4]).abs().max().item() <= 1e-3 * full[4].abs().max().item()
+    again = run()                       # budget cleared: back to the default grids
+    assert torch.equal(again[0].view(torch.int16), full[0].view(torch.int16))
+
+
 # ------------------------------------------------------------------------------------------------- loss
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
 @pytest.mark.parametrize("batch,C", [(4096, 1000), (1000, 1000), (37, 16), (65536, 1000), (512, 1024)])

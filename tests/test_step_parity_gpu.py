@@ -158,6 +158,41 @@ def test_tail_batch_and_epoch_wraparound():
     assert _param_err(oracle, eng) <= 1e-2
 
 
+@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
+def test_prefetched_preprocess_schedule(optimizer):
+    """StepConfig.prefetch_pre (opt-in): K-pre of the next batch runs inside the current step, after the
+    embedding tables' optimizer launch.  Same results as the plain schedule across graph replay, a tail batch, an
+    evaluation and a host-fed step in between (each of which overwrites the prefetched batch)."""
+    spec = SMALL
+    rows, batch = 1400, 256
+    ds = make_synthetic(rows, spec)
+    idx = rank_indices(rows, 1, 0)
+    lr = 0.1 if optimizer == "sgd" else 1e-3
+    oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, precision="bf16", optimizer=optimizer, lr=lr)
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, idx,
+                    StepConfig(batch_size=batch, precision="bf16", optimizer=optimizer, lr=lr, prefetch_pre=True))
+    assert eng.prefetch
+    for epoch in range(3):
+        if epoch == 1:
+            acc = eng.evaluate()                       # forward-only pass over the dataset: clobbers x0
+            assert 0.0 <= acc <= 1.0
+        for b in range(6):
+            lo = oracle.step()[0]
+            if epoch == 2 and b == 2:                  # a host-fed step in the middle of an epoch
+                r = idx[b * batch:(b + 1) * batch]
+                t = eng.step_from_host(eng.pack_host_batch(ds.dense[r], ds.cat[r], ds.label[r]))
+                lg = eng.host_loss(t)
+                with torch.cuda.stream(eng.main):      # the host-fed step does not move the resident cursor
+                    eng.cursor += 1
+                eng.synchronize()
+            else:
+                eng.step() if b < 5 else eng.step_tail()
+                lg = eng.loss_value()
+            assert abs(lo - lg) <= 2e-3 * max(1.0, abs(lo)), (epoch, b, lo, lg)
+    assert int(eng.cursor.item()) == 0 and int(eng.step_ctr.item()) == 18
+    assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
+
+
 def test_dropout_step_matches_oracle():
     spec = dataclasses.replace(SMALL, dropout=0.25)
     ds, oracle, eng, lo, lg = _run_pair(spec, rows=1024, batch=256, steps=8, precision="bf16")
