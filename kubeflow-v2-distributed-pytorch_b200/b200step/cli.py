@@ -106,6 +106,9 @@ def build_parser() -> argparse.ArgumentParser:
                      help="also save the trained state_dict to <model_dir>/<model_filename>.final at the end "
                           "(the reference only ever saves before training an epoch, SURVEY.md App. B-8)")
     add.add_argument("--quiet_steps", action="store_true", help="suppress the per-step 'training with gpu' line")
+    add.add_argument("--set_epoch", action="store_true",
+                     help="reshuffle each epoch like DistributedSampler.set_epoch(epoch) would; the reference never "
+                          "calls it, so by default every epoch sees the same order (SURVEY.md App. B-4)")
     return parser
 
 
@@ -270,6 +273,8 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
                 print(f"Epoch: {epoch}, Accuracy: {accuracy}, Time: {epoch_middle}")
                 print("-" * 75)
 
+        if args.set_epoch and epoch > 0:
+            step.set_row_order(rank_indices(len(dataset), world, rank, epoch=epoch))
         for b in bounds:                                            # task.py:303
             if not args.quiet_steps:
                 print(f"training with gpu {args.gpu}")              # task.py:306 (host-side only, no device sync)

@@ -445,6 +445,16 @@ class TrainStep:
         self._pre_ready = self.prefetch
         self.host_steps += 1
 
+    def set_row_order(self, row_idx: torch.Tensor) -> None:
+        """`DistributedSampler.set_epoch` for the resident path: replace this rank's sample order (same length) in
+        place, so the captured graph keeps reading the same buffer.  The reference never calls set_epoch (SURVEY.md
+        App. B-4); `task.py --set_epoch` does, once per epoch, with the cursor back at batch 0."""
+        if row_idx.numel() != self.num_samples:
+            raise ValueError(f"sample order has {row_idx.numel()} entries, this rank holds {self.num_samples}")
+        with torch.cuda.stream(self.main):
+            self.row_idx.copy_(row_idx.to(torch.int64))
+        self._pre_ready = False
+
     def step_tail(self) -> None:
         """The last, partial batch of an epoch (DataLoader drop_last=False, task.py:263): eager launch with the
         smaller row count; does not move the full-batch cursor."""

@@ -50,6 +50,26 @@ def test_sampler_restatement_equals_torch_classes():
         rank_indices(10, 2, 2)
 
 
+def test_sampler_set_epoch_equals_torch():
+    """`task.py --set_epoch` (additive): epoch e's order == DistributedSampler.set_epoch(e)."""
+    from torch.utils.data.distributed import DistributedSampler
+
+    class _DS(torch.utils.data.Dataset):
+        def __len__(self):
+            return 1003
+
+        def __getitem__(self, i):
+            return i
+
+    for world in (1, 3, 8):
+        for rank in range(world):
+            smp = DistributedSampler(_DS(), num_replicas=world, rank=rank)
+            for epoch in (0, 1, 7):
+                smp.set_epoch(epoch)
+                assert list(smp) == rank_indices(1003, world, rank, epoch=epoch).tolist()
+    assert not torch.equal(rank_indices(1003, 1, 0, epoch=0), rank_indices(1003, 1, 0, epoch=1))
+
+
 def test_init_matches_module_construction_order():
     ds = make_synthetic(64, SMALL)
     tr = OracleTrainer(_sd(SMALL), ds, batch_size=32, seed=3)

@@ -193,6 +193,25 @@ def test_prefetched_preprocess_schedule(optimizer):
     assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
 
 
+def test_set_row_order_reshuffles_between_epochs():
+    """TrainStep.set_row_order (task.py --set_epoch): the graph-replayed step follows the new order."""
+    spec = SMALL
+    rows, batch = 1024, 256
+    ds = make_synthetic(rows, spec)
+    a = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(rows, 1, 0), StepConfig(batch_size=batch))
+    b = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(rows, 1, 0, epoch=1), StepConfig(batch_size=batch))
+    for _ in range(4):
+        a.step()                                   # epoch 0 on `a` only, in epoch-0 order
+    a.set_row_order(rank_indices(rows, 1, 0, epoch=1))
+    a.step()
+    b.step()
+    # first batch of the epoch-1 order went through K-pre on both engines: same rows, same labels
+    assert torch.equal(a.y, b.y) and torch.equal(a.idx, b.idx)
+    assert not torch.equal(rank_indices(rows, 1, 0)[:batch], rank_indices(rows, 1, 0, epoch=1)[:batch])
+    with pytest.raises(ValueError):
+        a.set_row_order(torch.arange(10))
+
+
 def test_dropout_step_matches_oracle():
     spec = dataclasses.replace(SMALL, dropout=0.25)
     ds, oracle, eng, lo, lg = _run_pair(spec, rows=1024, batch=256, steps=8, precision="bf16")
