@@ -106,6 +106,9 @@ def build_parser() -> argparse.ArgumentParser:
                      help="also save the trained state_dict to <model_dir>/<model_filename>.final at the end "
                           "(the reference only ever saves before training an epoch, SURVEY.md App. B-8)")
     add.add_argument("--quiet_steps", action="store_true", help="suppress the per-step 'training with gpu' line")
+    add.add_argument("--peer_optimizer", action="store_true",
+                     help="EXPERIMENTAL: gradient reduction + optimizer + parameter broadcast as one kernel per bucket "
+                          "over NVLink peer memory instead of NCCL all-reduce + optimizer (single node, <= 8 GPUs)")
     add.add_argument("--set_epoch", action="store_true",
                      help="reshuffle each epoch like DistributedSampler.set_epoch(epoch) would; the reference never "
                           "calls it, so by default every epoch sees the same order (SURVEY.md App. B-4)")
@@ -244,7 +247,8 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
 
     cfg = StepConfig(batch_size=batch_size, world=world, rank=rank, precision=args.precision,
                      optimizer=args.optimizer, lr=args.learning_rate, momentum=args.momentum,
-                     weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph)
+                     weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph,
+                     peer_optimizer=args.peer_optimizer)
     step = TrainStep(spec, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
 
     for epoch in range(num_epochs):

@@ -323,6 +323,43 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta)
       : "memory");
 }
 
+// Folded step bookkeeping: the LAST block of the optimizer grid to finish (a ticket counter tells) advances the
+// device-side batch cursor and step count, so the step needs no separate 1-thread kernel.  Every other block has
+// finished — hence has read *step — before the last one takes its ticket.
+struct StepAdvance {
+  int* cursor;
+  int* step;
+  int steps_per_epoch;
+  unsigned* ticket;  // nullptr: no bookkeeping in this launch
+};
+__device__ __forceinline__ void advance_if_last_block(const StepAdvance& a) {
+  if (a.ticket == nullptr) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned t = atomicAdd(a.ticket, 1u);
+    if (t == gridDim.x - 1) {
+      *a.ticket = 0u;
+      if (a.cursor) {
+        const int c = *a.cursor + 1;
+        *a.cursor = (c >= a.steps_per_epoch) ? 0 : c;
+      }
+      if (a.step) *a.step = *a.step + 1;
+    }
+  }
+}
+
+// w1 = (float)(1-beta1), w2 = (float)(1-beta2): formed in double on the host like torch's python scalars
+__device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v, float wd, float w1, float b2,
+                                          float w2, float eps, float step_size, float bc2_sqrt) {
+  g = __fmaf_rn(p, wd, g);                               // grad.add(param, alpha=wd)
+  m = __fmaf_rn(__fsub_rn(g, m), w1, m);                 // exp_avg.lerp_(grad, 1-beta1)
+  v = __fmaf_rn(__fmul_rn(g, g), w2, __fmul_rn(v, b2));  // mul_(beta2).addcmul_(g, g, 1-beta2)
+  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), bc2_sqrt), eps);
+  p = __fmaf_rn(__fdiv_rn(m, denom), -step_size, p);     // addcdiv_(m, denom, value=-step_size)
+  return p;
+}
+
 // ---- Philox4x32-10 (dropout mask; the CPU oracle regenerates the identical stream) ------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;

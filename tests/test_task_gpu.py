@@ -27,14 +27,15 @@ def _sd(spec):
     return d
 
 
-def _launch(ngpus, tmp, rows, batch, epochs, port, precision="bf16"):
+def _launch(ngpus, tmp, rows, batch, epochs, port, precision="bf16", extra=()):
     env = dict(os.environ)
     env.update({"WORLD_SIZE": "1", "RANK": "0", "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
                 "CUDA_VISIBLE_DEVICES": ",".join(str(i) for i in range(ngpus))})
     cmd = [sys.executable, os.path.join(ROOT, "task.py"), "--dist-url=env://", "--multiprocessing-distributed",
            f"--num_epochs={epochs}", "--local_training", "--arch", "tabular_mlp", "--hidden", "64,32",
            "--cardinality", str(CARD), "--num_classes", str(CLASSES), "--batch_size", str(batch),
-           "--synthetic_rows", str(rows), "--model_dir", str(tmp), "--save_final", "--precision", precision]
+           "--synthetic_rows", str(rows), "--model_dir", str(tmp), "--save_final", "--precision", precision,
+           *extra]
     return subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600, cwd=ROOT)
 
 
@@ -83,3 +84,26 @@ def test_task_py_two_gpus_matches_ddp_oracle(tmp_path):
     lg = float(re.search(r"final local loss \(rank 0\): ([0-9.eE+-]+)", r.stdout).group(1))
     assert abs(l0 - lg) <= 2e-3 * max(1.0, abs(l0))
     _compare(torch.load(os.path.join(tmp_path, "resnet_distributed.pth.final")), oracle, 1e-2)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2 or os.environ.get("B200STEP_TEST_PEER") != "1",
+                    reason="EXPERIMENTAL path: needs 2 GPUs and B200STEP_TEST_PEER=1 (the 2-rank run has not passed on "
+                           "hardware yet; the single-rank path is covered by test_peer_optimizer_single_rank)")
+@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
+def test_task_py_two_gpus_peer_optimizer(tmp_path, optimizer):
+    """--peer_optimizer (EXPERIMENTAL): the NVLink peer-memory reduce + update + broadcast kernel instead of NCCL
+    all-reduce + optimizer; same DDP semantics, same oracle, same tolerances."""
+    rows, batch, epochs = 2048 + 100, 256, 3          # 4 full batches + a partial one per rank and epoch
+    lr = "0.1" if optimizer == "sgd" else "0.001"
+    r = _launch(2, tmp_path, rows, batch, epochs, 29563 + (optimizer == "adam"),
+                extra=("--peer_optimizer", "--optimizer", optimizer, "--learning_rate", lr))
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
+    ds = make_synthetic(rows, SPEC)
+    oracle = OracleTrainer(_sd(SPEC), ds, world=2, batch_size=batch, precision="bf16", optimizer=optimizer,
+                           lr=float(lr))
+    for _ in range(epochs * oracle.steps_per_epoch):
+        l0 = oracle.step()[0]
+    lg = float(re.search(r"final local loss \(rank 0\): ([0-9.eE+-]+)", r.stdout).group(1))
+    assert abs(l0 - lg) <= 2e-3 * max(1.0, abs(l0))
+    _compare(torch.load(os.path.join(tmp_path, "resnet_distributed.pth.final")), oracle,
+             1e-2 if optimizer == "sgd" else 5e-2)
