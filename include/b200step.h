@@ -201,7 +201,7 @@ int b200_comm_destroy(void);
  * device pointers indexed by rank (entry `rank` = the local buffer).  `flags`: b200_peer_flag_words() uint32 per
  * rank, zero-initialised; slot s of rank q is written by the other ranks only.  Every bucket uses two slots
  * (gradients ready / slice done).  `step` is the device-side step counter shared with the rest of the step; flags
- * carry step+1.  `err` (device uint32, zero-initialised) receives 1+slot when a wait timed out after 10 s.
+ * carry step+1.  `err` (device uint32, zero-initialised) receives 1+slot when a wait timed out (120 s; B200STEP_PEER_TIMEOUT_S).
  *   b200_peer_signal   after the bucket's last gradient kernel: "my gradients of this bucket are complete"
  *   b200_peer_*_step   wait for every rank's ready flag, reduce + update + broadcast this rank's slice, flag done
  *   b200_peer_finish   wait for the done flags of all listed slots from all ranks, zero the local gradient buffer

@@ -620,7 +620,7 @@ class TrainStep:
             code = self.peer.error_code()
             if code:
                 raise B200Error(f"peer optimizer: a wait on flag slot {code - 1} timed out (a rank of the node died or "
-                                "fell more than 10 s behind)")
+                                "fell further behind than B200STEP_PEER_TIMEOUT_S, default 120 s)")
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """Same keys/shapes as the reference's `model.state_dict()` under DDP (task.py:283/287)."""

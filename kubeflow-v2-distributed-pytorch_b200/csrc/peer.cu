@@ -24,7 +24,7 @@
 //     every read of the weights (forward, dgrad chain, K-pre) precedes the first ready-flag; the next forward starts
 //     after the finishing kernel.
 // Flags carry the step number (+1) and only ever grow, so no reset races; every wait has a time-out that records an
-// error word instead of hanging the device.
+// error word instead of hanging the device (120 s by default).
 #include "common.cuh"
 
 namespace b200 {
@@ -32,7 +32,17 @@ namespace b200 {
 constexpr int PEER_MAX_WORLD = 8;
 constexpr int PEER_SLOTS = 64;          // flag slots per rank (two per bucket)
 constexpr int PEER_THREADS = 256;
-constexpr unsigned long long PEER_TIMEOUT_NS = 10ull * 1000ull * 1000ull * 1000ull;  // 10 s
+// How long a kernel polls a flag before it records an error and goes on: long enough for rank 0's evaluation +
+// checkpoint write while the other ranks already wait for it (task.py:279-297), B200STEP_PEER_TIMEOUT_S overrides.
+static unsigned long long peer_timeout_ns() {
+  static unsigned long long v = 0;
+  if (v == 0) {
+    const char* e = getenv("B200STEP_PEER_TIMEOUT_S");
+    const double s = (e && atof(e) > 0.0) ? atof(e) : 120.0;
+    v = (unsigned long long)(s * 1e9);
+  }
+  return v;
+}
 
 struct PeerTable {
   float* g[PEER_MAX_WORLD];
@@ -53,6 +63,7 @@ struct PeerOptArgs {
   float eps;
   unsigned* ticket;
   unsigned* err;
+  unsigned long long timeout_ns;
 };
 
 struct PeerSlots {
@@ -81,10 +92,11 @@ __device__ __forceinline__ float4 ld_peer4(const float* p) {
 }
 
 // thread `t` of the block polls flag `f` until it reaches `want` (wrap-safe); records the slot on time-out
-__device__ __forceinline__ void spin_until(const unsigned* f, unsigned want, unsigned* err, unsigned code) {
+__device__ __forceinline__ void spin_until(const unsigned* f, unsigned want, unsigned* err, unsigned code,
+                                           unsigned long long timeout_ns) {
   const unsigned long long t0 = globaltimer_ns();
   while ((int)(ld_acquire_sys(f) - want) < 0) {
-    if (globaltimer_ns() - t0 > PEER_TIMEOUT_NS) {
+    if (globaltimer_ns() - t0 > timeout_ns) {
       atomicExch(err, code);
       break;
     }
@@ -106,7 +118,8 @@ __global__ void __launch_bounds__(PEER_THREADS)
 peer_opt_kernel(const PeerTable t, const PeerOptArgs a) {
   const unsigned want = (unsigned)(*a.step) + 1u;
   if (threadIdx.x < t.world)
-    spin_until(t.flags[t.rank] + a.slot_ready * PEER_MAX_WORLD + threadIdx.x, want, a.err, 1u + a.slot_ready);
+    spin_until(t.flags[t.rank] + a.slot_ready * PEER_MAX_WORLD + threadIdx.x, want, a.err, 1u + a.slot_ready,
+               a.timeout_ns);
   __syncthreads();
 
   const long long n = a.end - a.start;
@@ -192,11 +205,11 @@ peer_opt_kernel(const PeerTable t, const PeerOptArgs a) {
 
 __global__ void __launch_bounds__(PEER_THREADS)
 peer_finish_kernel(const unsigned* flags_local, int world, const PeerSlots slots, const int* step, float* g,
-                   long long n, const StepAdvance adv, unsigned* err) {
+                   long long n, const StepAdvance adv, unsigned* err, unsigned long long timeout_ns) {
   const unsigned want = (unsigned)(*step) + 1u;
   for (int w = threadIdx.x; w < slots.count * world; w += blockDim.x) {
     const int s = slots.slot[w / world];
-    spin_until(flags_local + s * PEER_MAX_WORLD + (w % world), want, err, 1u + s);
+    spin_until(flags_local + s * PEER_MAX_WORLD + (w % world), want, err, 1u + s, timeout_ns);
   }
   __syncthreads();
   // every owner has read this rank's gradients: zero them for the next step's accumulation (optimizer.zero_grad())
@@ -243,6 +256,7 @@ static int peer_opt_launch(bool adam, void* const* g, void* const* p, void* cons
                "flag slots must be in [0, %d)", PEER_SLOTS);
   B200_REQUIRE(a.s1 != nullptr && a.step != nullptr && a.ticket != nullptr && a.err != nullptr &&
                    (!adam || a.s2 != nullptr), "optimizer state / step / ticket / err pointers must not be NULL");
+  a.timeout_ns = peer_timeout_ns();
   const long long n = a.end - a.start;
   const long long per = (((n + world - 1) / world) + 3) & ~3ll;
   long long blocks = ((per >> 2) + PEER_THREADS - 1) / PEER_THREADS;
@@ -363,7 +377,7 @@ extern "C" int b200_peer_finish(const void* flags_local, int world, const int32_
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   peer_finish_kernel<<<(unsigned)blocks, PEER_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const unsigned*>(flags_local), world, s, step, g, n, adv, err);
+      static_cast<const unsigned*>(flags_local), world, s, step, g, n, adv, err, peer_timeout_ns());
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
