@@ -26,6 +26,16 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+def slice_bounds(start: int, end: int, world: int, rank: int):
+    """[lo, hi) of the bucket [start, end) that `rank` reduces and updates — the same arithmetic as peer_opt_kernel
+    (csrc/peer.cu): `world` equal slices, each a multiple of 4 elements, the last one possibly shorter or empty."""
+    n = end - start
+    per = (((n + world - 1) // world) + 3) & ~3
+    lo = start + per * rank
+    hi = min(lo + per, end)
+    return (lo, max(lo, hi)) if lo < end else (end, end)
+
+
 class PeerBuffers:
     def __init__(self, total: int, n_shadow: int, rank: int, world: int, device: torch.device):
         lib = get_lib()
