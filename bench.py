@@ -13,6 +13,7 @@ Workloads (BASELINE.json configs):
                   the 1/2/4/8-GPU metric is quoted on (weak scaling: per-GPU batch fixed)
   t0_fp32_b4096   config 2: T0, fp32 storage / TF32 tensor cores, batch 4096, single GPU
   t1_bf16_b65536  config 4: widened MLP (4x1024, 26 x 65536 x 64 embeddings), bf16, batch 65536 per GPU
+  t0_fp32_b4096_cpu_gloo2  config 1 (`--impl reference` only): the oracle as real DDP over gloo, 2 CPU processes
 Timing: CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks.  The per-step
 working set (activations of a 65536-row batch, > 500 MB) is larger than the 126 MB L2, so no explicit flush.
 """
@@ -38,6 +39,9 @@ WORKLOADS = {
     "t0_fp32_b4096": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd"),
     "t1_bf16_b65536": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="sgd"),
     "t1_bf16_b65536_adam": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="adam"),
+    # BASELINE config 1 (CPU only, `--impl reference`): the oracle as real DistributedDataParallel over gloo,
+    # 2 processes x (host cores / 2) threads, 4096 rows per rank
+    "t0_fp32_b4096_cpu_gloo2": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd", cpu_gloo=2),
 }
 BATCHES_PER_RANK = 8          # distinct batches per rank, cycled (N = W*B*8 rows)
 REF_SAMPLE_CAP = 65536        # rows per step of the CPU arms (bounded sample)
@@ -146,9 +150,12 @@ def run_reference(args, rank):
 
     wl = WORKLOADS[args.workload]
     spec = ARCHS[wl["arch"]]
-    sample = min(wl["batch"] * args.gpus, REF_SAMPLE_CAP)
     steps = max(1, min(args.steps, 8))
     warm = max(1, min(args.warmup, 2))
+    if wl.get("cpu_gloo"):
+        _run_reference_gloo(args, wl, spec, steps, warm)
+        return
+    sample = min(wl["batch"] * args.gpus, REF_SAMPLE_CAP)
     r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, steps, warm, threads=os.cpu_count())
     out = {
         "impl": "reference", "metric": "train samples/sec", "value": r["samples_per_s"], "unit": "samples/s",
@@ -160,6 +167,37 @@ def run_reference(args, rank):
                          "sample": f"{steps} steps of {sample} rows (global batch capped at {REF_SAMPLE_CAP}), "
                                    f"fp32 torch CPU, host threads={r['cores']} of {os.cpu_count()} logical cpus"},
         "e2e": {"value": r["samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(out), flush=True)
+
+
+def _run_reference_gloo(args, wl, spec, steps, warm):
+    """Config 1: the oracle under torch's own DistributedDataParallel, gloo backend, one process per rank."""
+    import torch
+
+    from b200step.data import make_synthetic
+    from oracle.reference_step import run_ddp_gloo
+
+    world, B = wl["cpu_gloo"], wl["batch"]
+    threads = max(1, (os.cpu_count() or 2) // world)
+    sd = dataclasses.asdict(spec)
+    sd.pop("name")
+    ds = make_synthetic(world * B * 2, spec)
+    res = run_ddp_gloo(sd, ds, world=world, batch_size=B, steps=warm + steps, threads=threads,
+                       port=29500 + (os.getpid() % 400), time_it=True)[0]
+    times = res["times"][warm:]
+    sps = world * B * len(times) / sum(times)
+    out = {
+        "impl": "reference", "metric": "train samples/sec", "value": sps, "unit": "samples/s", "n_gpus": 0,
+        "steps": len(times), "warmup": warm, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "arch": wl["arch"], "per_rank_batch": B, "ranks": world,
+                   "backend": "gloo", "optimizer": wl["optimizer"]},
+        "cpu_baseline": {"value": sps, "unit": "samples/s", "cores": threads * world, "kind": "port",
+                         "sample": f"{len(times)} DDP steps of {world} x {B} rows, {world} processes x {threads} "
+                                   f"threads, torch {torch.__version__} CPU fp32 over gloo"},
+        "e2e": {"value": sps, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "final_loss": res["losses"][-1],
     }
     print(json.dumps(out), flush=True)
 
@@ -178,6 +216,8 @@ def run_b200(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     wl = WORKLOADS[args.workload]
+    if wl.get("cpu_gloo"):
+        raise SystemExit(f"--workload {args.workload} is the CPU/gloo baseline (config 1): run it with --impl reference")
     spec = ARCHS[wl["arch"]]
     B = wl["batch"]
     comm = None

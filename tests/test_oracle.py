@@ -186,3 +186,22 @@ def test_peer_slices_partition_every_bucket():
                 assert lo % 4 == 0 and (hi - lo) % 4 == 0 and lo <= hi <= end
                 pos = hi if hi > lo else pos
             assert pos == end
+
+
+def test_bench_reference_arm_config1_line():
+    """`bench.py --impl reference --workload t0_fp32_b4096_cpu_gloo2` (BASELINE config 1: the oracle under real DDP over
+    gloo, 2 CPU processes) prints one JSON line with the reference arm's keys."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--workload",
+                        "t0_fp32_b4096_cpu_gloo2", "--steps", "1", "--warmup", "1"], capture_output=True, text=True,
+                       timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["impl"] == "reference" and line["unit"] == "samples/s" and line["value"] > 0
+    assert line["config"]["ranks"] == 2 and line["config"]["backend"] == "gloo"
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
