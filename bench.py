@@ -202,6 +202,68 @@ def _run_reference_gloo(args, wl, spec, steps, warm):
     print(json.dumps(out), flush=True)
 
 
+# --------------------------------------------------------------------------------------------- parity leg
+PARITY_LOSS_REL = 2e-3      # same bars as tests/test_step_parity_gpu.py (bf16 path against the bf16-storage oracle)
+PARITY_PARAM_REL_L2 = 1e-2
+
+
+def parity_check(rank, world, dev, comm, dist):
+    """Correctness evidence printed with every bench line, OUTSIDE the timed region: 4 steps (eager, then graph
+    capture + replay) of a T0-shaped model through the same TrainStep / Communicator / bucket schedule as the
+    measured run, against OracleTrainer(world=N) on rank 0 (the oracle here is the checker, never the thing
+    measured).  The tables are cut to 100 rows and the batch to 512 rows per rank so that the CPU side takes
+    seconds; layer widths (448/512/512/1000) and hence the gradient buckets are T0's."""
+    import torch
+
+    from b200step.data import make_synthetic
+    from b200step.engine import StepConfig, TrainStep
+    from b200step.model import ARCHS, init_parameters
+    from b200step.sampler import rank_indices
+
+    spec = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=100)
+    B, steps = 512, 4
+    rows = world * B * 2
+    ds = make_synthetic(rows, spec)
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(rows, world, rank),
+                    StepConfig(batch_size=B, world=world, rank=rank, precision="bf16"), comm, device=dev)
+    losses = []
+    for _ in range(steps):
+        eng.step()
+        losses.append(eng.loss_value())
+    eng.synchronize()
+    flat = eng.p.detach().clone()
+    mine = torch.tensor(losses, dtype=torch.float64, device=dev)
+    layout, n_buckets = eng.layout, len(eng.buckets)
+    eng.close()
+    identical, all_losses = True, [mine]
+    if world > 1:
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        identical = all(torch.equal(g, gathered[0]) for g in gathered)
+        all_losses = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(all_losses, mine)
+    if rank != 0:
+        return None
+    from oracle.reference_step import OracleTrainer
+
+    sd = dataclasses.asdict(spec)
+    sd.pop("name")
+    oracle = OracleTrainer(sd, ds, world=world, batch_size=B, precision="bf16")
+    loss_rel = 0.0
+    for s in range(steps):
+        ref = oracle.step()                     # one local loss per rank (task.py:310 on that rank)
+        for r in range(world):
+            loss_rel = max(loss_rel, abs(ref[r] - float(all_losses[r][s])) / max(1.0, abs(ref[r])))
+    so, sg = oracle.state_dict(), layout.unflatten(flat)
+    param_rel = max(((so[k] - sg[k]).norm() / so[k].norm().clamp_min(1e-12)).item() for k in so)
+    ok = bool(identical and loss_rel <= PARITY_LOSS_REL and param_rel <= PARITY_PARAM_REL_L2)
+    return {"ok": ok, "loss_rel_max": loss_rel, "param_rel_l2_max": param_rel, "ranks_bit_identical": bool(identical),
+            "steps": steps, "world": world, "gradient_buckets": n_buckets,
+            "model": "T0 layer widths, 26 x 100 x 16 tables, 512 rows per rank, bf16, SGD",
+            "against": "OracleTrainer(world=N) on rank 0 (oracle/reference_step.py)",
+            "tolerance": {"loss_rel": PARITY_LOSS_REL, "param_rel_l2": PARITY_PARAM_REL_L2}}
+
+
 # --------------------------------------------------------------------------------------------- GPU arm
 def run_b200(args, rank, local_rank, world):
     import torch
@@ -230,6 +292,8 @@ def run_b200(args, rank, local_rank, world):
         uid = [Communicator.make_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         comm = Communicator(rank, world, uid[0])
+
+    parity = None if args.no_parity else parity_check(rank, world, dev, comm, dist)
 
     rows = world * B * BATCHES_PER_RANK
     ds = make_synthetic(rows, spec, zipf_alpha=args.zipf_alpha)
@@ -362,6 +426,8 @@ def run_b200(args, rank, local_rank, world):
         "roofline": roof, "roofline_hbm": roof_hbm, "kernels": prof, "step_tflops_per_gpu": step_tflops,
         "final_loss": loss_after,
     }
+    if parity is not None:
+        out["parity"] = parity
     if world == 1 and not args.no_cpu_baseline:
         sample = min(B, REF_SAMPLE_CAP)
         r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, 5, 2)
@@ -371,6 +437,8 @@ def run_b200(args, rank, local_rank, world):
     print(json.dumps(out), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit(f"parity check failed: {json.dumps(parity)}")
 
 
 def profile_kernels(eng, spec, B, world):
@@ -457,6 +525,8 @@ def main():
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="t0_bf16_b65536")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--no-parity", dest="no_parity", action="store_true",
+                    help="skip the parity leg (4 small steps against the CPU oracle, outside the timed region)")
     ap.add_argument("--zipf-alpha", dest="zipf_alpha", type=float, default=None,
                     help="categorical ids ~ Zipf(alpha) instead of uniform (SURVEY.md §8d secondary dataset row)")
     args = ap.parse_args()

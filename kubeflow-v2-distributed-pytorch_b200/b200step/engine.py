@@ -266,12 +266,14 @@ class TrainStep:
             inp = self.acts[li][sl]
         return n
 
-    def evaluate(self) -> float:
+    def evaluate(self, return_predictions: bool = False):
         """Top-1 accuracy over the whole resident dataset in its stored order (the reference's evaluate(),
-        task.py:30-46, over a shuffle=False loader, task.py:267): forward only, eval mode (no dropout)."""
+        task.py:30-46, over a shuffle=False loader, task.py:267): forward only, eval mode (no dropout).
+        `return_predictions` also hands back each row's predicted class (`predicted` at task.py:40)."""
         n_rows, B = len(self.ds), self.cfg.batch_size
         order = torch.arange(n_rows, dtype=torch.int64, device=self.dev)
         correct = torch.zeros((), dtype=torch.int64, device=self.dev)
+        preds = torch.empty(n_rows, dtype=torch.int64, device=self.dev) if return_predictions else None
         torch.cuda.synchronize(self.dev)
         self._pre_ready = False                                  # x0 / y / idx are overwritten below
         with torch.cuda.stream(self.main):
@@ -280,8 +282,11 @@ class TrainStep:
                 self._forward(b, None, order[s:], None, training=False)
                 pred = self.acts[-1][:b].argmax(dim=1)          # torch.max(outputs, 1), task.py:40
                 correct += (pred == self.y[:b]).sum()           # task.py:42
+                if preds is not None:
+                    preds[s: s + b] = pred
         self.main.synchronize()
-        return correct.item() / n_rows
+        acc = correct.item() / n_rows
+        return (acc, preds.cpu()) if return_predictions else acc
 
     # --------------------------------------------------------------------------------------- the schedule
     def _enqueue(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,

@@ -33,6 +33,11 @@ GEMM_SHAPES = [
     (4096, 1000, 512),    # ragged N (output layer: 1000 classes)
     (333, 1000, 448),
     (4096, 512, 448),
+    # T1 (`tabular_mlp_wide`, BASELINE config 4): 16 and 27 k-blocks against the 6-stage operand ring
+    (4096, 1024, 1728),
+    (4096, 1024, 1024),
+    (4096, 1000, 1024),
+    (333, 1024, 1728),
 ]
 
 
@@ -96,7 +101,7 @@ def test_linear_wgrad(ops, dtype, M, N, K):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
-@pytest.mark.parametrize("M,N,K", [(1000, 512, 448), (4096, 1000, 512), (65536, 512, 512)])
+@pytest.mark.parametrize("M,N,K", [(1000, 512, 448), (4096, 1000, 512), (65536, 512, 512), (4096, 1024, 1728)])
 def test_relu_bitmask_and_fused_bias_grad(ops, dtype, M, N, K):
     """fwd writes 1 bit per output (y > 0); the next layer's dgrad consumes it instead of re-reading the
     activation, and emits the column sums of what it stores (= bias gradient of the layer below)."""
@@ -133,11 +138,15 @@ def test_relu_bitmask_and_fused_bias_grad(ops, dtype, M, N, K):
     torch.testing.assert_close(db3, db, rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
 
 
+T0_LAYERS = [(1000, 512), (512, 512), (512, 448)]                                        # (N, K), output layer first
+T1_LAYERS = [(1000, 1024), (1024, 1024), (1024, 1024), (1024, 1024), (1024, 1728)]     # five problems in one launch
+
+
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
-@pytest.mark.parametrize("M", [4096, 65536, 1000])
-def test_linear_wgrad_grouped(ops, dtype, M):
+@pytest.mark.parametrize("M,shapes", [(4096, T0_LAYERS), (65536, T0_LAYERS), (1000, T0_LAYERS), (4096, T1_LAYERS),
+                                      (333, T1_LAYERS)], ids=["t0-4096", "t0-65536", "t0-1000", "t1-4096", "t1-333"])
+def test_linear_wgrad_grouped(ops, dtype, M, shapes):
     """All layers' weight gradients in one launch == the per-layer kernel (same tiles, same arithmetic)."""
-    shapes = [(1000, 512), (512, 512), (512, 448)]   # (N, K) of T0's three Linear layers
     dys = [_rand((M, n), dtype, 70 + i, 0.1) for i, (n, k) in enumerate(shapes)]
     xs = [_rand((M, k), dtype, 80 + i) for i, (n, k) in enumerate(shapes)]
     dws = [torch.zeros((n, k), dtype=torch.float32, device="cuda") for (n, k) in shapes]
