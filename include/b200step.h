@@ -41,6 +41,17 @@ int b200_device_sm_count(int* out_host);     /* SM count of the current device *
  * (task.py:189).  Here a collective on another stream needs free SMs, otherwise its CTAs wait for a grid boundary
  * and then push part of the next persistent grid into a second wave.  Results do not depend on the budget. */
 int b200_set_sm_budget(int sms);
+/* Where later launches report input that torch would have rejected with an exception (the kernels cannot raise):
+ * a zero-initialised uint32 in device memory onto which they OR the bits below; NULL (the default) turns reporting
+ * off.  The host reads the word whenever it synchronises anyway.  Offending values are made harmless first:
+ *   B200_STATUS_BAD_CATEGORICAL_ID  b200_preprocess met an id outside [0, table_rows) (nn.Embedding raises
+ *                                   IndexError): that id is replaced by row 0;
+ *   B200_STATUS_BAD_LABEL           b200_ce_loss_grad / b200_linear_ce met a label outside [0, num_classes) that is
+ *                                   not ignore_index (nn.CrossEntropyLoss raises): that row is dropped like an
+ *                                   ignored one. */
+#define B200_STATUS_BAD_CATEGORICAL_ID 1u
+#define B200_STATUS_BAD_LABEL 2u
+int b200_set_status_word(uint32_t* device_word);
 
 /* ---- K-pre: fused batch load + standardise + categorical gather ---------------------------
  * Replaces the reference's host-side input pipeline for one batch:
@@ -58,13 +69,17 @@ int b200_set_sm_budget(int sms);
  * cursor may be NULL (treated as 0); it is read on the device so a captured graph can be replayed.  The batch is
  * rows row_idx[*cursor * cursor_stride + b], b < batch; cursor_stride <= 0 means `batch` (a step may be processed
  * in several row chunks: each call then gets row_idx advanced by its chunk offset and cursor_stride = full batch).
+ * label_stats (nullable): 4 zero-initialised int32 of device memory; after the kernel, label_stats[0] = number of
+ * rows of this batch whose label != ignore_index (what nn.CrossEntropyLoss's mean divides by, loss.py:1379-1387);
+ * words 1..3 are the kernel's own accumulator / ticket and return to zero, so a captured graph can be replayed.
  */
 int b200_preprocess(const float* ds_dense, const void* ds_cat, int cat_id_bytes, const int64_t* ds_label,
                     const int64_t* row_idx, const int32_t* cursor,
                     const float* mean, const float* std, const float* tables,
                     void* x_out, int64_t* y_out, int32_t* idx_out,
                     int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
-                    int64_t ldx, int x_dtype, int64_t cursor_stride, b200_stream_t stream);
+                    int64_t ldx, int x_dtype, int64_t cursor_stride, int32_t* label_stats, int64_t ignore_index,
+                    b200_stream_t stream);
 
 /* ---- K-gemm: tcgen05/TMEM linear layers ----------------------------------------------------
  * M = batch rows, N = out_features, K = in_features for all three.
@@ -112,13 +127,18 @@ int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx,
  * scratch: b200_ce_scratch_floats(C) floats of device memory, contents need not be initialised.
  * loss_scale <= 0 means 1/batch; accumulate != 0 adds loss and dbias onto the existing values (a batch processed in
  * row chunks: grad_scale = 1/(full batch * world), loss_scale = 1/full batch, accumulate on every chunk but the first).
+ * ignore_index (torch's default: -100): rows with that label add neither loss nor gradient (their dlogits row is 0).
+ * n_valid (nullable): device int32 = number of rows of the batch whose label != ignore_index (label_stats[0] of
+ * b200_preprocess); when given, loss and gradient are divided by it instead of by `batch` (torch's mean over the
+ * non-ignored targets; 0 valid rows -> loss NaN, gradient 0, like torch).  With NULL the divisor stays `batch`.
+ * A label outside [0, num_classes) that is not ignore_index sets B200_STATUS_BAD_LABEL and is treated as ignored.
  */
 int64_t b200_ce_scratch_floats(int num_classes);
 int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels,
                       void* dlogits, int64_t lddl, float* loss_out, float* dbias,
                       float* scratch, int64_t scratch_floats,
                       int64_t batch, int num_classes, float grad_scale, float loss_scale, int accumulate,
-                      int dtype, b200_stream_t stream);
+                      int64_t ignore_index, const int32_t* n_valid, int dtype, b200_stream_t stream);
 
 /* ---- column sum: bias gradients of the hidden layers (task.py:311, addmm backward wrt bias) -
  * out[N] = sum_m dy[m, :]  (fp32, deterministic two-stage reduction through scratch) */

@@ -86,8 +86,9 @@ def build_parser() -> argparse.ArgumentParser:
     # ---- additive flags (defaults = reference behaviour) ----
     add = parser.add_argument_group("B200 step (additive)")
     add.add_argument("--optimizer", choices=["sgd", "adam"], default="sgd")
-    add.add_argument("--precision", choices=["bf16", "fp32"], default="bf16",
-                     help="bf16 storage + fp32 accumulate/master weights, or fp32 storage + TF32 tensor cores")
+    add.add_argument("--precision", choices=["fp32", "tf32", "bf16"], default="fp32",
+                     help="fp32 (default: the reference trains in fp32, task.py:309): fp32 storage; tf32: fp32 storage, "
+                          "single-pass TF32 tensor-core products; bf16: bf16 storage + fp32 accumulate / master weights")
     add.add_argument("--dropout", type=float, default=0.0)
     add.add_argument("--synthetic_rows", type=int, default=10000,
                      help="rows of the synthetic tabular dataset (the reference's CIFAR-10 test split has 10000)")
@@ -106,9 +107,6 @@ def build_parser() -> argparse.ArgumentParser:
                      help="also save the trained state_dict to <model_dir>/<model_filename>.final at the end "
                           "(the reference only ever saves before training an epoch, SURVEY.md App. B-8)")
     add.add_argument("--quiet_steps", action="store_true", help="suppress the per-step 'training with gpu' line")
-    add.add_argument("--peer_optimizer", action="store_true",
-                     help="EXPERIMENTAL: gradient reduction + optimizer + parameter broadcast as one kernel per bucket "
-                          "over NVLink peer memory instead of NCCL all-reduce + optimizer (single node, <= 8 GPUs)")
     add.add_argument("--set_epoch", action="store_true",
                      help="reshuffle each epoch like DistributedSampler.set_epoch(epoch) would; the reference never "
                           "calls it, so by default every epoch sees the same order (SURVEY.md App. B-4)")
@@ -248,7 +246,9 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
     cfg = StepConfig(batch_size=batch_size, world=world, rank=rank, precision=args.precision,
                      optimizer=args.optimizer, lr=args.learning_rate, momentum=args.momentum,
                      weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph,
-                     peer_optimizer=args.peer_optimizer)
+                     # K-opt-peer stays behind an environment variable until its multi-rank parity test has passed
+                     # on hardware
+                     peer_optimizer=os.environ.get("B200STEP_PEER_OPT") == "1")
     step = TrainStep(spec, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
 
     for epoch in range(num_epochs):
@@ -286,6 +286,9 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
                 step.step()
             else:
                 step.step_tail()                                    # drop_last=False: the partial last batch
+        # once per epoch, on every rank: surface device-side reports (bad ids / labels, peer-flag time-outs) instead
+        # of training on for epochs with neutralised input
+        step.synchronize()
 
     step.synchronize()
     epoch_end = datetime.now().strftime("%Y_%m_%d_%H_%M_%S")

@@ -67,9 +67,10 @@ class StepConfig:
                                          # bucket's all-reduce start earlier when world > 1
 
 
-# SMs the GEMMs that run while an all-reduce is in flight leave free (B200_FLAG_SM_RESERVE).  The GEMM grids are
-# persistent and sized for every SM: when NCCL's CTAs take some, the displaced GEMM CTAs become a second wave.
-# Measured with scripts/gpu_allreduce_sweep.py (profiles/r01_allreduce_reserve_matrix_w2.md).
+# SMs the GEMMs that run while an all-reduce is in flight leave free (b200_set_sm_budget around those launches).  The
+# GEMM grids are persistent and sized for every SM: when NCCL's CTAs take some, the displaced GEMM CTAs become a
+# second wave.  Measured with scripts/gpu_allreduce_sweep.py (profiles/r01_comm_overlap_experiments.md): leaving SMs
+# free cost more than it recovered on T0, hence 0.
 DEFAULT_COMM_SM_RESERVE = 0
 
 
@@ -106,8 +107,8 @@ class TrainStep:
                  device: Optional[torch.device] = None):
         if not torch.cuda.is_available():
             raise B200Error("no CUDA device: the B200 training step has no CPU fallback")
-        if cfg.precision not in ("bf16", "fp32"):
-            raise ValueError(f"precision must be bf16 or fp32, got {cfg.precision}")
+        if cfg.precision not in ("bf16", "fp32", "tf32"):
+            raise ValueError(f"precision must be bf16, fp32 or tf32, got {cfg.precision}")
         if cfg.optimizer not in ("sgd", "adam"):
             raise ValueError(f"optimizer must be sgd or adam, got {cfg.optimizer}")
         if cfg.world > 1 and comm is None:
@@ -170,6 +171,10 @@ class TrainStep:
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)   # last-block detector of the optimizer launch
+        # [0] = rows of the current batch whose label != ignore_index (K-pre counts, K-loss divides by it)
+        self.label_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        # bits the kernels set when they meet an id / label torch would have raised on (checked in synchronize())
+        self.status = ops.status_word(dev)
         self.ce_scratch = torch.empty(ops.ce_scratch_floats(spec.num_classes), dtype=torch.float32, device=dev)
         # 1 bit per hidden activation (ReLU/dropout mask for backward), row stride padded to 16 bytes
         self.masks = [torch.zeros(B, ((o + 31) // 32 + 3) // 4 * 4, dtype=torch.int32, device=dev)
@@ -238,7 +243,8 @@ class TrainStep:
         ops.preprocess(ds.dense, ds.cat, ds.label, row_idx[r0:], cursor, ds.mean, ds.std,
                        self.tables if spec.num_cat else None, self.x0[sl], self.y[sl], self.idx[sl], batch=rows,
                        num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
-                       embed_dim=spec.embed_dim, cursor_stride=batch, stream=self.main)
+                       embed_dim=spec.embed_dim, cursor_stride=batch,
+                       label_stats=self.label_stats if rows == batch else None, stream=self.main)
         return 1
 
     def _forward(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
@@ -315,7 +321,7 @@ class TrainStep:
             ops.ce_loss_grad(self.acts[-1][sl], self.y[sl], self.dlogits[sl], self.loss, self._b(L - 1, grad=True),
                              self.ce_scratch, batch=rows, num_classes=spec.num_classes,
                              grad_scale=1.0 / (batch * cfg.world), loss_scale=1.0 / batch, accumulate=ci > 0,
-                             stream=st)
+                             n_valid=self.label_stats if len(chunks) == 1 else None, stream=st)
             n += 2
             # backward ------------------------------------------------------------------------------------------
             # Phase 1 walks the dgrad chain down to the embedding gradient, phase 2 runs the wgrad GEMMs.  The table
@@ -621,6 +627,17 @@ class TrainStep:
     def synchronize(self) -> None:
         self.main.synchronize()
         self.comm_stream.synchronize()
+        bits = int(self.status.item())
+        if bits:
+            self.status.zero_()
+            what = []
+            if bits & ops.STATUS_BAD_CATEGORICAL_ID:
+                what.append(f"a categorical id outside [0, {self.spec.cardinality}) (nn.Embedding raises IndexError)")
+            if bits & ops.STATUS_BAD_LABEL:
+                what.append(f"a label outside [0, {self.spec.num_classes}) that is not ignore_index "
+                            "(nn.CrossEntropyLoss raises)")
+            raise B200Error("the step met " + " and ".join(what) + "; the offending rows were neutralised on the "
+                            "device (id -> row 0, label -> ignored) but the input is invalid")
         if self.peer is not None:
             code = self.peer.error_code()
             if code:

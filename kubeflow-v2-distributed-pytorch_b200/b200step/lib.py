@@ -29,7 +29,9 @@ SIGNATURES = {
     "b200_abi_version": (_i, []),
     "b200_device_sm_count": (_i, [C.POINTER(_i)]),
     "b200_set_sm_budget": (_i, [_i]),
-    "b200_preprocess": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _i, _i, _i64, _i, _i64, _i, _i64, _p]),
+    "b200_set_status_word": (_i, [_p]),
+    "b200_preprocess": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _i, _i, _i64, _i, _i64, _i, _i64, _p,
+                             _i64, _p]),
     "b200_linear_fwd": (_i, [_p, _i64, _p, _i64, _p, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _u64, _p, _i, _i64, _p, _i64,
                              _p]),
     "b200_linear_dgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _p, _i64, _p,
@@ -38,7 +40,7 @@ SIGNATURES = {
     "b200_dgrad_scratch_floats": (_i64, [_i64, _i64]),
     "b200_linear_wgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _p]),
     "b200_ce_scratch_floats": (_i64, [_i]),
-    "b200_ce_loss_grad": (_i, [_p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i, _f, _f, _i, _i, _p]),
+    "b200_ce_loss_grad": (_i, [_p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i, _f, _f, _i, _i64, _p, _i, _p]),
     "b200_colsum_scratch_floats": (_i64, [_i64]),
     "b200_colsum": (_i, [_p, _i64, _p, _p, _i64, _i64, _i64, _i, _p]),
     "b200_colsum_static": (_i, [_p, _i64, _p, _i64, _i64, _i, _p]),

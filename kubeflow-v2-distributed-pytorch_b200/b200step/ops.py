@@ -43,13 +43,13 @@ def _cuda(*ts):
 
 def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x_out, y_out, idx_out, *,
                batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, cursor_stride: int = 0,
-               stream=None):
-    _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out)
+               label_stats=None, ignore_index: int = -100, stream=None):
+    _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out, label_stats)
     get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ds_cat.element_size() if ds_cat is not None else 8,
                          ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
                          ptr(std), ptr(tables), ptr(x_out), ptr(y_out), ptr(idx_out), batch, num_dense,
                          num_cat, table_rows, embed_dim, x_out.stride(0), dtype_code(x_out.dtype),
-                         cursor_stride, _stream(stream))
+                         cursor_stride, ptr(label_stats), int(ignore_index), _stream(stream))
 
 
 def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,
@@ -99,12 +99,13 @@ def ce_scratch_floats(num_classes: int) -> int:
 
 
 def ce_loss_grad(logits, labels, dlogits, loss_out, dbias, scratch, *, batch: int, num_classes: int,
-                 grad_scale: float, loss_scale: float = 0.0, accumulate: bool = False, stream=None):
-    _cuda(logits, labels, dlogits, loss_out, dbias, scratch)
+                 grad_scale: float, loss_scale: float = 0.0, accumulate: bool = False, ignore_index: int = -100,
+                 n_valid=None, stream=None):
+    _cuda(logits, labels, dlogits, loss_out, dbias, scratch, n_valid)
     get_lib().ce_loss_grad(ptr(logits), logits.stride(0), ptr(labels), ptr(dlogits), dlogits.stride(0),
                            ptr(loss_out), ptr(dbias), ptr(scratch), scratch.numel(), batch, num_classes,
-                           float(grad_scale), float(loss_scale), int(accumulate), dtype_code(logits.dtype),
-                           _stream(stream))
+                           float(grad_scale), float(loss_scale), int(accumulate), int(ignore_index), ptr(n_valid),
+                           dtype_code(logits.dtype), _stream(stream))
 
 
 def colsum_scratch_floats(n: int) -> int:
@@ -158,6 +159,26 @@ def sm_count() -> int:
     n = C.c_int(0)
     get_lib().device_sm_count(C.byref(n))
     return int(n.value)
+
+
+STATUS_BAD_CATEGORICAL_ID = 1
+STATUS_BAD_LABEL = 2
+
+
+_status_words = {}
+
+
+def status_word(device=None) -> torch.Tensor:
+    """The process-wide status word of `device` (one int32, allocated once and registered with the library): kernels
+    OR the B200_STATUS_* bits onto it (include/b200step.h).  One device per process is the rule here (task.py:124
+    spawns one process per GPU); a second device gets its own word and re-registers."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    w = _status_words.get(dev)
+    if w is None:
+        w = torch.zeros(1, dtype=torch.int32, device=dev)
+        _status_words[dev] = w
+    get_lib().set_status_word(ptr(w))
+    return w
 
 
 def set_sm_budget(sms: int) -> None:

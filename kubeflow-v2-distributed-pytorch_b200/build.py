@@ -38,7 +38,7 @@ def _nvcc() -> str:
     return cand if os.path.exists(cand) else "nvcc"
 
 
-def _flags(verbose: bool) -> list[str]:
+def _flags(verbose: bool, experiments: bool = False) -> list[str]:
     f = [
         "-std=c++17", "-O3", "-lineinfo",
         "-gencode", "arch=compute_100a,code=sm_100a",
@@ -47,6 +47,8 @@ def _flags(verbose: bool) -> list[str]:
     ]
     if verbose:
         f += ["-Xptxas", "-v"]
+    if experiments or os.environ.get("B200STEP_BUILD_EXPERIMENTS") == "1":
+        f += ["-DB200STEP_EXPERIMENTS"]   # timing knobs inside the GEMM (results are wrong when they are switched on)
     return f
 
 
@@ -59,11 +61,11 @@ def _stamp(srcs: list[str], flags: list[str]) -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, experiments: bool = False) -> str:
     os.makedirs(BUILD, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
     sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    flags = _flags(verbose)
+    flags = _flags(verbose, experiments)
     deps = [os.path.join(CSRC, s) for s in sources] + [
         os.path.join(CSRC, "common.cuh"),
         os.path.join(HERE, "..", "include", "b200step.h"),
@@ -102,5 +104,6 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--experiments", action="store_true", help="compile the GEMM timing knobs in (never ship this)")
     a = ap.parse_args()
-    print(build(force=a.force, verbose=a.verbose))
+    print(build(force=a.force, verbose=a.verbose, experiments=a.experiments))

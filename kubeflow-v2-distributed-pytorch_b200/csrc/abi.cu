@@ -33,6 +33,9 @@ int sm_count() {
   return (g_sm_budget > 0 && g_sm_budget < n) ? g_sm_budget : n;
 }
 
+static uint32_t* g_status_word = nullptr;
+uint32_t* status_word() { return g_status_word; }
+
 bool pdl_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -61,6 +64,11 @@ extern "C" int b200_device_sm_count(int* out_host) {
 extern "C" int b200_set_sm_budget(int sms) {
   B200_REQUIRE(sms >= 0, "SM budget must be >= 0 (0 = every SM of the device)");
   g_sm_budget = (sms > 0 && sms < 2) ? 2 : sms;  // a CTA pair needs two
+  return 0;
+}
+
+extern "C" int b200_set_status_word(uint32_t* device_word) {
+  g_status_word = device_word;
   return 0;
 }
 

@@ -33,6 +33,12 @@ void set_error(const char* fmt, ...);
 int sm_count();           // SMs the persistent grids are sized for (b200_set_sm_budget), <= sm_count_physical()
 int sm_count_physical();  // cached per process (current device at first call)
 bool pdl_enabled();  // programmatic dependent launch (B200STEP_PDL=0 turns it off)
+// Device word (b200_set_status_word; may be null) onto which kernels OR the B200_STATUS_* bits when they meet input
+// that torch would have rejected (nn.Embedding / nn.CrossEntropyLoss raise on out-of-range indices).
+uint32_t* status_word();
+__device__ __forceinline__ void flag_status(uint32_t* word, uint32_t bit) {
+  if (word != nullptr) atomicOr(word, bit);
+}
 // out[c] = sum_r partials[r * row_stride + c] for c < ncols, fixed order (defined in loss.cu)
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out, cudaStream_t st);
 

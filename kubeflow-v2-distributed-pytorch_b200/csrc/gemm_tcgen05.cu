@@ -221,7 +221,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                      : make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t bd = kBMN ? make_smem_desc(sb + k * UMMA_K * 128, MN_BOX_BYTES, MN_SBO, MN_LAYOUT)
                                      : make_smem_desc(sb + k * 32, 16, 1024);
+#ifdef B200STEP_EXPERIMENTS
             if (p.flags & 0x800) continue;  // timing experiment: stream the operands, skip the MMAs
+#endif
             if constexpr (kCtas == 2) umma_ss_pair<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
             else umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
@@ -305,7 +307,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int g = chalf * GROUPS_PER_WARP + gi;
           const int gcol0 = n0 + g * GROUP_COLS;
           if (gcol0 >= p.N) break;  // warp-uniform
+#ifdef B200STEP_EXPERIMENTS
           if (p.flags & 0x200) break;  // timing experiment
+#endif
           uint32_t vv[LDS_PER_GROUP][32];  // the whole group's accumulators: one TMEM round trip, not two
 #pragma unroll
           for (int h = 0; h < LDS_PER_GROUP; ++h) tmem_ld32(taddr + g * GROUP_COLS + h * 32, vv[h]);
@@ -434,14 +438,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
           __syncwarp();
-          if (lane == 0 && row0 < p.M && !(p.flags & 0x100)) {
+#ifdef B200STEP_EXPERIMENTS
+          const bool skip_store = (p.flags & 0x100) != 0;  // timing experiment
+#else
+          constexpr bool skip_store = false;
+#endif
+          if (lane == 0 && row0 < p.M && !skip_store) {
             tma_store_2d(&tmC, sbuf_ptr, gcol0, row0);
             bulk_commit();
           }
         }
         if constexpr (kEpi == EPI_FWD) {
           // the row's 128 mask bits of this column half leave as one 16-byte store
-          if (p.mask_out != nullptr && row_ok && !(p.flags & 0x400)) {
+#ifdef B200STEP_EXPERIMENTS
+          const bool skip_mask = (p.flags & 0x400) != 0;  // timing experiment
+#else
+          constexpr bool skip_mask = false;
+#endif
+          if (p.mask_out != nullptr && row_ok && !skip_mask) {
             const long long wbase = (n0 >> 5) + chalf * 4;
             if (wbase + 4 <= p.ldmask)
               *reinterpret_cast<uint4*>(p.mask_out + (long long)row * p.ldmask + wbase) =
@@ -714,7 +728,11 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
   cuuint32_t estr[2] = {1, 1};
   // fp32 operands: the TFLOAT32 tensor-map type rounds to tf32 (nearest) on the way into shared memory; with
   // plain FLOAT32 the tensor core would truncate the low 13 mantissa bits, a biased error that accumulates.
+#ifdef B200STEP_EXPERIMENTS
   static const bool tf32_truncate = getenv("B200STEP_TF32_TRUNCATE") != nullptr;  // debugging knob
+#else
+  constexpr bool tf32_truncate = false;
+#endif
   const CUtensorMapDataType dt = !tf32 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                  : ((tf32_truncate || is_output) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                                                  : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32);
@@ -772,12 +790,17 @@ static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUt
   return 0;
 }
 
-// timing experiments only (results are wrong): bit 8 = do not issue the output TMA stores, bit 9 = skip the
-// epilogue math and staging, bit 10 = skip the ReLU bit-mask store, bit 11 = skip the MMAs (operand streaming only)
+// Timing experiments (results are wrong), compiled only with -DB200STEP_EXPERIMENTS (build.py --experiments), never
+// into the shipped library: bit 8 = do not issue the output TMA stores, bit 9 = skip the epilogue math and staging,
+// bit 10 = skip the ReLU bit-mask store, bit 11 = skip the MMAs (operand streaming only)
 static int gemm_debug_flags() {
+#ifdef B200STEP_EXPERIMENTS
   static int v = -1;
   if (v < 0) v = getenv("B200STEP_GEMM_DEBUG") ? (atoi(getenv("B200STEP_GEMM_DEBUG")) << 8) : 0;
   return v;
+#else
+  return 0;
+#endif
 }
 
 template <int kTf32, bool kAMN, bool kBMN, int kEpi>

@@ -28,7 +28,8 @@ template <bool kBf16>
 __global__ void __launch_bounds__(CE_THREADS, 1)
 ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64_t* __restrict__ labels,
                     void* __restrict__ dlogits_, long long lddl, float* __restrict__ partials,
-                    long long batch, int C, float scale, int want_dbias) {
+                    long long batch, int C, float scale, int want_dbias, long long ignore_index,
+                    const int32_t* __restrict__ n_valid, uint32_t* __restrict__ status) {
   constexpr int VEC = kBf16 ? 8 : 4;          // elements per 16-byte vector
   constexpr int ITERS = 32 / VEC;             // vectors per lane (covers 1024 columns)
   constexpr int ES = kBf16 ? 2 : 4;
@@ -52,6 +53,10 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
   }
   __syncthreads();
   pdl_wait();  // the logits come from the previous kernel
+  if (n_valid != nullptr) {  // mean over the rows that are not ignore_index (counted by K-pre) instead of all rows
+    const int nv = *n_valid;
+    scale = nv > 0 ? scale * (float)batch / (float)nv : 0.f;
+  }
 
   auto issue_load = [&](long long tile, int buf) {  // one thread
     const long long r0 = tile * TILE_ROWS;
@@ -89,7 +94,19 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
     for (int rr = warp; rr < rows; rr += CE_WARPS) {
       const long long row = r0 + rr;
       const uint32_t srow = sbuf + rr * row_bytes;
-      const int y = (int)__ldg(labels + row);
+      const long long y64 = __ldg(labels + row);
+      if (y64 == ignore_index || y64 < 0 || y64 >= C) {  // warp-uniform
+        // nn.CrossEntropyLoss: a target equal to ignore_index contributes neither loss nor gradient; any other
+        // target outside [0, C) makes torch raise — here the row is dropped the same way and the host is told
+        if (y64 != ignore_index && lane == 0) flag_status(status, B200_STATUS_BAD_LABEL);
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          const int v = lane + 32 * i;
+          if (v < nvec) st_shared_v4(srow + v * 16, 0u, 0u, 0u, 0u);
+        }
+        continue;
+      }
+      const int y = (int)y64;
       const int vy = y / VEC, jy = y - vy * VEC;  // 16-byte vector / slot that holds the label's logit
       float z[32];
       float zmax = -INFINITY;
@@ -220,9 +237,11 @@ constexpr int RED_THREADS = 256;
 __global__ void __launch_bounds__(RED_THREADS)
 reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
                        float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out,
-                       int accumulate) {
+                       int accumulate, const int32_t* __restrict__ n_valid, float batch_rows) {
   pdl_launch_dependents();
   pdl_wait();
+  // mean over the non-ignored rows: 1/batch -> 1/n_valid (no valid row at all gives 0 * inf = NaN, like torch)
+  if (n_valid != nullptr) loss_scale = loss_scale * batch_rows / (float)(*n_valid);
   __shared__ float part[RED_THREADS / 32][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = blockIdx.x * 32 + lane;
@@ -258,8 +277,8 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
 
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out,
                            cudaStream_t st) {
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials, nrows, row_stride, ncols, out, -1, 0.f,
-                                                                 nullptr, 0));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials,
+                             nrows, row_stride, ncols, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -347,7 +366,8 @@ extern "C" int64_t b200_ce_scratch_floats(int num_classes) {
 extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels, void* dlogits,
                                  int64_t lddl, float* loss_out, float* dbias, float* scratch,
                                  int64_t scratch_floats, int64_t batch, int num_classes, float grad_scale,
-                                 float loss_scale, int accumulate, int dtype, b200_stream_t stream) {
+                                 float loss_scale, int accumulate, int64_t ignore_index, const int32_t* n_valid,
+                                 int dtype, b200_stream_t stream) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   const int vec = dtype == B200_F32 ? 4 : 8;
   B200_REQUIRE(num_classes > 0 && num_classes <= CE_MAX_CLASSES && num_classes % vec == 0,
@@ -372,21 +392,25 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
       B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
       cfg = true;
     }
-    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<true>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                              num_classes, grad_scale, dbias != nullptr));
+    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<true>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels,
+                               dlogits, lddl, scratch, batch, num_classes, grad_scale, (int)(dbias != nullptr),
+                               (long long)ignore_index, n_valid, status_word()));
   } else {
     static bool cfg = false;
     if (!cfg) {
       B200_CHECK_CUDA(cudaFuncSetAttribute(ce_loss_grad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CE_BUFS * 64 * CE_MAX_CLASSES));
       cfg = true;
     }
-    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<false>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels, dlogits, lddl, scratch, batch,
-                                                               num_classes, grad_scale, dbias != nullptr));
+    B200_CHECK_CUDA(launch_pdl(ce_loss_grad_kernel<false>, dim3(grid), dim3(CE_THREADS), smem, st, logits, ldl, labels,
+                               dlogits, lddl, scratch, batch, num_classes, grad_scale, (int)(dbias != nullptr),
+                               (long long)ignore_index, n_valid, status_word()));
   }
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((stride + 31) / 32), dim3(RED_THREADS), 0, st, scratch, grid, stride, num_classes, dbias,
-                                                             num_classes, loss_scale > 0.f ? loss_scale : 1.0f / (float)batch, loss_out, accumulate));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((stride + 31) / 32), dim3(RED_THREADS), 0, st, scratch, grid,
+                             stride, num_classes, dbias, num_classes,
+                             loss_scale > 0.f ? loss_scale : 1.0f / (float)batch, loss_out, accumulate, n_valid,
+                             (float)batch));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -399,6 +423,8 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   const int vec = dtype == B200_F32 ? 4 : 8;
   B200_REQUIRE(M > 0 && N > 0 && N % vec == 0 && lddy % vec == 0, "colsum: N and lddy must be multiples of %d", vec);
   B200_REQUIRE(N < (1 << 30), "colsum: N too large");
+  B200_REQUIRE(dy != nullptr && out != nullptr && (reinterpret_cast<uintptr_t>(dy) & 15) == 0,
+               "colsum: dy and out must not be NULL and dy must be 16-byte aligned (128-bit loads)");
   const int nvec = (int)(N / vec);
   const int panels = (nvec + CS_THREADS - 1) / CS_THREADS;
   int slabs = (sm_count() * 4 + panels - 1) / panels;
@@ -414,7 +440,7 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3(slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, nullptr, 0));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -454,6 +480,8 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   const int vec = dtype == B200_F32 ? 4 : 8;
   B200_REQUIRE(M > 0 && N > 0 && N % vec == 0 && lddy % vec == 0, "colsum: N and lddy must be multiples of %d", vec);
+  B200_REQUIRE(dy != nullptr && out != nullptr && (reinterpret_cast<uintptr_t>(dy) & 15) == 0,
+               "colsum: dy and out must not be NULL and dy must be 16-byte aligned (128-bit loads)");
   B200_REQUIRE(N <= CS_STATIC_MAX_N,
                "b200_colsum_static: N=%lld exceeds the static scratch limit of %d columns; use b200_colsum with "
                "caller-provided scratch", (long long)N, CS_STATIC_MAX_N);
@@ -476,7 +504,7 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3((int)slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, nullptr, 0));
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -35,6 +35,18 @@ __device__ __forceinline__ void store4(__nv_bfloat16* dst, uint4 raw) {
 __device__ __forceinline__ void store1(float* dst, float v) { *dst = v; }
 __device__ __forceinline__ void store1(__nv_bfloat16* dst, float v) { *dst = __float2bfloat16_rn(v); }
 
+// A categorical id as a 32-bit table row.  nn.Embedding raises on ids outside [0, num_embeddings); a kernel cannot,
+// so the id is clamped to row 0 (every later access stays inside its table, here and in the embedding backward,
+// which reuses the stored ids) and the status word tells the host.
+template <typename IdT>
+__device__ __forceinline__ int checked_id(IdT raw, long long table_rows, uint32_t* status) {
+  if ((unsigned long long)raw >= (unsigned long long)table_rows) {
+    flag_status(status, B200_STATUS_BAD_CATEGORICAL_ID);
+    return 0;
+  }
+  return (int)raw;
+}
+
 template <typename OutT, typename IdT, int kThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
 preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds_cat,
@@ -43,10 +55,12 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
                   const float* __restrict__ stdv, const float* __restrict__ tables,
                   OutT* __restrict__ x_out, int64_t* __restrict__ y_out, int32_t* __restrict__ idx_out,
                   long long batch, int num_dense, int num_cat, long long table_rows, int embed_dim,
-                  int vpr_shift, long long ldx, long long cursor_stride) {
+                  int vpr_shift, long long ldx, long long cursor_stride, uint32_t* __restrict__ status,
+                  int32_t* __restrict__ label_stats, long long ignore_index) {
   pdl_launch_dependents();
   pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int n_counted = 0;  // lane 0: labels != ignore_index among this warp's samples
   const long long cur = cursor ? (long long)(*cursor) : 0;
   const int64_t* ridx = row_idx + cur * cursor_stride;
   const int vec_per_row = embed_dim >> 2;        // float4 chunks per table row
@@ -70,7 +84,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
   long long label_b = 0;
   if (b < batch) {
     if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
-    if (lane < num_cat) id_b = (int)__ldg(ds_cat + r_b * num_cat + lane);
+    if (lane < num_cat) id_b = checked_id(__ldg(ds_cat + r_b * num_cat + lane), table_rows, status);
     if (lane == 0) label_b = __ldg(ds_label + r_b);
   }
   for (; b < batch; b += stride) {
@@ -86,7 +100,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
     r_b = __shfl_sync(0xffffffffu, rgrp, k);
     if (bn < batch) {
       if (lane < num_dense) dense_b = __ldg(ds_dense + r_b * num_dense + lane);
-      if (lane < num_cat) id_b = (int)__ldg(ds_cat + r_b * num_cat + lane);
+      if (lane < num_cat) id_b = checked_id(__ldg(ds_cat + r_b * num_cat + lane), table_rows, status);
       if (lane == 0) label_b = __ldg(ds_label + r_b);
     }
 
@@ -95,7 +109,7 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
     for (int tb = 0; tb < num_cat; tb += 32) {
       const int t = tb + lane;
       int id = id_cur;
-      if (tb > 0) id = t < num_cat ? (int)__ldg(ds_cat + r_cur * num_cat + t) : 0;
+      if (tb > 0) id = t < num_cat ? checked_id(__ldg(ds_cat + r_cur * num_cat + t), table_rows, status) : 0;
       if (t < num_cat) idx_out[b * num_cat + t] = id;
       const int tcount = min(32, num_cat - tb);
       const int nvec = tcount * vec_per_row;
@@ -135,7 +149,25 @@ preprocess_kernel(const float* __restrict__ ds_dense, const IdT* __restrict__ ds
         store1(xr + emb_cols + e, w);
       }
     }
-    if (lane == 0) y_out[b] = label_cur;
+    if (lane == 0) {
+      y_out[b] = label_cur;
+      n_counted += (label_cur != ignore_index);
+    }
+  }
+  // Rows that count towards the mean of the loss (nn.CrossEntropyLoss divides by the number of targets that are not
+  // ignore_index): every warp adds its count, the LAST block to finish (ticket) publishes the total for K-loss and
+  // re-arms the accumulator, so a captured graph can be replayed without a memset.
+  if (label_stats != nullptr) {
+    if (lane == 0 && n_counted) atomicAdd(label_stats + 1, n_counted);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(reinterpret_cast<unsigned*>(label_stats + 2), 1u) == gridDim.x - 1) {
+        __threadfence();
+        label_stats[0] = atomicExch(label_stats + 1, 0);
+        label_stats[2] = 0;
+      }
+    }
   }
 }
 
@@ -148,8 +180,10 @@ extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int ca
                                const float* stdv, const float* tables, void* x_out, int64_t* y_out,
                                int32_t* idx_out, int64_t batch, int num_dense, int num_cat,
                                int64_t table_rows, int embed_dim, int64_t ldx, int x_dtype,
-                               int64_t cursor_stride, b200_stream_t stream) {
+                               int64_t cursor_stride, int32_t* label_stats, int64_t ignore_index,
+                               b200_stream_t stream) {
   if (cursor_stride <= 0) cursor_stride = batch;
+  uint32_t* status = status_word();
   B200_REQUIRE(x_dtype == B200_F32 || x_dtype == B200_BF16, "unknown dtype code %d", x_dtype);
   B200_REQUIRE(batch > 0, "batch must be positive");
   B200_REQUIRE(num_dense >= 0 && num_cat >= 0 && embed_dim >= 0, "negative feature counts");
@@ -189,13 +223,14 @@ extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int ca
       B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(PRE_FAT_THREADS), PRE_FAT_SMEM, st, ds_dense,            \
                                  static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor, mean, stdv, tables, \
                                  static_cast<OUT_T*>(x_out), y_out, idx_out, batch, num_dense, num_cat,           \
-                                 table_rows, embed_dim, vpr_shift, ldx, (long long)cursor_stride));               \
+                                 table_rows, embed_dim, vpr_shift, ldx, (long long)cursor_stride, status,         \
+                                 label_stats, (long long)ignore_index));                                          \
     } else {                                                                                                      \
       B200_CHECK_CUDA(launch_pdl(preprocess_kernel<OUT_T, ID_T, PRE_THREADS, 4>, dim3(grid), dim3(PRE_THREADS),   \
                                  0, st, ds_dense, static_cast<const ID_T*>(ds_cat), ds_label, row_idx, cursor,    \
                                  mean, stdv, tables, static_cast<OUT_T*>(x_out), y_out, idx_out, batch,           \
                                  num_dense, num_cat, table_rows, embed_dim, vpr_shift, ldx,                       \
-                                 (long long)cursor_stride));                                                      \
+                                 (long long)cursor_stride, status, label_stats, (long long)ignore_index));        \
     }                                                                                                             \
   } while (0)
   if (x_dtype == B200_F32) {

@@ -394,3 +394,95 @@ def test_cast_and_advance(ops):
     torch.cuda.synchronize()
     assert torch.equal(dst, src.to(torch.bfloat16))
     assert cursor.item() == 0 and step.item() == 10
+
+
+# ----------------------------------------------------------- inputs torch would reject / ignore_index semantics
+def test_ce_ignore_index_and_bad_labels(ops):
+    """nn.CrossEntropyLoss defaults (loss.py:1379-1387): targets equal to ignore_index=-100 add neither loss nor
+    gradient and the mean runs over the remaining rows; any other target outside [0, C) makes torch raise - the
+    kernel drops the row and sets B200_STATUS_BAD_LABEL."""
+    import torch.nn.functional as F
+
+    B, C = 777, 1000
+    status = ops.status_word()
+    status.zero_()
+    for dtype in (torch.float32, torch.bfloat16):
+        logits = _rand((B, C), dtype, 21, 3.0)
+        g = torch.Generator().manual_seed(22)
+        labels = torch.randint(0, C, (B,), generator=g)
+        labels[torch.randperm(B, generator=g)[:100]] = -100
+        labels = labels.cuda()
+        n_valid = torch.tensor([int((labels != -100).sum())], dtype=torch.int32, device="cuda")
+        dl = torch.full_like(logits, float("nan"))
+        loss = torch.zeros(1, device="cuda")
+        db = torch.zeros(C, device="cuda")
+        scratch = torch.empty(ops.ce_scratch_floats(C), device="cuda")
+        ops.ce_loss_grad(logits, labels, dl, loss, db, scratch, batch=B, num_classes=C, grad_scale=1.0 / B,
+                         n_valid=n_valid)
+        torch.cuda.synchronize()
+        z = logits.double().requires_grad_(True)
+        ref = F.cross_entropy(z, labels)            # ignore_index=-100, reduction="mean"
+        ref.backward()
+        assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+        tol = 1e-6 if dtype == torch.float32 else 2e-2
+        torch.testing.assert_close(dl.double(), z.grad, rtol=tol, atol=tol / B)
+        assert torch.count_nonzero(dl[labels == -100]).item() == 0
+        assert int(status.item()) == 0
+        # a label torch would raise on: dropped like an ignored row, and reported
+        bad = labels.clone()
+        bad[5] = C + 3
+        ops.ce_loss_grad(logits, bad, dl, loss, db, scratch, batch=B, num_classes=C, grad_scale=1.0 / B)
+        torch.cuda.synchronize()
+        assert int(status.item()) == ops.STATUS_BAD_LABEL
+        assert torch.count_nonzero(dl[5]).item() == 0 and torch.isfinite(dl).all()
+        status.zero_()
+    # no valid row at all: torch's mean is 0/0
+    labels = torch.full((64,), -100, dtype=torch.int64, device="cuda")
+    logits = _rand((64, C), torch.float32, 23)
+    dl = torch.full_like(logits, float("nan"))
+    ops.ce_loss_grad(logits, labels, dl, loss, None, scratch, batch=64, num_classes=C, grad_scale=1.0 / 64,
+                     n_valid=torch.zeros(1, dtype=torch.int32, device="cuda"))
+    torch.cuda.synchronize()
+    assert torch.isnan(loss).all() and torch.count_nonzero(dl).item() == 0
+
+
+@pytest.mark.parametrize("id_dtype", [torch.int64, torch.int32])
+def test_preprocess_flags_out_of_range_ids_and_counts_labels(ops, id_dtype):
+    """nn.Embedding raises IndexError on an id outside its table; K-pre clamps it to row 0 (so neither it nor the
+    embedding backward, which reuses the stored ids, leaves the table) and sets B200_STATUS_BAD_CATEGORICAL_ID.
+    label_stats[0] = rows whose label is not ignore_index, re-armed after every launch."""
+    batch, nd, nc, rows, dim, ldx = 1000, 13, 26, 100, 16, 448
+    g = torch.Generator().manual_seed(31)
+    dense = torch.randn(batch, nd, generator=g).cuda()
+    cat = torch.randint(0, rows, (batch, nc), generator=g).to(id_dtype)
+    label = torch.randint(0, 10, (batch,), generator=g)
+    label[::7] = -100
+    mean, std = dense.mean(0).contiguous(), dense.std(0).contiguous()
+    tables = torch.randn(nc * rows * dim, generator=g).cuda()
+    row_idx = torch.arange(batch).cuda()
+    status = ops.status_word()
+    status.zero_()
+    stats = torch.zeros(4, dtype=torch.int32, device="cuda")
+
+    def run(cat_t):
+        x = torch.full((batch, ldx), float("nan"), dtype=torch.bfloat16, device="cuda")
+        y = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        idx = torch.full((batch, nc), -1, dtype=torch.int32, device="cuda")
+        ops.preprocess(dense, cat_t.cuda(), label.cuda(), row_idx, None, mean, std, tables, x, y, idx, batch=batch,
+                       num_dense=nd, num_cat=nc, table_rows=rows, embed_dim=dim, label_stats=stats)
+        torch.cuda.synchronize()
+        return x, idx
+
+    for _ in range(2):                         # twice: the accumulator and ticket must re-arm themselves
+        x, idx = run(cat)
+        assert int(status.item()) == 0
+        assert stats.tolist() == [int((label != -100).sum()), 0, 0, 0]
+    bad = cat.clone()
+    bad[3, 4] = rows            # one past the end
+    bad[10, 0] = -1
+    x, idx = run(bad)
+    assert int(status.item()) == ops.STATUS_BAD_CATEGORICAL_ID
+    assert idx[3, 4].item() == 0 and idx[10, 0].item() == 0 and torch.isfinite(x.float()).all()
+    tv = tables.view(nc, rows, dim)
+    assert torch.equal(x[3, 4 * dim: 5 * dim].float(), tv[4][0].to(torch.bfloat16).float())
+    status.zero_()

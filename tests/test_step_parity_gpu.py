@@ -350,3 +350,20 @@ def test_state_dict_layout_matches_reference_keys():
     assert list(so.keys()) == list(sg.keys()) and all(k.startswith("module.") for k in sg)
     for k in so:                       # untrained: bit-identical to the seeded torch initialisation
         assert torch.equal(so[k], sg[k]), k
+
+
+def test_out_of_range_input_is_reported_at_synchronize():
+    """torch raises on an embedding id outside its table; the device step neutralises it (row 0) and the host gets
+    a B200Error the next time it synchronises — training never continues silently on invalid input."""
+    from b200step.lib import B200Error
+
+    spec = SMALL
+    ds = make_synthetic(512, spec)
+    ds.cat[7, 3] = spec.cardinality + 11
+    eng = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(512, 1, 0), StepConfig(batch_size=256))
+    eng.step()
+    eng.step()
+    with pytest.raises(B200Error, match="categorical id outside"):
+        eng.synchronize()
+    eng.synchronize()      # the report is cleared once raised
+    eng.close()

@@ -27,8 +27,9 @@ def _sd(spec):
     return d
 
 
-def _launch(ngpus, tmp, rows, batch, epochs, port, precision="bf16", extra=()):
+def _launch(ngpus, tmp, rows, batch, epochs, port, precision="bf16", extra=(), env_extra=None):
     env = dict(os.environ)
+    env.update(env_extra or {})
     env.update({"WORLD_SIZE": "1", "RANK": "0", "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
                 "CUDA_VISIBLE_DEVICES": ",".join(str(i) for i in range(ngpus))})
     cmd = [sys.executable, os.path.join(ROOT, "task.py"), "--dist-url=env://", "--multiprocessing-distributed",
@@ -91,12 +92,12 @@ def test_task_py_two_gpus_matches_ddp_oracle(tmp_path):
                            "hardware yet; the single-rank path is covered by test_peer_optimizer_single_rank)")
 @pytest.mark.parametrize("optimizer", ["sgd", "adam"])
 def test_task_py_two_gpus_peer_optimizer(tmp_path, optimizer):
-    """--peer_optimizer (EXPERIMENTAL): the NVLink peer-memory reduce + update + broadcast kernel instead of NCCL
+    """B200STEP_PEER_OPT=1 (EXPERIMENTAL, no CLI flag until this test has passed on hardware): the NVLink peer-memory reduce + update + broadcast kernel instead of NCCL
     all-reduce + optimizer; same DDP semantics, same oracle, same tolerances."""
     rows, batch, epochs = 2048 + 100, 256, 3          # 4 full batches + a partial one per rank and epoch
     lr = "0.1" if optimizer == "sgd" else "0.001"
     r = _launch(2, tmp_path, rows, batch, epochs, 29563 + (optimizer == "adam"),
-                extra=("--peer_optimizer", "--optimizer", optimizer, "--learning_rate", lr))
+                extra=("--optimizer", optimizer, "--learning_rate", lr), env_extra={"B200STEP_PEER_OPT": "1"})
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
     ds = make_synthetic(rows, SPEC)
     oracle = OracleTrainer(_sd(SPEC), ds, world=2, batch_size=batch, precision="bf16", optimizer=optimizer,

@@ -42,9 +42,31 @@ def test_colsum_static_matches_colsum_twice_in_a_row(dtype):
         torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-3 * (M ** 0.5) * 1e-2)
         # and again on the same input: identical to the first static call, bit for bit
         again = torch.full((N,), float("nan"), device="cuda")
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()      # the driver's own count of free device memory
+        reserved_before = torch.cuda.memory_reserved()  # and what torch's pool holds
         _call_static(lib, dy, again, M, N, code)
         torch.cuda.synchronize()
+        # the property the entry point exists for: the call took no device memory, from the driver or from torch
+        assert torch.cuda.mem_get_info()[0] == free_before
+        assert torch.cuda.memory_reserved() == reserved_before
         assert torch.equal(got, again)
+
+
+def test_colsum_static_rejects_misaligned_and_null_pointers():
+    """128-bit loads need a 16-byte aligned matrix: a misaligned view must be refused up front with an error
+    message, not fault asynchronously on the device."""
+    from b200step.lib import B200Error, get_lib
+
+    lib = get_lib()
+    base = torch.zeros(64 * 512 + 8, dtype=torch.bfloat16, device="cuda")
+    out = torch.zeros(512, device="cuda")
+    skew = base[1:1 + 64 * 512].view(64, 512)          # starts 2 bytes off a 16-byte boundary
+    with pytest.raises(B200Error, match="16-byte aligned"):
+        _call_static(lib, skew, out, 64, 512, 1)
+    with pytest.raises(B200Error, match="NULL"):
+        lib.colsum_static(None, 512, out.data_ptr(), 64, 512, 1, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
 
 
 def test_colsum_static_rejects_rows_wider_than_its_limit():
