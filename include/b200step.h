@@ -140,6 +140,21 @@ int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels,
                       int64_t batch, int num_classes, float grad_scale, float loss_scale, int accumulate,
                       int64_t ignore_index, const int32_t* n_valid, int dtype, b200_stream_t stream);
 
+/* ---- K-gemm-ce: the output layer and the loss as ONE kernel ------------------------------------
+ * Replaces b200_linear_fwd (last nn.Linear, task.py:309) followed by b200_ce_loss_grad (task.py:310-311) without
+ * ever storing the logits: z = x[M,K]·w[N,K]^T + bias (rounded to `dtype` exactly as the stored logits would have
+ * been), loss_out[0] = mean_b(logsumexp(z_b) - z_b[y_b]), dlogits[M,N] = (softmax(z) - onehot(y)) * grad_scale,
+ * dbias[N] (nullable) = column sums of dlogits as stored.  Same semantics for grad_scale / loss_scale / accumulate /
+ * ignore_index / n_valid / out-of-range labels as b200_ce_loss_grad.  N <= 1024 classes (a cluster of up to four
+ * CTA pairs holds one softmax row in tensor memory); scratch: b200_linear_ce_scratch_floats(N) floats, contents
+ * need not be initialised.  Loss and dbias are summed in a fixed order (run-to-run deterministic). */
+int64_t b200_linear_ce_scratch_floats(int64_t N);
+int b200_linear_ce(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias,
+                   const int64_t* labels, void* dlogits, int64_t lddl, float* loss_out, float* dbias,
+                   float* scratch, int64_t scratch_floats, int64_t M, int64_t N, int64_t K, int dtype,
+                   float grad_scale, float loss_scale, int accumulate, int64_t ignore_index,
+                   const int32_t* n_valid, b200_stream_t stream);
+
 /* ---- column sum: bias gradients of the hidden layers (task.py:311, addmm backward wrt bias) -
  * out[N] = sum_m dy[m, :]  (fp32, deterministic two-stage reduction through scratch) */
 int64_t b200_colsum_scratch_floats(int64_t N);

@@ -62,6 +62,8 @@ class StepConfig:
                                          # tables' optimizer launch, i.e. under the all-reduces still in flight
                                          # (device-resident `step()` path only).  Off by default: measured on T0
                                          # +0.6 % at 2 GPUs, -2 % at 8 GPUs (profiles/r01_comm_overlap_experiments.md)
+    fused_ce: Optional[bool] = None      # output layer + cross-entropy as one kernel (K-gemm-ce): the logits never go to
+                                         # HBM.  None = whenever it applies (<= 1024 classes, logits not kept)
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1
@@ -175,7 +177,12 @@ class TrainStep:
         self.label_stats = torch.zeros(4, dtype=torch.int32, device=dev)
         # bits the kernels set when they meet an id / label torch would have raised on (checked in synchronize())
         self.status = ops.status_word(dev)
-        self.ce_scratch = torch.empty(ops.ce_scratch_floats(spec.num_classes), dtype=torch.float32, device=dev)
+        self.fused_ce = (spec.num_classes <= 1024 and not cfg.keep_logits) if cfg.fused_ce is None else cfg.fused_ce
+        if self.fused_ce and (spec.num_classes > 1024 or cfg.keep_logits):
+            raise ValueError("fused_ce needs <= 1024 classes and keep_logits off (the logits are never stored)")
+        self.ce_scratch = torch.empty(max(ops.ce_scratch_floats(spec.num_classes),
+                                          ops.linear_ce_scratch_floats(spec.num_classes) if self.fused_ce else 0),
+                                      dtype=torch.float32, device=dev)
         # 1 bit per hidden activation (ReLU/dropout mask for backward), row stride padded to 16 bytes
         self.masks = [torch.zeros(B, ((o + 31) // 32 + 3) // 4 * 4, dtype=torch.int32, device=dev)
                       for (_, o) in dims[:-1]]
@@ -249,7 +256,7 @@ class TrainStep:
 
     def _forward(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
                  cursor: Optional[torch.Tensor], training: bool, r0: int = 0, rows: Optional[int] = None,
-                 skip_pre: bool = False) -> int:
+                 skip_pre: bool = False, skip_last: bool = False) -> int:
         """K-pre + the Linear stack (task.py:309) for rows [r0, r0 + rows) of the batch; dropout only when training
         (model.train(), task.py:301)."""
         spec, cfg, st = self.spec, self.cfg, self.main
@@ -264,6 +271,8 @@ class TrainStep:
         for li, (k, o) in enumerate(dims):
             kk = self.k0 if li == 0 else k
             last = li == self.L - 1
+            if last and skip_last:      # the caller fuses the output layer with the loss (K-gemm-ce)
+                break
             ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li][sl], M=rows, N=o, K=kk, relu=not last,
                            dropout_p=spec.dropout if (training and not last) else 0.0, seed=cfg.dropout_seed,
                            step=self.step_ctr, layer_id=li,
@@ -316,12 +325,22 @@ class TrainStep:
         for ci, (r0, rows) in enumerate(chunks):
             sl = slice(r0, r0 + rows)
             last_chunk = ci == len(chunks) - 1
-            n += self._forward(batch, src, row_idx, cursor, training=True, r0=r0, rows=rows, skip_pre=prefetch)
+            n += self._forward(batch, src, row_idx, cursor, training=True, r0=r0, rows=rows, skip_pre=prefetch,
+                               skip_last=self.fused_ce)
             # loss + dlogits + db_L (summed over the chunks) ---------------------------------------------------
-            ops.ce_loss_grad(self.acts[-1][sl], self.y[sl], self.dlogits[sl], self.loss, self._b(L - 1, grad=True),
-                             self.ce_scratch, batch=rows, num_classes=spec.num_classes,
-                             grad_scale=1.0 / (batch * cfg.world), loss_scale=1.0 / batch, accumulate=ci > 0,
-                             n_valid=self.label_stats if len(chunks) == 1 else None, stream=st)
+            n_valid = self.label_stats if len(chunks) == 1 else None
+            if self.fused_ce:
+                # output layer and loss in one kernel: logits live in tensor memory only, dlogits is what is stored
+                k_last = dims[L - 1][0] if L > 1 else self.k0
+                ops.linear_ce(self.x0[sl] if L == 1 else self.acts[L - 2][sl], self._w(L - 1), self._b(L - 1),
+                              self.y[sl], self.dlogits[sl], self.loss, self._b(L - 1, grad=True), self.ce_scratch,
+                              M=rows, N=spec.num_classes, K=k_last, grad_scale=1.0 / (batch * cfg.world),
+                              loss_scale=1.0 / batch, accumulate=ci > 0, n_valid=n_valid, stream=st)
+            else:
+                ops.ce_loss_grad(self.acts[-1][sl], self.y[sl], self.dlogits[sl], self.loss,
+                                 self._b(L - 1, grad=True), self.ce_scratch, batch=rows,
+                                 num_classes=spec.num_classes, grad_scale=1.0 / (batch * cfg.world),
+                                 loss_scale=1.0 / batch, accumulate=ci > 0, n_valid=n_valid, stream=st)
             n += 2
             # backward ------------------------------------------------------------------------------------------
             # Phase 1 walks the dgrad chain down to the embedding gradient, phase 2 runs the wgrad GEMMs.  The table

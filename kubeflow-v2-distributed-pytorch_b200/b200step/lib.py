@@ -41,6 +41,9 @@ SIGNATURES = {
     "b200_linear_wgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _p]),
     "b200_ce_scratch_floats": (_i64, [_i]),
     "b200_ce_loss_grad": (_i, [_p, _i64, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i, _f, _f, _i, _i64, _p, _i, _p]),
+    "b200_linear_ce_scratch_floats": (_i64, [_i64]),
+    "b200_linear_ce": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _i64, _i64, _i64, _i64, _i, _f, _f, _i,
+                            _i64, _p, _p]),
     "b200_colsum_scratch_floats": (_i64, [_i64]),
     "b200_colsum": (_i, [_p, _i64, _p, _p, _i64, _i64, _i64, _i, _p]),
     "b200_colsum_static": (_i, [_p, _i64, _p, _i64, _i64, _i, _p]),
@@ -82,6 +85,7 @@ SIGNATURES = {
 
 # functions whose int return value is NOT an error code
 _NO_CHECK = {"b200_last_error", "b200_abi_version", "b200_ce_scratch_floats", "b200_colsum_scratch_floats",
+             "b200_linear_ce_scratch_floats",
              "b200_dgrad_scratch_floats", "b200_peer_flag_words"}
 
 

@@ -108,6 +108,20 @@ def ce_loss_grad(logits, labels, dlogits, loss_out, dbias, scratch, *, batch: in
                            dtype_code(logits.dtype), _stream(stream))
 
 
+def linear_ce_scratch_floats(num_classes: int) -> int:
+    return int(get_lib().linear_ce_scratch_floats(num_classes))
+
+
+def linear_ce(x, w, bias, labels, dlogits, loss_out, dbias, scratch, *, M: int, N: int, K: int, grad_scale: float,
+              loss_scale: float = 0.0, accumulate: bool = False, ignore_index: int = -100, n_valid=None, stream=None):
+    """Output layer + cross-entropy in one kernel: the logits stay in tensor memory, only dlogits is written."""
+    _cuda(x, w, bias, labels, dlogits, loss_out, dbias, scratch, n_valid)
+    get_lib().linear_ce(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(labels), ptr(dlogits),
+                        dlogits.stride(0), ptr(loss_out), ptr(dbias), ptr(scratch), scratch.numel(), M, N, K,
+                        dtype_code(x.dtype), float(grad_scale), float(loss_scale), int(accumulate), int(ignore_index),
+                        ptr(n_valid), _stream(stream))
+
+
 def colsum_scratch_floats(n: int) -> int:
     return int(get_lib().colsum_scratch_floats(n))
 

@@ -21,7 +21,7 @@ CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libb200step.so")
-SOURCES = ["abi.cu", "preprocess.cu", "gemm_tcgen05.cu", "loss.cu", "optim.cu", "comm.cu", "peer.cu"]
+SOURCES = ["abi.cu", "preprocess.cu", "gemm_tcgen05.cu", "gemm_ce.cu", "loss.cu", "optim.cu", "comm.cu", "peer.cu"]
 
 
 def _nccl_include() -> str:
@@ -68,6 +68,7 @@ def build(force: bool = False, verbose: bool = False, experiments: bool = False)
     flags = _flags(verbose, experiments)
     deps = [os.path.join(CSRC, s) for s in sources] + [
         os.path.join(CSRC, "common.cuh"),
+        os.path.join(CSRC, "gemm_common.cuh"),
         os.path.join(HERE, "..", "include", "b200step.h"),
     ]
     stamp = _stamp(deps, flags)

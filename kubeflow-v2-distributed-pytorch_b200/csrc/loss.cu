@@ -230,14 +230,17 @@ ce_loss_grad_kernel(const void* __restrict__ logits_, long long ldl, const int64
   }
 }
 
-// out[c] (+)= sum over partial rows in a fixed order; column `loss_col` (if >= 0) is scaled and written/added to loss_out.
-// One CTA per 32 columns: warp w walks rows w, w+8, ... (128 contiguous bytes per warp and row, four
+// out[c] (+)= sum over partial rows in a fixed order.  Columns [loss_col, loss_col + loss_ncols) (if loss_col >= 0;
+// they must sit inside one 32-column block) are loss partials instead: their totals are added up in column order,
+// scaled, and written/added to loss_out.
+// One CTA per 32 columns: warp w walks rows w, w+8, ... (128 contiguous bytes per warp and row, eight
 // independent loads in flight), then the 8 per-warp sums are combined in a fixed order -> deterministic.
 constexpr int RED_THREADS = 256;
 __global__ void __launch_bounds__(RED_THREADS)
 reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_stride, int ncols,
-                       float* __restrict__ out, int loss_col, float loss_scale, float* __restrict__ loss_out,
-                       int accumulate, const int32_t* __restrict__ n_valid, float batch_rows) {
+                       float* __restrict__ out, int loss_col, int loss_ncols, float loss_scale,
+                       float* __restrict__ loss_out, int accumulate, const int32_t* __restrict__ n_valid,
+                       float batch_rows) {
   pdl_launch_dependents();
   pdl_wait();
   // mean over the non-ignored rows: 1/batch -> 1/n_valid (no valid row at all gives 0 * inf = NaN, like torch)
@@ -245,7 +248,7 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
   __shared__ float part[RED_THREADS / 32][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = blockIdx.x * 32 + lane;
-  const bool is_loss = (c == loss_col);
+  const bool is_loss = loss_col >= 0 && c >= loss_col && c < loss_col + loss_ncols;
   const bool live = c < row_stride && (c < ncols || is_loss) && (is_loss || out != nullptr);
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   if (live) {
@@ -263,24 +266,38 @@ reduce_partials_kernel(const float* __restrict__ partials, int nrows, int row_st
   }
   part[warp][lane] = (s0 + s1) + (s2 + s3);
   __syncthreads();
-  if (warp == 0 && live) {
+  if (warp == 0) {
     float s = 0.f;
+    if (live) {
 #pragma unroll
-    for (int w = 0; w < RED_THREADS / 32; ++w) s += part[w][lane];
-    if (is_loss) {
-      if (loss_out) loss_out[0] = (accumulate ? loss_out[0] : 0.f) + s * loss_scale;
-    } else {
-      out[c] = (accumulate ? out[c] : 0.f) + s;
+      for (int w = 0; w < RED_THREADS / 32; ++w) s += part[w][lane];
     }
+    if (__any_sync(0xffffffffu, is_loss)) {  // the block that holds the loss columns
+      float total = 0.f;
+      for (int l = 0; l < 32; ++l) {  // column order
+        const float v = __shfl_sync(0xffffffffu, is_loss ? s : 0.f, l);
+        total += v;
+      }
+      if (lane == 0 && loss_out) loss_out[0] = (accumulate ? loss_out[0] : 0.f) + total * loss_scale;
+    }
+    if (live && !is_loss) out[c] = (accumulate ? out[c] : 0.f) + s;
   }
+}
+
+int launch_reduce_partials_loss(const float* partials, int nrows, int row_stride, int ncols, float* out, int loss_col,
+                                int loss_ncols, float loss_scale, float* loss_out, int accumulate,
+                                const int32_t* n_valid, float batch_rows, cudaStream_t st) {
+  B200_REQUIRE(loss_col < 0 || (loss_col % 32) + loss_ncols <= 32, "loss columns must sit inside one 32-column block");
+  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials,
+                             nrows, row_stride, ncols, out, loss_col, loss_ncols, loss_scale, loss_out, accumulate,
+                             n_valid, batch_rows));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 int launch_reduce_partials(const float* partials, int nrows, int row_stride, int ncols, float* out,
                            cudaStream_t st) {
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((row_stride + 31) / 32), dim3(RED_THREADS), 0, st, partials,
-                             nrows, row_stride, ncols, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
-  B200_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_reduce_partials_loss(partials, nrows, row_stride, ncols, out, -1, 0, 0.f, nullptr, 0, nullptr, 0.f, st);
 }
 
 // ---- column sum (hidden-layer bias gradients) -------------------------------------------------------
@@ -407,12 +424,9 @@ extern "C" int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t*
   }
   B200_CHECK_CUDA(cudaGetLastError());
   const int stride = num_classes + 1;
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((stride + 31) / 32), dim3(RED_THREADS), 0, st, scratch, grid,
-                             stride, num_classes, dbias, num_classes,
-                             loss_scale > 0.f ? loss_scale : 1.0f / (float)batch, loss_out, accumulate, n_valid,
-                             (float)batch));
-  B200_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_reduce_partials_loss(scratch, grid, stride, num_classes, dbias, num_classes, 1,
+                                     loss_scale > 0.f ? loss_scale : 1.0f / (float)batch, loss_out, accumulate, n_valid,
+                                     (float)batch, st);
 }
 
 extern "C" int64_t b200_colsum_scratch_floats(int64_t N) { return (int64_t)CS_MAX_BLOCKS * N; }
@@ -440,9 +454,7 @@ extern "C" int b200_colsum(const void* dy, int64_t lddy, float* out, float* scra
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3(slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, slabs, (int)N, (int)N, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
-  B200_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_reduce_partials(scratch, slabs, (int)N, (int)N, out, st);
 }
 
 // ---- column sum without any allocation --------------------------------------------------------------------
@@ -504,7 +516,5 @@ extern "C" int b200_colsum_static(const void* dy, int64_t lddy, float* out, int6
   else
     B200_CHECK_CUDA(launch_pdl(colsum_kernel<false>, dim3((int)slabs * panels), dim3(CS_THREADS), 0, st, dy, lddy, scratch, M, (int)N, rows_per_block, panels));
   B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(launch_pdl(reduce_partials_kernel, dim3((int)((N + 31) / 32)), dim3(RED_THREADS), 0, st, scratch, (int)slabs, (int)N, (int)N, out, -1, 0.f, (float*)nullptr, 0, (const int32_t*)nullptr, 0.f));
-  B200_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_reduce_partials(scratch, (int)slabs, (int)N, (int)N, out, st);
 }

@@ -486,3 +486,83 @@ def test_preprocess_flags_out_of_range_ids_and_counts_labels(ops, id_dtype):
     tv = tables.view(nc, rows, dim)
     assert torch.equal(x[3, 4 * dim: 5 * dim].float(), tv[4][0].to(torch.bfloat16).float())
     status.zero_()
+
+
+# ------------------------------------------------------------------- output layer + cross-entropy in one kernel
+LINEAR_CE_SHAPES = [
+    # (M, N classes, K)
+    (4096, 1000, 512),     # T0 output layer: a cluster of 4 CTA pairs, last tile ragged (1000 = 3*256 + 232)
+    (65536, 1000, 512),    # BASELINE config 3's batch
+    (333, 1000, 512),      # ragged rows
+    (1000, 40, 64),        # one pair (the small test models)
+    (1000, 512, 448),      # two pairs
+    (512, 600, 128),       # three class tiles -> four pairs, the last one idle
+    (777, 1024, 512),      # all 1024 classes
+    (4096, 1000, 1024),    # T1 output layer (16 k-blocks)
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,K", LINEAR_CE_SHAPES)
+def test_linear_ce_matches_linear_then_loss(ops, dtype, M, N, K):
+    """b200_linear_ce (logits kept in tensor memory) against b200_linear_fwd + b200_ce_loss_grad (logits through
+    HBM) and against torch in fp64.  Both kernel paths round the logits to the storage dtype before the softmax, so
+    they differ only by fp32 summation order and a possible last-bit flip of a stored bf16 gradient."""
+    import torch.nn.functional as F
+
+    x = _rand((M, K), dtype, 41)
+    w = _rand((N, K), dtype, 42, 0.08)
+    b = _rand((N,), torch.float32, 43, 0.5)
+    g = torch.Generator().manual_seed(44)
+    labels = torch.randint(0, N, (M,), generator=g)
+    labels[torch.randperm(M, generator=g)[: M // 9]] = -100       # some ignored rows (torch's ignore_index)
+    labels = labels.cuda()
+    n_valid = torch.tensor([int((labels != -100).sum())], dtype=torch.int32, device="cuda")
+    scale = 1.0 / (M * 2)   # world = 2
+
+    logits = torch.empty((M, N), dtype=dtype, device="cuda")
+    d_ref = torch.full((M, N), float("nan"), dtype=dtype, device="cuda")
+    loss_ref, db_ref = torch.zeros(1, device="cuda"), torch.zeros(N, device="cuda")
+    ops.linear_fwd(x, w, b, logits, M=M, N=N, K=K, relu=False)
+    ops.ce_loss_grad(logits, labels, d_ref, loss_ref, db_ref, torch.empty(ops.ce_scratch_floats(N), device="cuda"),
+                     batch=M, num_classes=N, grad_scale=scale, n_valid=n_valid)
+
+    d = torch.full((M, N), float("nan"), dtype=dtype, device="cuda")
+    loss, db = torch.full((1,), float("nan"), device="cuda"), torch.full((N,), float("nan"), device="cuda")
+    scratch = torch.empty(ops.linear_ce_scratch_floats(N), device="cuda")
+    ops.linear_ce(x, w, b, labels, d, loss, db, scratch, M=M, N=N, K=K, grad_scale=scale, n_valid=n_valid)
+    torch.cuda.synchronize()
+
+    assert torch.isfinite(d.float()).all()
+    assert abs(loss.item() - loss_ref.item()) <= 1e-5 * max(1.0, abs(loss_ref.item())), (loss.item(), loss_ref.item())
+    if dtype == torch.float32:
+        torch.testing.assert_close(d, d_ref, rtol=1e-4, atol=1e-10)
+    else:   # same fp32 value up to summation order, rounded once: at most the last bf16 bit differs
+        torch.testing.assert_close(d.float(), d_ref.float(), rtol=8e-3, atol=1e-10)
+    assert torch.count_nonzero(d[labels == -100]).item() == 0
+    torch.testing.assert_close(db.double(), d.double().sum(0), rtol=1e-4, atol=1e-7)   # sums of what IS stored
+    # against torch in fp64 on the same stored-precision logits
+    z = logits.double().requires_grad_(True)
+    ref = F.cross_entropy(z, labels)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) <= 1e-5 * max(1.0, abs(ref.item()))
+    torch.testing.assert_close(d.double(), z.grad * (n_valid.item() * scale), rtol=1e-4 if dtype == torch.float32 else 8e-3,
+                               atol=1e-9)
+    # deterministic, and `accumulate` adds onto loss / bias gradient
+    loss2, db2 = loss.clone(), db.clone()
+    ops.linear_ce(x, w, b, labels, d, loss2, db2, scratch, M=M, N=N, K=K, grad_scale=scale, n_valid=n_valid,
+                  accumulate=True)
+    torch.cuda.synchronize()
+    assert torch.equal(loss2, loss + loss) and torch.equal(db2, db + db)
+
+
+def test_linear_ce_rejects_more_than_1024_classes(ops):
+    from b200step.lib import B200Error
+
+    x = torch.zeros(128, 64, dtype=torch.bfloat16, device="cuda")
+    w = torch.zeros(1032, 64, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(B200Error, match="1024 classes"):
+        ops.linear_ce(x, w, torch.zeros(1032, device="cuda"), torch.zeros(128, dtype=torch.int64, device="cuda"),
+                      torch.zeros(128, 1032, dtype=torch.bfloat16, device="cuda"), torch.zeros(1, device="cuda"), None,
+                      torch.zeros(ops.linear_ce_scratch_floats(1024), device="cuda"), M=128, N=1032, K=64,
+                      grad_scale=1.0)
