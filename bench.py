@@ -448,7 +448,7 @@ def profile_kernels(eng, spec, B, world):
 
     from b200step import ops
 
-    names = ["preprocess", "linear_fwd", "ce_loss_grad", "linear_dgrad", "linear_wgrad", "linear_wgrad_grouped",
+    names = ["preprocess", "linear_fwd", "linear_ce", "ce_loss_grad", "linear_dgrad", "linear_wgrad", "linear_wgrad_grouped",
              "colsum", "emb_bwd", "zero", "sgd_step", "adam_step"]
     records = []
     orig = {n: getattr(ops, n) for n in names}
@@ -468,7 +468,7 @@ def profile_kernels(eng, spec, B, world):
             elif name.startswith("linear_"):
                 M, N, K = k["M"], k["N"], k["K"]
                 label = f"{name}[{M}x{N}x{K}]" + ("+dbias" if k.get("dbias") is not None else "")
-                work = {"flops": 2.0 * M * N * K}
+                work = {"flops": 2.0 * M * N * K}    # linear_ce: the output layer's GEMM; the loss rides along
             elif name == "preprocess":
                 raw = 4 * spec.num_dense + 8 * spec.num_cat + 8 + 8
                 work = {"bytes": B * (raw + 4 * spec.num_cat * spec.embed_dim + es * eng.k0 + 8 + 4 * spec.num_cat)}

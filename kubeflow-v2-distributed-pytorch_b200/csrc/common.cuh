@@ -181,6 +181,27 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
+// packed fp32 pairs (sm_100: FADD2 / FMUL2 / FFMA2 — two results per issue slot)
+__device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n.reg .b64 ra, rb;\nmov.b64 ra, {%0,%1};\nmov.b64 rb, {%2,%3};\nadd.rn.f32x2 ra, ra, rb;\n"
+      "mov.b64 {%0,%1}, ra;\n}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void fmul2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n.reg .b64 ra, rb;\nmov.b64 ra, {%0,%1};\nmov.b64 rb, {%2,%3};\nmul.rn.f32x2 ra, ra, rb;\n"
+      "mov.b64 {%0,%1}, ra;\n}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+// (d0, d1) = (a0, a1) * (b0, b1) + (c0, c1)
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0,
+                                      float c1) {
+  asm("{\n.reg .b64 ra, rb, rc;\nmov.b64 ra, {%2,%3};\nmov.b64 rb, {%4,%5};\nmov.b64 rc, {%6,%7};\n"
+      "fma.rn.f32x2 ra, ra, rb, rc;\nmov.b64 {%0,%1}, ra;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
 // 1-D bulk store shared -> global (bytes % 16 == 0, both 16-byte aligned)
 __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),

@@ -11,31 +11,40 @@
 // (tcgen05 cta_group::2, as in gemm_tcgen05.cu: each CTA stages its 128 rows of A and half of the pair's 256-wide
 // B tile, the leader issues 256x256 UMMAs) sit side by side along N, pair j computing classes [256j, 256j+256).
 // Per tile, every epilogue thread owns one row of its CTA's 128 x 256 accumulator (tcgen05.ld 32x32b: lane = row):
-//   pass 1  online softmax over the thread's 128 columns: z = acc + bias (rounded to the storage dtype, which is
-//           what a separate loss kernel would have read back), running max m and Σ exp(z − m); the exponentials
-//           are written back INTO the accumulator columns (tcgen05.st), each 32-column chunk with the running max it
+//   pass 1  online softmax over the thread's 128 columns: z = acc + bias in fp32 (the logits are never rounded to the
+//           storage dtype, because they are never stored), running max m and Σ exp(z − m); the exponentials are
+//           written back INTO the accumulator columns (tcgen05.st), each 32-column chunk with the running max it
 //           was formed against, so pass 2 needs no second exp per element;
-//   xchg    (m, Σ) of every (CTA, column half) go to the CTAs that hold the same rows — distributed shared memory
-//           stores + one cluster-scope mbarrier per accumulator stage — and every thread combines the 2·pairs
-//           partial pairs of its row into the row's max M and Z = Σ exp(z − M);
+//   xchg    the four column-quarter warps of a row fold their (m, Σ) in shared memory; the CTA's pair goes to the CTAs
+//           that hold the same rows with st.async (distributed shared memory; the bytes are credited to an mbarrier of
+//           the receiving CTA, so no fences are needed), and every thread combines the `pairs` entries of its row
+//           into the row's max M and Z = Σ exp(z − M);
 //   pass 2  dlogits = e · exp(m_chunk − M) · grad_scale / Z, minus grad_scale at the label; rounded, staged in
 //           swizzled shared memory and written by TMA; column sums of what is stored accumulate in registers
 //           (output-layer bias gradient); the row's loss M + ln Z − z[y] is summed per thread.
 // Partials (bias gradient, loss) leave as one row per (cluster, CTA, lane quarter) and are summed in a fixed order by
 // reduce_partials_kernel, so both are run-to-run deterministic.
 //
-// Roles (384 threads, as gemm_tcgen05.cu): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator,
-// warps4-11 = epilogue.
+// Roles (640 threads): warp0 = TMA producer, warp1 = MMA issuer, warp2 = TMEM allocator, warps4-19 = epilogue
+// (4 TMEM lane quarters x 4 column quarters of 64 classes: the epilogue is the long pole of this kernel and needs the
+// warps to hide its TMEM / MUFU / shared-memory latencies).
 #include "gemm_common.cuh"
 
 namespace b200 {
 
-constexpr int CE_STAGES = 5;                                          // operand ring: 5 x 32 KiB
+constexpr int CE_THREADS = 640;                                       // 4 control warps + 16 epilogue warps
+constexpr int CE_EPI_WARPS = 16;                                      // 4 lane quarters x 4 column quarters
+constexpr int CE_WARP_COLS = BLOCK_N / 4;                             // 64 classes per epilogue warp
+constexpr int CE_STAGES = 4;                                          // operand ring: 4 x 32 KiB
 constexpr int CE_STAGE_BYTES = A_TILE_BYTES + (BLOCK_N / 2) * 128;
 constexpr int CE_PIPE_BYTES = CE_STAGES * CE_STAGE_BYTES;
+constexpr int CE_STAGING_BYTES = CE_EPI_WARPS * EPI_BUF_BYTES;        // one 32-row x 128-byte slab per epilogue warp
 constexpr int CE_MAX_PAIRS = 4;                                       // CTA pairs along N: up to 1024 classes
-constexpr int CE_STATS_BYTES = 2 * CE_MAX_PAIRS * 2 * BLOCK_M * 8;    // [stage][pair][column half][row] float2
-constexpr int CE_SMEM_BYTES = CE_PIPE_BYTES + EPI_STAGING_BYTES + CE_STATS_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int CE_STATS_BYTES = 2 * CE_MAX_PAIRS * BLOCK_M * 8;        // [stage][pair][row] float2, filled by the peers
+constexpr int CE_LSTATS_BYTES = 4 * BLOCK_M * 8;                      // [column quarter][row] float2, this CTA only
+constexpr int CE_BIAS_BYTES = BLOCK_N * 4;                            // this CTA's 256 biases
+constexpr int CE_SMEM_BYTES = CE_PIPE_BYTES + CE_STAGING_BYTES + CE_STATS_BYTES + CE_LSTATS_BYTES + CE_BIAS_BYTES +
+                              1024 /*align*/ + 256 /*barriers*/;
 constexpr int CE_LOSS_COLS = 32;                                      // loss partial columns behind the class columns
 constexpr float L2E = 1.4426950408889634f;
 
@@ -74,34 +83,24 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t saddr, uint32_t cta) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(cta));
   return r;
 }
-__device__ __forceinline__ void st_cluster_v2f(uint32_t raddr, float a, float b) {
-  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(raddr), "f"(a), "f"(b) : "memory");
+// 8 bytes into a peer CTA's shared memory; their arrival is counted (complete_tx) on an mbarrier of THAT CTA, so the
+// reader needs no fence: once its barrier phase completes the bytes are there
+__device__ __forceinline__ void st_async_v2f(uint32_t raddr, float a, float b, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(raddr),
+               "f"(a), "f"(b), "r"(rbar)
+               : "memory");
 }
 __device__ __forceinline__ float2 ld_shared_v2f(uint32_t saddr) {
   float2 r;
   asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(r.x), "=f"(r.y) : "r"(saddr));
   return r;
 }
-__device__ __forceinline__ void fence_acq_rel_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
-__device__ __forceinline__ void mbar_arrive_release_cluster(uint32_t raddr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(raddr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_acquire_cluster(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "LAB_WAIT_CL:\n"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE_CL;\n"
-      "bra LAB_WAIT_CL;\n"
-      "DONE_CL:\n"
-      "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
+__device__ __forceinline__ void st_shared_v2f(uint32_t saddr, float a, float b) {
+  asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(saddr), "f"(a), "f"(b) : "memory");
 }
 
 template <int kTf32>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(CE_THREADS, 1)
 linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const CeParams p) {
   constexpr int ESIZE = kTf32 ? 4 : 2;
@@ -111,14 +110,15 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr uint32_t IDESC = make_idesc(kTf32 ? 2 : 1, 0, 0, BLOCK_M * 2, BLOCK_N);
   constexpr int B_ROWS = BLOCK_N / 2;
   constexpr int TILE_M = BLOCK_M * 2;
-  constexpr int CHUNKS = BLOCK_N / 2 / 32;             // 32-column chunks per epilogue warp (4)
-  constexpr int LDS_PER_GROUP = EPR / 32;              // chunks per output slab: 2 (bf16) / 1 (fp32)
-  constexpr int GROUPS_PER_WARP = CHUNKS / LDS_PER_GROUP;
+  constexpr int CHUNKS = CE_WARP_COLS / 32;            // 32-column chunks per epilogue warp (2)
+  constexpr int CHUNKS_PER_SLAB = EPR / 32;            // chunks per output slab: 2 (bf16) / 1 (fp32)
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* stats = smem + CE_PIPE_BYTES + EPI_STAGING_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stats + CE_STATS_BYTES);
+  uint8_t* stats = smem + CE_PIPE_BYTES + CE_STAGING_BYTES;
+  uint8_t* lstats = stats + CE_STATS_BYTES;
+  float* bias_smem = reinterpret_cast<float*>(lstats + CE_LSTATS_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(lstats + CE_LSTATS_BYTES + CE_BIAS_BYTES);
   uint64_t* full_bar = bars;                       // [CE_STAGES]
   uint64_t* empty_bar = bars + CE_STAGES;          // [CE_STAGES]
   uint64_t* acc_full = bars + 2 * CE_STAGES;       // [NUM_ACC]
@@ -150,8 +150,8 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < NUM_ACC; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], EPI_WARPS * 2);
-      mbar_init(&stat_bar[i], EPI_WARPS * p.pairs);   // one arrive per epilogue warp of every CTA that holds my rows
+      mbar_init(&acc_empty[i], CE_EPI_WARPS * 2);   // one arrive per epilogue warp of both CTAs of the pair
+      mbar_init(&stat_bar[i], 1);                   // one local arrive (expect_tx); the peers' bytes complete it
     }
     fence_mbar_init();
   }
@@ -214,42 +214,77 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp >= 4) {
     // ===================== epilogue: softmax statistics, exchange, gradient =====================
     const int q = warp & 3;             // TMEM lane quarter -> rows q*32 .. q*32+31 of this CTA's 128
-    const int chalf = (warp - 4) >> 2;  // column half of the CTA's 256 classes
+    const int cq = (warp - 4) >> 2;     // column quarter of the CTA's 256 classes
     uint8_t* sbuf_ptr = smem + CE_PIPE_BYTES + (warp - 4) * EPI_BUF_BYTES;
+    const uint32_t sbuf = smem_u32(sbuf_ptr);
     float scale = p.scale;
     if (p.n_valid != nullptr) {  // mean over the rows whose label is not ignore_index
       const int nv = *p.n_valid;
       scale = nv > 0 ? scale * p.batch / (float)nv : 0.f;
     }
-    float csacc[CHUNKS];
+    const int wcol0 = n0 + cq * CE_WARP_COLS;   // first class of this warp's 64 columns
+    // the CTA's 256 biases -> shared memory once (broadcast 128-bit reads later); one warp per column quarter
+    const uint32_t sbias = smem_u32(bias_smem) + cq * CE_WARP_COLS * 4;
+    if (q == 0) {
 #pragma unroll
-    for (int c = 0; c < CHUNKS; ++c) csacc[c] = 0.f;
+      for (int k = 0; k < CHUNKS; ++k) {
+        const int col = wcol0 + k * 32 + lane;
+        bias_smem[cq * CE_WARP_COLS + k * 32 + lane] = col < p.N ? __ldg(p.bias + col) : 0.f;
+      }
+    }
+    asm volatile("bar.sync 5, 512;" ::: "memory");   // the sixteen epilogue warps
+    // read-back addresses for the column sums of a stored slab: lane owns 4 bytes (a bf16 column pair / one fp32
+    // column) of every row; 16-byte chunk c of row r sits at chunk c ^ (r & 7)
+    uint32_t rb_addr[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) rb_addr[k] = sbuf + ((((uint32_t)lane >> 2) ^ (uint32_t)k) << 4) + (lane & 3) * 4;
+    float csacc[2] = {0.f, 0.f};   // bf16: columns (2*lane, 2*lane+1) of the warp's 64;  fp32: columns lane, 32+lane
     float loss_acc = 0.f;
-    const int wcol0 = n0 + chalf * (BLOCK_N / 2);   // first class of this warp's 128 columns
+    // Column sums of a slab AS STORED (output-layer bias gradient): every lane walks the 32 rows of its own 4 bytes —
+    // conflict-free under the swizzle.  bf16: one slab per warp and tile, so the walk is deferred into the next tile's
+    // wait for the statistics exchange, where the warp would otherwise idle (the slab stays intact until pass 2).
+    auto colsum_slab_bf16 = [&]() {
+      float lo0 = 0.f, hi0 = 0.f, lo1 = 0.f, hi1 = 0.f;
+#pragma unroll
+      for (int r = 0; r < 32; r += 2) {
+        const uint32_t w0 = ld_shared_u32(rb_addr[r & 7] + r * 128);
+        const uint32_t w1 = ld_shared_u32(rb_addr[(r + 1) & 7] + (r + 1) * 128);
+        fadd2(lo0, hi0, bf16_lo(w0), bf16_hi(w0));
+        fadd2(lo1, hi1, bf16_lo(w1), bf16_hi(w1));
+      }
+      csacc[0] += lo0 + lo1;
+      csacc[1] += hi0 + hi1;
+    };
+    const bool warp_live = wcol0 < p.N;   // this warp's 64 columns hold at least one real class
+    const uint32_t my_lstat = smem_u32(lstats) + (uint32_t)((cq * BLOCK_M + q * 32 + lane) * 8);
     int it = 0;
+    long long y64 = (unit < p.m_tiles && unit * TILE_M + rank * BLOCK_M + q * 32 + lane < p.M)
+                        ? __ldg(p.labels + unit * TILE_M + rank * BLOCK_M + q * 32 + lane) : p.ignore_index;
     for (int w = unit; w < p.m_tiles; w += nunits, ++it) {
       const int a = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int row0 = w * TILE_M + rank * BLOCK_M + q * 32;
       const int row = row0 + lane;
       const bool row_ok = row < p.M;
-      // the label: fetched while the MMAs still run
       int y = -1;
       bool valid = false;
       if (row_ok) {
-        const long long y64 = __ldg(p.labels + row);
         if (y64 >= 0 && y64 < p.N && y64 != p.ignore_index) {
           y = (int)y64;
           valid = true;
-        } else if (y64 != p.ignore_index && nj == 0 && chalf == 0) {
+        } else if (y64 != p.ignore_index && nj == 0 && cq == 0) {
           flag_status(p.status, B200_STATUS_BAD_LABEL);  // torch raises; here the row is dropped like an ignored one
         }
       }
+      {  // the next tile's label: in flight while this tile is processed
+        const long long nrow = (long long)(w + nunits) * TILE_M + rank * BLOCK_M + q * 32 + lane;
+        y64 = (w + nunits < p.m_tiles && nrow < p.M) ? __ldg(p.labels + nrow) : p.ignore_index;
+      }
       mbar_wait(&acc_full[a], aph);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BLOCK_N + chalf * (BLOCK_N / 2);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * BLOCK_N + cq * CE_WARP_COLS;
 
-      // ---- pass 1: online max / sum-exp over this thread's columns; exponentials go back into TMEM
+      // ---- pass 1: online max / sum-exp over this thread's 64 columns; exponentials go back into TMEM
       float m_run = -INFINITY, s_run = 0.f, zy = 0.f;
       float mref[CHUNKS];
 #pragma unroll
@@ -259,28 +294,19 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (col0 < p.N) {  // warp-uniform
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          const bool full = col0 + 32 <= p.N;
           float z[32];
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            if (full || col0 + j < p.N) {  // N % 4 == 0: a float4 of biases is all in or all out
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-              z[j + 0] = __uint_as_float(v[j + 0]) + b4.x;
-              z[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
-              z[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
-              z[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
-            } else {
-              z[j + 0] = z[j + 1] = z[j + 2] = z[j + 3] = -INFINITY;  // classes that do not exist
-            }
+            const uint4 b4 = ld_shared_v4(sbias + (c * 32 + j) * 4);
+            z[j + 0] = __uint_as_float(b4.x); z[j + 1] = __uint_as_float(b4.y);
+            z[j + 2] = __uint_as_float(b4.z); z[j + 3] = __uint_as_float(b4.w);
           }
-          if constexpr (!kTf32) {  // the logits as they would have been stored (bf16, RNE)
+          tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const uint32_t pk = pack_bf16x2(z[j], z[j + 1]);
-              z[j] = bf16_lo(pk);
-              z[j + 1] = bf16_hi(pk);
-            }
+          for (int j = 0; j < 32; j += 2) fadd2(z[j], z[j + 1], __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+          if (col0 + 32 > p.N) {  // ragged last chunk: classes that do not exist
+#pragma unroll
+            for (int j = 0; j < 32; ++j) z[j] = (col0 + j < p.N) ? z[j] : -INFINITY;
           }
           float cm[8];
 #pragma unroll
@@ -289,7 +315,7 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                    fmaxf(fmaxf(cm[4], cm[5]), fmaxf(cm[6], cm[7])));
           const float m_new = fmaxf(m_run, cmax);   // finite: the chunk holds at least one real class
           s_run *= ex2_approx((m_run - m_new) * L2E);  // first chunk: 0 * 2^-inf = 0
-          const float mnl = m_new * L2E;
+          const float nmnl = -m_new * L2E;
           if (__any_sync(0xffffffffu, (unsigned)(y - col0) < 32u)) {  // some row's label lives in this chunk
             const int yrel = y - col0;
 #pragma unroll
@@ -297,130 +323,153 @@ linear_ce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           float cs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            z[j] = ex2_approx(fmaf(z[j], L2E, -mnl));  // exp(z - m_new); missing classes give 2^-inf = 0
-            cs[j & 3] += z[j];
-            v[j] = __float_as_uint(z[j]);
+          for (int j = 0; j < 32; j += 4) {
+            // exp(z - m_new) = 2^(z*log2e - m_new*log2e); missing classes give 2^-inf = 0
+            ffma2(z[j], z[j + 1], z[j], z[j + 1], L2E, L2E, nmnl, nmnl);
+            ffma2(z[j + 2], z[j + 3], z[j + 2], z[j + 3], L2E, L2E, nmnl, nmnl);
+            z[j] = ex2_approx(z[j]); z[j + 1] = ex2_approx(z[j + 1]);
+            z[j + 2] = ex2_approx(z[j + 2]); z[j + 3] = ex2_approx(z[j + 3]);
+            fadd2(cs[0], cs[1], z[j], z[j + 1]);
+            fadd2(cs[2], cs[3], z[j + 2], z[j + 3]);
           }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(z[j]);
           s_run += (cs[0] + cs[1]) + (cs[2] + cs[3]);
           tmem_st32(taddr + c * 32, v);
           mref[c] = m_new;
           m_run = m_new;
         }
       }
-      tmem_st_wait();
 
-      // ---- exchange (m, s) with the CTAs that hold the same rows, then the row's global max and normaliser
-      {
-        const uint32_t slot = smem_u32(stats) +
-                              ((((uint32_t)a * CE_MAX_PAIRS + nj) * 2 + chalf) * BLOCK_M + q * 32 + lane) * 8;
-        for (int k = 0; k < p.pairs; ++k) st_cluster_v2f(mapa_shared(slot, 2 * k + rank), m_run, s_run);
-        fence_acq_rel_cluster();
-        __syncwarp();
-        if (lane == 0) {
-          const uint32_t sb = smem_u32(&stat_bar[a]);
-          for (int k = 0; k < p.pairs; ++k) mbar_arrive_release_cluster(mapa_shared(sb, 2 * k + rank));
+      // ---- (m, s) of the four column quarters of a row meet in this CTA's shared memory; the quarter-0 warp folds them
+      // and sends the CTA's pair to every CTA that holds the same rows (st.async: data + barrier credit travel
+      // together, so neither side needs a fence); then everybody reads the `pairs` entries of its row
+      st_shared_v2f(my_lstat, m_run, s_run);
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + q) : "memory");   // the four warps that share these 32 rows
+      if (cq == 0) {
+        if (q == 0 && lane == 0) mbar_expect_tx(&stat_bar[a], (uint32_t)p.pairs * BLOCK_M * 8);
+        float2 e4[4];
+        float mc = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          e4[k] = ld_shared_v2f(smem_u32(lstats) + (uint32_t)((k * BLOCK_M + q * 32 + lane) * 8));
+          mc = fmaxf(mc, e4[k].x);
         }
-        mbar_wait_acquire_cluster(&stat_bar[a], aph);
+        const float mcs = (mc == -INFINITY) ? 0.f : mc;   // a CTA with no real class at all sends (-inf, 0), not NaN
+        float sc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sc += e4[k].y * ex2_approx((e4[k].x - mcs) * L2E);  // empty quarter: 0 * 2^-inf
+        const uint32_t slot = smem_u32(stats) + (uint32_t)((((a * CE_MAX_PAIRS) + nj) * BLOCK_M + q * 32 + lane) * 8);
+        const uint32_t sb = smem_u32(&stat_bar[a]);
+        for (int k = 0; k < p.pairs; ++k) st_async_v2f(mapa_shared(slot, 2 * k + rank), mc, sc, mapa_shared(sb, 2 * k + rank));
       }
+      if constexpr (!kTf32) {
+        if (it > 0 && warp_live) colsum_slab_bf16();   // the previous tile's slab, while the exchange is in flight
+      }
+      mbar_wait(&stat_bar[a], aph);
       float Mx = -INFINITY, Z = 0.f;
       {
-        const uint32_t base = smem_u32(stats) + (((uint32_t)a * CE_MAX_PAIRS * 2) * BLOCK_M + q * 32 + lane) * 8;
-        float2 st[2 * CE_MAX_PAIRS];
+        const uint32_t base = smem_u32(stats) + (uint32_t)(((a * CE_MAX_PAIRS) * BLOCK_M + q * 32 + lane) * 8);
+        float2 st[CE_MAX_PAIRS];
 #pragma unroll
-        for (int k = 0; k < 2 * CE_MAX_PAIRS; ++k) {
+        for (int k = 0; k < CE_MAX_PAIRS; ++k) {
           st[k] = make_float2(-INFINITY, 0.f);
-          if (k < 2 * p.pairs) st[k] = ld_shared_v2f(base + k * BLOCK_M * 8);
+          if (k < p.pairs) st[k] = ld_shared_v2f(base + k * BLOCK_M * 8);
           Mx = fmaxf(Mx, st[k].x);
         }
 #pragma unroll
-        for (int k = 0; k < 2 * CE_MAX_PAIRS; ++k) Z += st[k].y * ex2_approx((st[k].x - Mx) * L2E);
+        for (int k = 0; k < CE_MAX_PAIRS; ++k) Z += st[k].y * ex2_approx((st[k].x - Mx) * L2E);
       }
       if (valid) {
-        if (nj == 0 && chalf == 0) loss_acc += Mx + logf(Z);          // logsumexp, once per row
-        if ((unsigned)(y - wcol0) < (unsigned)(BLOCK_N / 2)) loss_acc -= zy;  // minus the label's logit, by its owner
+        if (nj == 0 && cq == 0) loss_acc += Mx + logf(Z);                       // logsumexp, once per row
+        if ((unsigned)(y - wcol0) < (unsigned)CE_WARP_COLS) loss_acc -= zy;     // minus the label's logit, by its owner
       }
       const float inv = valid ? scale / Z : 0.f;   // ignored / out-of-range / padding rows get a zero gradient
       const float mxl = Mx * L2E;
+      tmem_st_wait();
 
       // ---- pass 2: gradient from the cached exponentials, staged in swizzled shared memory, written by TMA
 #pragma unroll
-      for (int gi = 0; gi < GROUPS_PER_WARP; ++gi) {
-        const int gcol0 = wcol0 + gi * EPR;
-        if (gcol0 >= p.N) break;  // warp-uniform
-        uint32_t vv[LDS_PER_GROUP][32];
+      for (int c = 0; c < CHUNKS; ++c) {
+        const int col0 = wcol0 + c * 32;
+        const int h = c % CHUNKS_PER_SLAB;                     // position of the chunk inside its 128-byte slab row
+        const int slab_col0 = col0 - h * 32;
+        if (slab_col0 >= p.N) break;  // warp-uniform
+        uint32_t vv[32];
+        if (col0 < p.N) tmem_ld32(taddr + c * 32, vv);
+        if (h == 0) {
+          if (lane == 0) bulk_wait_read<0>();  // the previous store of this warp has finished READING the slab
+          __syncwarp();
+        }
+        float f[32];
+        if (col0 < p.N) {  // warp-uniform
+          const float fc = ex2_approx(fmaf(mref[c], L2E, -mxl)) * inv;
+          tmem_ld_wait();
 #pragma unroll
-        for (int h = 0; h < LDS_PER_GROUP; ++h) tmem_ld32(taddr + (gi * LDS_PER_GROUP + h) * 32, vv[h]);
-        tmem_ld_wait();
-#pragma unroll
-        for (int h = 0; h < LDS_PER_GROUP; ++h) {
-          const int c = gi * LDS_PER_GROUP + h;
-          const int col0 = gcol0 + h * 32;
-          const bool live = col0 < p.N;  // warp-uniform; a dead chunk was never written in pass 1
-          const float fc = live ? ex2_approx(fmaf(mref[c], L2E, -mxl)) * inv : 0.f;
-          float f[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = live ? __uint_as_float(vv[h][j]) * fc : 0.f;
+          for (int j = 0; j < 32; j += 2) {
+            f[j] = __uint_as_float(vv[j]);
+            f[j + 1] = __uint_as_float(vv[j + 1]);
+            fmul2(f[j], f[j + 1], fc, fc);
+          }
           if (__any_sync(0xffffffffu, valid && (unsigned)(y - col0) < 32u)) {
             const int yrel = valid ? y - col0 : -1;
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = (j == yrel) ? f[j] - scale : f[j];   // minus the one-hot
           }
-          {
-            // column sums over this warp's 32 rows of what is stored (rounded to the output dtype): halving
-            // butterfly, 31 shuffles, lane i ends with the sum of column col0 + i
-            float r[32];
+        } else {  // a chunk past the last class was never written in pass 1 (TMA clips it anyway)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) r[j] = kTf32 ? f[j] : __bfloat162float(__float2bfloat16_rn(f[j]));
-#pragma unroll
-            for (int half = 16; half >= 1; half >>= 1) {
-              const bool upper = (lane & half) != 0;
-#pragma unroll
-              for (int j = 0; j < half; ++j) {
-                const float send = upper ? r[j] : r[j + half];
-                const float keep = upper ? r[j + half] : r[j];
-                r[j] = keep + __shfl_xor_sync(0xffffffffu, send, half);
-              }
-            }
-            csacc[c] += r[0];
-          }
-          if (h == 0) {  // the previous store of this warp must have finished READING the slab before we refill it
-            if (lane == 0) bulk_wait_read<0>();
-            __syncwarp();
-          }
-          const uint32_t srow = smem_u32(sbuf_ptr) + lane * 128;
-          if constexpr (kTf32) {
-#pragma unroll
-            for (int cc = 0; cc < 8; ++cc)
-              st_shared_v4(srow + ((cc ^ (lane & 7)) << 4), __float_as_uint(f[4 * cc]), __float_as_uint(f[4 * cc + 1]),
-                           __float_as_uint(f[4 * cc + 2]), __float_as_uint(f[4 * cc + 3]));
-          } else {
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc)
-              st_shared_v4(srow + (((h * 4 + cc) ^ (lane & 7)) << 4), pack_bf16x2(f[8 * cc], f[8 * cc + 1]),
-                           pack_bf16x2(f[8 * cc + 2], f[8 * cc + 3]), pack_bf16x2(f[8 * cc + 4], f[8 * cc + 5]),
-                           pack_bf16x2(f[8 * cc + 6], f[8 * cc + 7]));
-          }
+          for (int j = 0; j < 32; ++j) f[j] = 0.f;
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0 && row0 < p.M) {
-          tma_store_2d(&tmC, sbuf_ptr, gcol0, row0);
-          bulk_commit();
+        const uint32_t srow = sbuf + lane * 128;
+        if constexpr (kTf32) {
+#pragma unroll
+          for (int cc = 0; cc < 8; ++cc)
+            st_shared_v4(srow + ((cc ^ (lane & 7)) << 4), __float_as_uint(f[4 * cc]), __float_as_uint(f[4 * cc + 1]),
+                         __float_as_uint(f[4 * cc + 2]), __float_as_uint(f[4 * cc + 3]));
+        } else {
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc)
+            st_shared_v4(srow + (((h * 4 + cc) ^ (lane & 7)) << 4), pack_bf16x2(f[8 * cc], f[8 * cc + 1]),
+                         pack_bf16x2(f[8 * cc + 2], f[8 * cc + 3]), pack_bf16x2(f[8 * cc + 4], f[8 * cc + 5]),
+                         pack_bf16x2(f[8 * cc + 6], f[8 * cc + 7]));
+        }
+        if (h == CHUNKS_PER_SLAB - 1) {  // slab complete
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < p.M) {
+            tma_store_2d(&tmC, sbuf_ptr, slab_col0, row0);
+            bulk_commit();
+          }
+          if constexpr (kTf32) {  // fp32: two slabs per tile share the buffer, so each is summed right away
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < 32; r += 2) {
+              s0 += __uint_as_float(ld_shared_u32(rb_addr[r & 7] + r * 128));
+              s1 += __uint_as_float(ld_shared_u32(rb_addr[(r + 1) & 7] + (r + 1) * 128));
+            }
+            csacc[c] += s0 + s1;
+          }
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&acc_empty[a], leader);  // the accumulator stage may be overwritten
     }
+    if constexpr (!kTf32) {
+      if (it > 0 && warp_live) colsum_slab_bf16();   // the last tile's slab
+    }
     // ---- partials: one row per (cluster, CTA of the pair, lane quarter); every cell is written exactly once
     {
       const long long prow = ((long long)unit * 2 + rank) * 4 + q;
       float* dst = p.partials + prow * p.pstride;
-#pragma unroll
-      for (int c = 0; c < CHUNKS; ++c) dst[wcol0 + c * 32 + lane] = csacc[c];
+      if constexpr (kTf32) {
+        dst[wcol0 + lane] = csacc[0];
+        dst[wcol0 + 32 + lane] = csacc[1];
+      } else {
+        *reinterpret_cast<float2*>(dst + wcol0 + 2 * lane) = make_float2(csacc[0], csacc[1]);
+      }
       const float wl = warp_sum(loss_acc);
-      if (lane == 0) dst[p.pairs * BLOCK_N + nj * 2 + chalf] = wl;
+      if (lane == 0) dst[p.pairs * BLOCK_N + nj * 4 + cq] = wl;
     }
     if (lane == 0) bulk_wait_all();
   }
@@ -453,7 +502,7 @@ static int ce_max_clusters(int pairs, int* out) {
       B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * pairs * 64);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(CE_THREADS);
     cfg.dynamicSmemBytes = CE_SMEM_BYTES;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -467,6 +516,9 @@ static int ce_max_clusters(int pairs, int* out) {
     B200_REQUIRE(n >= 1, "no cluster of %d CTAs with %d bytes of shared memory fits on this device", 2 * pairs,
                  CE_SMEM_BYTES);
     cached[pairs] = n;
+    if (getenv("B200STEP_VERBOSE"))
+      fprintf(stderr, "[b200step] linear_ce: clusters of %d CTAs, %d bytes smem: %d co-resident\n", 2 * pairs,
+              CE_SMEM_BYTES, n);
   }
   *out = cached[pairs];
   return 0;
@@ -520,7 +572,7 @@ extern "C" int b200_linear_ce(const void* x, int64_t ldx, const void* w, int64_t
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(clusters * 2 * pairs);
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(CE_THREADS);
   cfg.dynamicSmemBytes = CE_SMEM_BYTES;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
@@ -535,7 +587,7 @@ extern "C" int b200_linear_ce(const void* x, int64_t ldx, const void* w, int64_t
   if (tf32) B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, linear_ce_kernel<1>, ta, tb, tc, p));
   else B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, linear_ce_kernel<0>, ta, tb, tc, p));
   // bias gradient (class columns) and loss (the 2 * pairs loss columns behind them), fixed summation order
-  return launch_reduce_partials_loss(scratch, nrows, p.pstride, (int)N, dbias, pairs * BLOCK_N, 2 * pairs,
+  return launch_reduce_partials_loss(scratch, nrows, p.pstride, (int)N, dbias, pairs * BLOCK_N, 4 * pairs,
                                      loss_scale > 0.f ? loss_scale : 1.0f / (float)M, loss_out, accumulate, n_valid,
                                      (float)M, st);
 }

@@ -120,12 +120,15 @@ def _q(t: torch.Tensor, precision: str) -> torch.Tensor:
 
 def manual_forward_backward(model: TabularMLP, dense_std: torch.Tensor, cat: torch.Tensor, labels: torch.Tensor,
                             grad_scale: float, precision: str,
-                            keep_masks: Optional[List[torch.Tensor]] = None
+                            keep_masks: Optional[List[torch.Tensor]] = None, logits_rounded: bool = False
                             ) -> Tuple[torch.Tensor, Dict[str, torch.Tensor], Dict[str, torch.Tensor]]:
     """One forward + backward written out op by op, with the storage rounding points of the bf16 GPU path:
-    activations, logits and activation-gradients are stored in bf16, accumulation is fp32, weights enter the
-    GEMMs as bf16 copies of the fp32 masters, parameter gradients are fp32.  With precision='fp32' it must agree
-    with autograd (checked in tests/test_oracle.py), which is what ties this restatement to torch's own backward.
+    hidden activations and activation-gradients are stored in bf16, accumulation is fp32, weights enter the
+    GEMMs as bf16 copies of the fp32 masters, parameter gradients are fp32.  The logits are rounded to bf16 only
+    when `logits_rounded` (the GPU path that stores them: output layer and loss as two kernels); by default the
+    output layer is fused with the loss, the logits stay in fp32 on chip and are never rounded.  With
+    precision='fp32' it must agree with autograd (checked in tests/test_oracle.py), which is what ties this
+    restatement to torch's own backward.
 
     Returns (loss, grads keyed like state_dict, intermediates)."""
     L = len(model.layers)
@@ -139,7 +142,7 @@ def manual_forward_backward(model: TabularMLP, dense_std: torch.Tensor, cat: tor
             z = z.clamp_min(0)
             if keep_masks is not None:
                 z = torch.where(keep_masks[i], z * inv_keep, torch.zeros(()))
-        acts.append(_q(z, precision))
+        acts.append(_q(z, precision) if (i < L - 1 or logits_rounded) else z)
     logits = acts[-1]
     lse = torch.logsumexp(logits, dim=1)
     loss = (lse - logits.gather(1, labels[:, None])[:, 0]).mean()
@@ -177,8 +180,10 @@ class OracleTrainer:
 
     def __init__(self, spec: Dict, dataset, *, world: int = 1, batch_size: int, seed: int = 0,
                  lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4, optimizer: str = "sgd",
-                 precision: str = "fp32", dropout_seed: int = 0, use_autograd: Optional[bool] = None):
+                 precision: str = "fp32", dropout_seed: int = 0, use_autograd: Optional[bool] = None,
+                 logits_rounded: bool = False):
         assert precision in ("fp32", "bf16")
+        self.logits_rounded = logits_rounded   # bf16 only: True = logits stored (and rounded) between layer and loss
         self.spec, self.ds, self.world, self.batch_size = dict(spec), dataset, world, batch_size
         self.precision = precision
         self.model = build_model(self.spec, seed)                                   # task.py:162,171
@@ -217,7 +222,7 @@ class OracleTrainer:
             grads = {k: p.grad.detach().clone() for k, p in self.model.named_parameters()}
             return loss.detach(), grads
         loss, grads, _ = manual_forward_backward(self.model, dense_std, cat, labels, 1.0 / rows.numel(),
-                                                 self.precision, masks)
+                                                 self.precision, masks, self.logits_rounded)
         return loss, grads
 
     def step(self) -> List[float]:

@@ -505,9 +505,8 @@ LINEAR_CE_SHAPES = [
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
 @pytest.mark.parametrize("M,N,K", LINEAR_CE_SHAPES)
 def test_linear_ce_matches_linear_then_loss(ops, dtype, M, N, K):
-    """b200_linear_ce (logits kept in tensor memory) against b200_linear_fwd + b200_ce_loss_grad (logits through
-    HBM) and against torch in fp64.  Both kernel paths round the logits to the storage dtype before the softmax, so
-    they differ only by fp32 summation order and a possible last-bit flip of a stored bf16 gradient."""
+    """b200_linear_ce (logits kept in tensor memory, fp32, never rounded) against b200_linear_fwd + b200_ce_loss_grad
+    (logits through HBM in the storage dtype) and against torch in fp64."""
     import torch.nn.functional as F
 
     x = _rand((M, K), dtype, 41)
@@ -534,20 +533,23 @@ def test_linear_ce_matches_linear_then_loss(ops, dtype, M, N, K):
     torch.cuda.synchronize()
 
     assert torch.isfinite(d.float()).all()
-    assert abs(loss.item() - loss_ref.item()) <= 1e-5 * max(1.0, abs(loss_ref.item())), (loss.item(), loss_ref.item())
-    if dtype == torch.float32:
-        torch.testing.assert_close(d, d_ref, rtol=1e-4, atol=1e-10)
-    else:   # same fp32 value up to summation order, rounded once: at most the last bf16 bit differs
-        torch.testing.assert_close(d.float(), d_ref.float(), rtol=8e-3, atol=1e-10)
     assert torch.count_nonzero(d[labels == -100]).item() == 0
     torch.testing.assert_close(db.double(), d.double().sum(0), rtol=1e-4, atol=1e-7)   # sums of what IS stored
-    # against torch in fp64 on the same stored-precision logits
-    z = logits.double().requires_grad_(True)
-    ref = F.cross_entropy(z, labels)
-    ref.backward()
-    assert abs(loss.item() - ref.item()) <= 1e-5 * max(1.0, abs(ref.item()))
-    torch.testing.assert_close(d.double(), z.grad * (n_valid.item() * scale), rtol=1e-4 if dtype == torch.float32 else 8e-3,
-                               atol=1e-9)
+    if dtype == torch.float32:
+        # same TF32 products, fp32 logits in both paths: only the order of the fp32 sums differs
+        assert abs(loss.item() - loss_ref.item()) <= 1e-5 * max(1.0, abs(loss_ref.item()))
+        torch.testing.assert_close(d, d_ref, rtol=1e-4, atol=1e-10)
+    else:
+        # bf16 operands are exact in the tensor core, accumulation is fp32: the fused kernel's logits are the fp64
+        # ones to ~1e-6, so its gradient is torch's fp64 gradient rounded once to bf16 ...
+        z = (x.double() @ w.double().t() + b.double()).requires_grad_(True)
+        ref = F.cross_entropy(z, labels)
+        ref.backward()
+        assert abs(loss.item() - ref.item()) <= 1e-5 * max(1.0, abs(ref.item())), (loss.item(), ref.item())
+        torch.testing.assert_close(d.double(), z.grad * (M * scale), rtol=8e-3, atol=1e-9)
+        # ... while the two-kernel path first rounds every logit to bf16 (|dz| <= 2^-9 |z|): close, not equal
+        assert abs(loss.item() - loss_ref.item()) <= 2e-3 * max(1.0, abs(loss_ref.item()))
+        assert (d.float() - d_ref.float()).norm() <= 2e-2 * d_ref.float().norm()
     # deterministic, and `accumulate` adds onto loss / bias gradient
     loss2, db2 = loss.clone(), db.clone()
     ops.linear_ce(x, w, b, labels, d, loss2, db2, scratch, M=M, N=N, K=K, grad_scale=scale, n_valid=n_valid,

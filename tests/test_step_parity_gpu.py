@@ -30,12 +30,14 @@ SMALL = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=50, hidden=(64, 32
 
 
 def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True,
-              micro_rows=0):
+              micro_rows=0, fused_ce=True):
+    """fused_ce=True (the default schedule): output layer + loss in one kernel, logits never stored; False: the
+    two-kernel path with stored (bf16-rounded) logits, which the oracle mirrors with logits_rounded."""
     ds = make_synthetic(rows, spec)
     oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, seed=seed, optimizer=optimizer,
-                           precision=precision, lr=lr)
+                           precision=precision, lr=lr, logits_rounded=not fused_ce)
     cfg = StepConfig(batch_size=batch, precision=precision, optimizer=optimizer, lr=lr, use_graph=use_graph,
-                     keep_logits=True, micro_rows=micro_rows)
+                     keep_logits=not fused_ce, fused_ce=fused_ce, micro_rows=micro_rows)
     eng = TrainStep(spec, init_parameters(spec, seed), ds, rank_indices(rows, 1, 0), cfg)
     o_losses, g_losses = [], []
     for _ in range(steps):
@@ -84,11 +86,12 @@ def test_preprocess_bit_exact_vs_oracle(precision):
     assert torch.equal(eng.idx.cpu().long(), ds.cat[r])
 
 
+@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused-ce", "two-kernel-ce"])
 @pytest.mark.parametrize("precision,optimizer", [("fp32", "sgd"), ("bf16", "sgd"), ("bf16", "adam"), ("fp32", "adam")])
-def test_small_model_n_steps(precision, optimizer):
+def test_small_model_n_steps(precision, optimizer, fused_ce):
     lr = 0.1 if optimizer == "sgd" else 1e-3
     ds, oracle, eng, lo, lg = _run_pair(SMALL, rows=2048, batch=256, steps=24, precision=precision,
-                                        optimizer=optimizer, lr=lr)
+                                        optimizer=optimizer, lr=lr, fused_ce=fused_ce)
     # per-step loss: TF32 inputs (10-bit mantissa) against a true-fp32 oracle -> rel 2e-3;
     # bf16 path against the bf16-storage oracle: same rounding points, fp32 accumulation order differs -> rel 2e-3
     for a, b in zip(lo, lg):
@@ -99,11 +102,12 @@ def test_small_model_n_steps(precision, optimizer):
     assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
 
 
+@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused-ce", "two-kernel-ce"])
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
-def test_t0_batch4096(precision):
+def test_t0_batch4096(precision, fused_ce):
     """BASELINE config 2 shape (T0, batch 4096): 6 steps, graph replay, 2 distinct batches per epoch."""
     spec = ARCHS["tabular_mlp"]
-    ds, oracle, eng, lo, lg = _run_pair(spec, rows=8192, batch=4096, steps=6, precision=precision)
+    ds, oracle, eng, lo, lg = _run_pair(spec, rows=8192, batch=4096, steps=6, precision=precision, fused_ce=fused_ce)
     for a, b in zip(lo, lg):
         assert abs(a - b) <= 2e-3 * max(1.0, abs(a)), (lo, lg)
     assert _param_err(oracle, eng) <= 5e-3
