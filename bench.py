@@ -448,7 +448,8 @@ def profile_kernels(eng, spec, B, world):
 
     from b200step import ops
 
-    names = ["preprocess", "linear_fwd", "linear_ce", "ce_loss_grad", "linear_dgrad", "linear_wgrad", "linear_wgrad_grouped",
+    names = ["preprocess", "linear_fwd", "linear_ce", "ce_loss_grad", "linear_dgrad", "linear_dgrad_emb", "linear_wgrad",
+             "linear_wgrad_grouped",
              "colsum", "emb_bwd", "zero", "sgd_step", "adam_step"]
     records = []
     orig = {n: getattr(ops, n) for n in names}
@@ -465,6 +466,10 @@ def profile_kernels(eng, spec, B, world):
             if name == "linear_wgrad_grouped":
                 label = f"linear_wgrad_grouped[{k['M']}x{len(k['Ns'])} layers]"
                 work = {"flops": sum(2.0 * k["M"] * n_ * k_ for n_, k_ in zip(k["Ns"], k["Ks"]))}
+            elif name == "linear_dgrad_emb":
+                kk = k["num_cat"] * k["embed_dim"]
+                label = f"linear_dgrad_emb[{k['M']}x{k['N']}x{kk}]"
+                work = {"flops": 2.0 * k["M"] * k["N"] * kk}   # embedding columns only; the scatter rides along
             elif name.startswith("linear_"):
                 M, N, K = k["M"], k["N"], k["K"]
                 label = f"{name}[{M}x{N}x{K}]" + ("+dbias" if k.get("dbias") is not None else "")

@@ -107,6 +107,16 @@ int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw,
                       int64_t M, int64_t N, int64_t K, int dtype, int flags, float dscale,
                       const uint32_t* relu_mask, int64_t ldmask,
                       float* dbias, float* scratch, int64_t scratch_floats, b200_stream_t stream);
+/* dgrad of the FIRST Linear fused with the embedding backward (task.py:311; addmm backward wrt input followed by
+ * embedding_dense_backward): the input row of that layer starts with the concatenated embedding rows
+ * [num_tables x embed_dim], so
+ *     dtables[t][idx[m,t]][:] += (dy[M,N] . w[N, 0 : num_tables*embed_dim])[m, t*embed_dim : (t+1)*embed_dim]
+ * straight from the fp32 accumulator (red.add; dtables must hold zeros or the value to add onto).  The input
+ * gradient itself is never stored — it has no other consumer — which removes its HBM round trip and the separate
+ * b200_emb_bwd launch.  idx: the int32 ids b200_preprocess wrote ([M, ld_idx]); embed_dim: a power of two >= 4. */
+int b200_linear_dgrad_emb(const void* dy, int64_t lddy, const void* w, int64_t ldw, const int32_t* idx,
+                          int64_t ld_idx, float* dtables, int64_t M, int64_t N, int num_tables,
+                          int64_t table_rows, int embed_dim, int dtype, b200_stream_t stream);
 /* wgrad of `count` (<= 8) layers that share the batch dimension M, in ONE launch: dw[j] += dy[j]^T . x[j].  All
  * arrays are HOST arrays of length count.  Results are accumulated with red.add: every dw[j] must hold zeros (or the
  * value to add onto).  One launch instead of `count`, and the epilogue of one work unit overlaps the MMAs of the next. */

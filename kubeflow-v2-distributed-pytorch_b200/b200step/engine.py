@@ -64,6 +64,9 @@ class StepConfig:
                                          # +0.6 % at 2 GPUs, -2 % at 8 GPUs (profiles/r01_comm_overlap_experiments.md)
     fused_ce: Optional[bool] = None      # output layer + cross-entropy as one kernel (K-gemm-ce): the logits never go to
                                          # HBM.  None = whenever it applies (<= 1024 classes, logits not kept)
+    fused_emb_bwd: Optional[bool] = None # layer-0 dgrad adds its output straight onto the table gradients (no dx0
+                                         # matrix, no separate scatter kernel).  None = whenever the embedding width
+                                         # is a power of two
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1
@@ -166,7 +169,12 @@ class TrainStep:
         wmax = (max([o for (_, o) in dims[:-1]] + [8]) + 7) // 8 * 8
         # gradient wrt each hidden activation; all stay alive until the wgrad phase
         self.dh = [torch.zeros(B, wmax, dtype=self.dt, device=dev) for _ in range(max(self.L - 1, 1))]
-        self.dx0 = torch.zeros(B, self.k0, dtype=self.dt, device=dev)
+        ed = spec.embed_dim
+        pow2 = ed >= 4 and (ed & (ed - 1)) == 0
+        self.fused_emb = (spec.num_cat > 0 and pow2) if cfg.fused_emb_bwd is None else cfg.fused_emb_bwd
+        if self.fused_emb and not (spec.num_cat > 0 and pow2):
+            raise ValueError("fused_emb_bwd needs categorical features with a power-of-two embedding width >= 4")
+        self.dx0 = None if self.fused_emb else torch.zeros(B, self.k0, dtype=self.dt, device=dev)
         self.y = torch.zeros(B, dtype=torch.int64, device=dev)
         self.idx = torch.zeros(B, max(spec.num_cat, 1), dtype=torch.int32, device=dev)
         self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -358,12 +366,19 @@ class TrainStep:
                 n += 2 if cfg.deterministic_bias_grad else 1
                 dys[li - 1] = dx
             if spec.num_cat:
-                ops.linear_dgrad(dys[0], self._w(0), None, self.dx0[sl], M=rows, N=dims[0][1], K=self.k0,
-                                 relu=False, stream=st)
                 # (the table gradients were zeroed by the previous optimizer pass / at allocation)
-                ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
-                            num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim, stream=st)
-                n += 2
+                if self.fused_emb:
+                    ops.linear_dgrad_emb(dys[0], self._w(0), self.idx[sl], self.gtables, M=rows, N=dims[0][1],
+                                         num_cat=spec.num_cat, table_rows=spec.cardinality,
+                                         embed_dim=spec.embed_dim, stream=st)
+                    n += 1
+                else:
+                    ops.linear_dgrad(dys[0], self._w(0), None, self.dx0[sl], M=rows, N=dims[0][1], K=self.k0,
+                                     relu=False, stream=st)
+                    ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
+                                num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim,
+                                stream=st)
+                    n += 2
                 if last_chunk:
                     for bi in bucket_of.get(-1, []):
                         n += self._reduce_bucket(bi)

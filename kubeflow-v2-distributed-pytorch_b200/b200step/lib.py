@@ -36,6 +36,7 @@ SIGNATURES = {
                              _p]),
     "b200_linear_dgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _p, _i64, _p,
                                _p, _i64, _p]),
+    "b200_linear_dgrad_emb": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i, _i64, _i, _i, _p]),
     "b200_linear_wgrad_grouped": (_i, [_i, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _i, _p]),
     "b200_dgrad_scratch_floats": (_i64, [_i64, _i64]),
     "b200_linear_wgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _p]),

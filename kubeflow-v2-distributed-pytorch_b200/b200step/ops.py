@@ -75,6 +75,14 @@ def linear_dgrad(dy, w, act, dx, *, M: int, N: int, K: int, relu: bool, dscale: 
                            scratch.numel() if scratch is not None else 0, _stream(stream))
 
 
+def linear_dgrad_emb(dy, w, idx, dtables, *, M: int, N: int, num_cat: int, table_rows: int, embed_dim: int,
+                     stream=None):
+    """Layer-0 dgrad whose output goes straight onto the embedding-table gradients (no dx0, no emb_bwd launch)."""
+    _cuda(dy, w, idx, dtables)
+    get_lib().linear_dgrad_emb(ptr(dy), dy.stride(0), ptr(w), w.stride(0), ptr(idx), idx.stride(0), ptr(dtables), M,
+                               N, num_cat, table_rows, embed_dim, dtype_code(dy.dtype), _stream(stream))
+
+
 def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False, stream=None):
     _cuda(dy, x, dw)
     get_lib().linear_wgrad(ptr(dy), dy.stride(0), ptr(x), x.stride(0), ptr(dw), dw.stride(0), M, N, K,

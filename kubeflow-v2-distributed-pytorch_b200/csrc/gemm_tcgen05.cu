@@ -15,7 +15,7 @@
 
 namespace b200 {
 
-enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2 };
+enum { EPI_FWD = 0, EPI_DGRAD = 1, EPI_WGRAD = 2, EPI_EMB = 3 };
 
 struct GemmParams {
   int M, N;          // D is M x N
@@ -38,6 +38,12 @@ struct GemmParams {
   const int* step;
   int layer_id;
   long long row0;            // fwd dropout: row index of this call's first row inside the whole batch
+  // EPI_EMB: the output columns are the concatenated embedding rows of a sample; they are not stored but added
+  // onto the table gradients, out = dtables[num_tables][emb_rows][1 << emb_shift]
+  const int32_t* emb_idx;    // [M, ld_idx] table row of sample m in table t
+  long long ld_idx;
+  long long emb_rows;
+  int emb_shift;             // log2(embedding width)
 };
 
 // kCtas = 2: the two CTAs of a cluster form a pair (tcgen05 cta_group::2).  The pair owns a 256 x 256 tile: each CTA
@@ -79,7 +85,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if constexpr (kEpi != EPI_WGRAD) tma_prefetch_desc(&tmC);
+    if constexpr (kEpi != EPI_WGRAD && kEpi != EPI_EMB) tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < NUM_STAGES; ++i) {
@@ -258,6 +264,36 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               } else {
                 *reinterpret_cast<uint4*>(o + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
               }
+            }
+          }
+        }
+      } else if constexpr (kEpi == EPI_EMB) {
+        // Layer-0 dgrad whose output row is [26 x dim embedding gradients]: nothing is stored.  Every 16 bytes of
+        // accumulator go straight onto the gradient of the table row the sample looked up (fp32 red.add, no bf16
+        // rounding on the way): the dx0 matrix, its HBM round trip and the separate scatter kernel disappear.
+        const int dim = 1 << p.emb_shift;
+#pragma unroll 1
+        for (int c = chalf * (BLOCK_N / 64); c < (chalf + 1) * (BLOCK_N / 64); ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (!row_ok) continue;
+          const int32_t* ids = p.emb_idx + (long long)row * p.ld_idx;
+          float* dst = nullptr;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const int col = col0 + j;
+            if (col < p.N) {  // N = num_tables * dim, a multiple of 4
+              const int off = col & (dim - 1);
+              if (j == 0 || off == 0) {  // first chunk of this thread's slice of a table row
+                const int t = col >> p.emb_shift;
+                dst = reinterpret_cast<float*>(p.out) + (((long long)t * p.emb_rows + __ldg(ids + t)) << p.emb_shift) + off;
+              }
+              red_add_v4(dst, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                         __uint_as_float(v[j + 3]));
+              dst += 4;
             }
           }
         }
@@ -811,6 +847,40 @@ extern "C" int64_t b200_dgrad_scratch_floats(int64_t M, int64_t K) {
   (void)M;
   (void)K;
   return (int64_t)sm_count_physical() * 4 * BLOCK_N;
+}
+
+// Layer-0 dgrad fused with the embedding backward: dtables[t][idx[m,t]][:] += (dy[M,N] . w[N, :num_tables*dim])[m, t*dim : (t+1)*dim]
+extern "C" int b200_linear_dgrad_emb(const void* dy, int64_t lddy, const void* w, int64_t ldw, const int32_t* idx,
+                                     int64_t ld_idx, float* dtables, int64_t M, int64_t N, int num_tables,
+                                     int64_t table_rows, int embed_dim, int dtype, b200_stream_t stream) {
+  const int64_t K = (int64_t)num_tables * embed_dim;
+  if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(embed_dim >= 4 && (embed_dim & (embed_dim - 1)) == 0,
+               "b200_linear_dgrad_emb needs a power-of-two embedding width >= 4 (got %d); use b200_linear_dgrad + "
+               "b200_emb_bwd", embed_dim);
+  B200_REQUIRE(idx != nullptr && dtables != nullptr && ld_idx >= num_tables, "idx / dtables missing or ld_idx too small");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(dtables) & 15) == 0, "dtables must be 16-byte aligned");
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;
+  const int epr = tf32 ? 32 : 64;
+  CUtensorMap ta, tb;
+  if (int r = make_tmap(&ta, tf32, dy, N, M, lddy, bk, BLOCK_M)) return r;
+  // only the embedding columns of W are read: the tensor map ends at K, boxes past it are zero-filled
+  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, epr, bk, true)) return r;
+  GemmParams p{};
+  p.M = (int)M; p.N = (int)K;
+  const int tile_m = BLOCK_M * gemm_ctas();
+  p.k_blocks = (int)((N + bk - 1) / bk);
+  p.m_tiles = (int)((M + tile_m - 1) / tile_m);
+  p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
+  p.splits = 1; p.kb_per_split = p.k_blocks;
+  p.out = dtables; p.dscale = 1.f;
+  p.emb_idx = idx; p.ld_idx = ld_idx; p.emb_rows = table_rows;
+  p.emb_shift = 0;
+  while ((1 << p.emb_shift) < embed_dim) ++p.emb_shift;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return tf32 ? launch_gemm<1, false, true, EPI_EMB>(ta, tb, ta /*unused*/, p, st)
+              : launch_gemm<0, false, true, EPI_EMB>(ta, tb, ta /*unused*/, p, st);
 }
 
 extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, int64_t ldx, float* dw,

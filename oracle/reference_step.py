@@ -120,13 +120,16 @@ def _q(t: torch.Tensor, precision: str) -> torch.Tensor:
 
 def manual_forward_backward(model: TabularMLP, dense_std: torch.Tensor, cat: torch.Tensor, labels: torch.Tensor,
                             grad_scale: float, precision: str,
-                            keep_masks: Optional[List[torch.Tensor]] = None, logits_rounded: bool = False
-                            ) -> Tuple[torch.Tensor, Dict[str, torch.Tensor], Dict[str, torch.Tensor]]:
+                            keep_masks: Optional[List[torch.Tensor]] = None, logits_rounded: bool = False,
+                            dx0_rounded: bool = False) -> Tuple[torch.Tensor, Dict[str, torch.Tensor], Dict[str, torch.Tensor]]:
     """One forward + backward written out op by op, with the storage rounding points of the bf16 GPU path:
     hidden activations and activation-gradients are stored in bf16, accumulation is fp32, weights enter the
     GEMMs as bf16 copies of the fp32 masters, parameter gradients are fp32.  The logits are rounded to bf16 only
     when `logits_rounded` (the GPU path that stores them: output layer and loss as two kernels); by default the
-    output layer is fused with the loss, the logits stay in fp32 on chip and are never rounded.  With
+    output layer is fused with the loss, the logits stay in fp32 on chip and are never rounded.  Likewise the
+    gradient with respect to the model input is rounded only when `dx0_rounded` (the path that stores it for a
+    separate embedding-backward kernel); by default the first layer's dgrad adds it onto the table gradients in
+    fp32.  With
     precision='fp32' it must agree with autograd (checked in tests/test_oracle.py), which is what ties this
     restatement to torch's own backward.
 
@@ -159,7 +162,7 @@ def manual_forward_backward(model: TabularMLP, dense_std: torch.Tensor, cat: tor
             if keep_masks is not None:
                 dx = dx * inv_keep
             dx = torch.where(acts[i] > 0, dx, torch.zeros(()))
-        dy = _q(dx, precision)
+        dy = _q(dx, precision) if (i > 0 or dx0_rounded) else dx
     inter["dx0"] = dy
     nd, d = model.num_dense, model.embed_dim
     for t in range(model.num_cat):
@@ -181,9 +184,10 @@ class OracleTrainer:
     def __init__(self, spec: Dict, dataset, *, world: int = 1, batch_size: int, seed: int = 0,
                  lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4, optimizer: str = "sgd",
                  precision: str = "fp32", dropout_seed: int = 0, use_autograd: Optional[bool] = None,
-                 logits_rounded: bool = False):
+                 logits_rounded: bool = False, dx0_rounded: bool = False):
         assert precision in ("fp32", "bf16")
         self.logits_rounded = logits_rounded   # bf16 only: True = logits stored (and rounded) between layer and loss
+        self.dx0_rounded = dx0_rounded         # bf16 only: True = input gradient stored (and rounded) before the scatter
         self.spec, self.ds, self.world, self.batch_size = dict(spec), dataset, world, batch_size
         self.precision = precision
         self.model = build_model(self.spec, seed)                                   # task.py:162,171
@@ -222,7 +226,7 @@ class OracleTrainer:
             grads = {k: p.grad.detach().clone() for k, p in self.model.named_parameters()}
             return loss.detach(), grads
         loss, grads, _ = manual_forward_backward(self.model, dense_std, cat, labels, 1.0 / rows.numel(),
-                                                 self.precision, masks, self.logits_rounded)
+                                                 self.precision, masks, self.logits_rounded, self.dx0_rounded)
         return loss, grads
 
     def step(self) -> List[float]:

@@ -568,3 +568,55 @@ def test_linear_ce_rejects_more_than_1024_classes(ops):
                       torch.zeros(128, 1032, dtype=torch.bfloat16, device="cuda"), torch.zeros(1, device="cuda"), None,
                       torch.zeros(ops.linear_ce_scratch_floats(1024), device="cuda"), M=128, N=1032, K=64,
                       grad_scale=1.0)
+
+
+# ------------------------------------------------------------ layer-0 dgrad + embedding backward in one kernel
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "f32"])
+@pytest.mark.parametrize("M,N,nc,rows,dim", [
+    (4096, 512, 26, 1000, 16),      # T0
+    (1000, 64, 26, 50, 16),         # small test model, ragged batch
+    (2048, 1024, 26, 4096, 64),     # T1 row shape (dim 64 = two 32-column chunks per table row)
+    (333, 128, 40, 17, 8),          # four tables per 32-column chunk, > 32 tables
+    (512, 64, 3, 9, 4),
+])
+def test_linear_dgrad_emb_matches_dgrad_then_scatter(ops, dtype, M, N, nc, rows, dim):
+    """b200_linear_dgrad_emb against b200_linear_dgrad + b200_emb_bwd and against torch index_add_ in fp64."""
+    K = nc * dim
+    kpad = (K + 13 + 63) // 64 * 64                       # the step's padded layer-0 width (dense + pad behind)
+    dy = _rand((M, N), dtype, 51, 0.05)
+    w = _rand((N, kpad), dtype, 52, 0.1)
+    g = torch.Generator().manual_seed(53)
+    idx = torch.randint(0, rows, (M, nc), generator=g, dtype=torch.int32).cuda()
+    ref = torch.zeros(nc * rows * dim, device="cuda")
+    dx = torch.empty(M, kpad, dtype=dtype, device="cuda")
+    ops.linear_dgrad(dy, w, None, dx, M=M, N=N, K=kpad, relu=False)
+    ops.emb_bwd(dx, idx, ref, batch=M, num_cat=nc, table_rows=rows, embed_dim=dim)
+    got = torch.zeros_like(ref)
+    ops.linear_dgrad_emb(dy, w, idx, got, M=M, N=N, num_cat=nc, table_rows=rows, embed_dim=dim)
+    torch.cuda.synchronize()
+    exact = torch.zeros(nc, rows, dim, dtype=torch.float64, device="cuda")
+    dx64 = (dy.double() @ w.double())[:, :K].view(M, nc, dim)
+    for t in range(nc):
+        exact[t].index_add_(0, idx[:, t].long(), dx64[:, t])
+    exact = exact.flatten()
+    scale = exact.abs().max().item()
+    # the fused kernel adds fp32 accumulators (bf16: exact products; f32: TF32 products) -> close to fp64;
+    # the two-kernel path rounds dx to the storage dtype first
+    tol = 2e-5 if dtype == torch.bfloat16 else 2e-3
+    assert (got.double() - exact).abs().max().item() <= tol * scale
+    assert (ref.double() - exact).abs().max().item() <= (1e-2 if dtype == torch.bfloat16 else 2e-3) * scale
+    # accumulates onto what is there
+    ops.linear_dgrad_emb(dy, w, idx, got, M=M, N=N, num_cat=nc, table_rows=rows, embed_dim=dim)
+    torch.cuda.synchronize()
+    assert (got.double() - 2 * exact).abs().max().item() <= 2 * tol * scale
+
+
+def test_linear_dgrad_emb_rejects_odd_embedding_width(ops):
+    from b200step.lib import B200Error
+
+    with pytest.raises(B200Error, match="power-of-two"):
+        ops.linear_dgrad_emb(torch.zeros(128, 64, dtype=torch.bfloat16, device="cuda"),
+                             torch.zeros(64, 64, dtype=torch.bfloat16, device="cuda"),
+                             torch.zeros(128, 4, dtype=torch.int32, device="cuda"),
+                             torch.zeros(4 * 10 * 12, device="cuda"),
+                             M=128, N=64, num_cat=4, table_rows=10, embed_dim=12)

@@ -31,13 +31,14 @@ SMALL = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=50, hidden=(64, 32
 
 def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True,
               micro_rows=0, fused_ce=True):
-    """fused_ce=True (the default schedule): output layer + loss in one kernel, logits never stored; False: the
-    two-kernel path with stored (bf16-rounded) logits, which the oracle mirrors with logits_rounded."""
+    """fused_ce=True (the default schedule): output layer + loss in one kernel (logits never stored) and layer-0
+    dgrad + embedding scatter in one kernel (input gradient never stored); False: the unfused kernels with stored
+    (bf16-rounded) logits and input gradient, which the oracle mirrors with logits_rounded / dx0_rounded."""
     ds = make_synthetic(rows, spec)
     oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, seed=seed, optimizer=optimizer,
-                           precision=precision, lr=lr, logits_rounded=not fused_ce)
+                           precision=precision, lr=lr, logits_rounded=not fused_ce, dx0_rounded=not fused_ce)
     cfg = StepConfig(batch_size=batch, precision=precision, optimizer=optimizer, lr=lr, use_graph=use_graph,
-                     keep_logits=not fused_ce, fused_ce=fused_ce, micro_rows=micro_rows)
+                     keep_logits=not fused_ce, fused_ce=fused_ce, fused_emb_bwd=fused_ce, micro_rows=micro_rows)
     eng = TrainStep(spec, init_parameters(spec, seed), ds, rank_indices(rows, 1, 0), cfg)
     o_losses, g_losses = [], []
     for _ in range(steps):
@@ -86,7 +87,7 @@ def test_preprocess_bit_exact_vs_oracle(precision):
     assert torch.equal(eng.idx.cpu().long(), ds.cat[r])
 
 
-@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused-ce", "two-kernel-ce"])
+@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused", "unfused"])
 @pytest.mark.parametrize("precision,optimizer", [("fp32", "sgd"), ("bf16", "sgd"), ("bf16", "adam"), ("fp32", "adam")])
 def test_small_model_n_steps(precision, optimizer, fused_ce):
     lr = 0.1 if optimizer == "sgd" else 1e-3
@@ -102,7 +103,7 @@ def test_small_model_n_steps(precision, optimizer, fused_ce):
     assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
 
 
-@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused-ce", "two-kernel-ce"])
+@pytest.mark.parametrize("fused_ce", [True, False], ids=["fused", "unfused"])
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_t0_batch4096(precision, fused_ce):
     """BASELINE config 2 shape (T0, batch 4096): 6 steps, graph replay, 2 distinct batches per epoch."""
