@@ -64,9 +64,11 @@ class StepConfig:
                                          # +0.6 % at 2 GPUs, -2 % at 8 GPUs (profiles/r01_comm_overlap_experiments.md)
     fused_ce: Optional[bool] = None      # output layer + cross-entropy as one kernel (K-gemm-ce): the logits never go to
                                          # HBM.  None = whenever it applies (<= 1024 classes, logits not kept)
-    fused_emb_bwd: Optional[bool] = None # layer-0 dgrad adds its output straight onto the table gradients (no dx0
-                                         # matrix, no separate scatter kernel).  None = whenever the embedding width
-                                         # is a power of two
+    fused_emb_bwd: bool = False          # layer-0 dgrad adds its output straight onto the table gradients (no dx0
+                                         # matrix, no separate scatter kernel).  Off by default: measured on T0 the
+                                         # 6.8 M L2 atomics per step take as long from the GEMM epilogue as from the
+                                         # scatter kernel (67 us fused vs 35 + 31 us) and 3x longer on Zipf ids;
+                                         # K-embbwd's shared-memory privatisation is what cuts them
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1
@@ -171,7 +173,7 @@ class TrainStep:
         self.dh = [torch.zeros(B, wmax, dtype=self.dt, device=dev) for _ in range(max(self.L - 1, 1))]
         ed = spec.embed_dim
         pow2 = ed >= 4 and (ed & (ed - 1)) == 0
-        self.fused_emb = (spec.num_cat > 0 and pow2) if cfg.fused_emb_bwd is None else cfg.fused_emb_bwd
+        self.fused_emb = bool(cfg.fused_emb_bwd)
         if self.fused_emb and not (spec.num_cat > 0 and pow2):
             raise ValueError("fused_emb_bwd needs categorical features with a power-of-two embedding width >= 4")
         self.dx0 = None if self.fused_emb else torch.zeros(B, self.k0, dtype=self.dt, device=dev)

@@ -6,6 +6,8 @@
 // optimizer.step() (task.py:312).  All of these are pure streaming kernels: 128-bit loads/stores,
 // grid sized to a multiple of the SM count, 20 B/param (SGD) or 28 B/param (Adam) of HBM traffic
 // plus 2 B/param for the bf16 operand copy where one is kept.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -127,6 +129,10 @@ __global__ void advance_step_kernel(int* cursor, int* step, int steps_per_epoch)
 // the gradient row (embedding columns start at emb_col0, a multiple of 4 — column 0 in the step's layout) and one
 // 128-bit red.global.add.v4.f32 into the table gradient.  Consecutive lanes read consecutive chunks (coalesced);
 // the scatter side is index-driven by nature and resolves in L2.
+// Measured alternatives (profiles/r02_emb_bwd_experiments.md): a per-table shared-memory copy filled with atomicAdd
+// is 2.7x SLOWER (fp32 shared-memory atomics are compare-and-swap loops on sm_100: 90 us against 33 us), and issuing
+// the same red.adds from the layer-0 dgrad epilogue (b200_linear_dgrad_emb) takes as long as GEMM + scatter: the
+// 6.8 M L2 atomics per step are the floor either way.
 template <bool kBf16>
 __global__ void __launch_bounds__(OPT_THREADS)
 emb_bwd_kernel(const void* __restrict__ dx_, long long lddx, const int32_t* __restrict__ idx,

@@ -31,9 +31,9 @@ SMALL = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=50, hidden=(64, 32
 
 def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True,
               micro_rows=0, fused_ce=True):
-    """fused_ce=True (the default schedule): output layer + loss in one kernel (logits never stored) and layer-0
-    dgrad + embedding scatter in one kernel (input gradient never stored); False: the unfused kernels with stored
-    (bf16-rounded) logits and input gradient, which the oracle mirrors with logits_rounded / dx0_rounded."""
+    """fused_ce=True: output layer + loss in one kernel (logits never stored; the default schedule) and, opt-in,
+    layer-0 dgrad + embedding scatter in one kernel (input gradient never stored); False: the unfused kernels with
+    stored (bf16-rounded) logits and input gradient, which the oracle mirrors with logits_rounded / dx0_rounded."""
     ds = make_synthetic(rows, spec)
     oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, seed=seed, optimizer=optimizer,
                            precision=precision, lr=lr, logits_rounded=not fused_ce, dx0_rounded=not fused_ce)
