@@ -307,7 +307,9 @@ def run_b200(args, rank, local_rank, world):
         cfg.peer_optimizer = True
     if os.environ.get("B200STEP_PREFETCH_RESERVE"):
         cfg.prefetch_sm_reserve = int(os.environ["B200STEP_PREFETCH_RESERVE"])
-    if os.environ.get("B200STEP_PREFETCH_PRE"):           # A/B: K-pre of the next batch under the last all-reduces
+    if os.environ.get("B200STEP_PREFETCH_CTAS"):          # A/B: CTA slots per SM of the overlapped K-pre
+        cfg.prefetch_ctas_per_sm = int(os.environ["B200STEP_PREFETCH_CTAS"])
+    if os.environ.get("B200STEP_PREFETCH_PRE"):           # A/B: K-pre of the next batch under wgrad / the all-reduces
         cfg.prefetch_pre = os.environ["B200STEP_PREFETCH_PRE"] != "0"
     idx = rank_indices(rows, world, rank)
     # keep only this rank's rows resident (same values as the global dataset, re-indexed 0..n-1)

@@ -72,6 +72,9 @@ int b200_set_status_word(uint32_t* device_word);
  * label_stats (nullable): 4 zero-initialised int32 of device memory; after the kernel, label_stats[0] = number of
  * rows of this batch whose label != ignore_index (what nn.CrossEntropyLoss's mean divides by, loss.py:1379-1387);
  * words 1..3 are the kernel's own accumulator / ticket and return to zero, so a captured graph can be replayed.
+ * max_ctas > 0 caps the grid (256-thread CTAs, no shared memory): a launch that is meant to run UNDER another
+ * kernel (the next batch's preprocessing under this step's wgrad GEMMs) takes one or two CTA slots per SM instead of
+ * filling the device, so the persistent GEMM grid launched after it still finds room on every SM.
  */
 int b200_preprocess(const float* ds_dense, const void* ds_cat, int cat_id_bytes, const int64_t* ds_label,
                     const int64_t* row_idx, const int32_t* cursor,
@@ -79,7 +82,7 @@ int b200_preprocess(const float* ds_dense, const void* ds_cat, int cat_id_bytes,
                     void* x_out, int64_t* y_out, int32_t* idx_out,
                     int64_t batch, int num_dense, int num_cat, int64_t table_rows, int embed_dim,
                     int64_t ldx, int x_dtype, int64_t cursor_stride, int32_t* label_stats, int64_t ignore_index,
-                    b200_stream_t stream);
+                    int max_ctas, b200_stream_t stream);
 
 /* ---- K-gemm: tcgen05/TMEM linear layers ----------------------------------------------------
  * M = batch rows, N = out_features, K = in_features for all three.

@@ -58,10 +58,14 @@ class StepConfig:
                                          # over NVLink peer memory, applies the optimizer and writes the new
                                          # parameters to every rank (csrc/peer.cu) instead of NCCL all-reduce +
                                          # optimizer launch.  Single node, world <= 8
-    prefetch_pre: bool = False           # run K-pre of the NEXT batch inside this step, right after the embedding
-                                         # tables' optimizer launch, i.e. under the all-reduces still in flight
-                                         # (device-resident `step()` path only).  Off by default: measured on T0
-                                         # +0.6 % at 2 GPUs, -2 % at 8 GPUs (profiles/r01_comm_overlap_experiments.md)
+    prefetch_pre: Optional[bool] = None  # run K-pre of the NEXT batch inside this step (device-resident `step()`
+                                         # path only).  world == 1: the table gradients are complete before the wgrad
+                                         # GEMMs start, so a side stream updates the tables and gathers the next batch
+                                         # UNDER the wgrad launch (x0 is double-buffered: wgrad still reads this
+                                         # batch's).  world > 1: K-pre follows the embedding tables' optimizer launch,
+                                         # under the all-reduces still in flight (+0.6 % at 2 GPUs, -2 % at 8 GPUs on
+                                         # T0, profiles/r01_comm_overlap_experiments.md).  None = on when world == 1
+    prefetch_ctas_per_sm: int = 2        # CTA slots per SM the overlapped K-pre takes (the GEMM grid needs the rest)
     fused_ce: Optional[bool] = None      # output layer + cross-entropy as one kernel (K-gemm-ce): the logits never go to
                                          # HBM.  None = whenever it applies (<= 1024 classes, logits not kept)
     fused_emb_bwd: bool = False          # layer-0 dgrad adds its output straight onto the table gradients (no dx0
@@ -165,7 +169,9 @@ class TrainStep:
         dims = spec.layer_dims
         self.L = len(dims)
         self.k0 = spec.in_features_padded
-        self.x0 = torch.zeros(B, self.k0, dtype=self.dt, device=dev)
+        # the preprocessed batch; two buffers so that the next batch can be gathered while wgrad still reads this one
+        self.x0s = [torch.zeros(B, self.k0, dtype=self.dt, device=dev) for _ in range(2)]
+        self.cur = 0
         self.acts = [torch.zeros(B, o, dtype=self.dt, device=dev) for (_, o) in dims]  # acts[-1] = logits
         self.dlogits = torch.zeros_like(self.acts[-1]) if cfg.keep_logits else self.acts[-1]
         wmax = (max([o for (_, o) in dims[:-1]] + [8]) + 7) // 8 * 8
@@ -183,6 +189,9 @@ class TrainStep:
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)   # last-block detector of the optimizer launch
+        # the table optimizer of the overlapped schedule runs beside the dense one: own step counter, own ticket
+        self.step_ctr2 = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ticket2 = torch.zeros(1, dtype=torch.int32, device=dev)
         # [0] = rows of the current batch whose label != ignore_index (K-pre counts, K-loss divides by it)
         self.label_stats = torch.zeros(4, dtype=torch.int32, device=dev)
         # bits the kernels set when they meet an id / label torch would have raised on (checked in synchronize())
@@ -207,10 +216,15 @@ class TrainStep:
             raise ValueError(f"peer_optimizer: {len(self.buckets)} buckets need more flag slots than the library has")
         self._ev_ready = [torch.cuda.Event() for _ in self.buckets]
         self._ev_done = [torch.cuda.Event() for _ in self.buckets]
-        self.graph = None
+        self.graphs = [None, None]     # one captured step per x0 buffer (the prefetch schedule alternates them)
         self.kernels_per_step = 0
         self.host_steps = 0
-        self.prefetch = bool(cfg.prefetch_pre) and len(self._chunks(B)) == 1 and self.steps_per_epoch_full > 0
+        want_prefetch = (cfg.world == 1 and self.peer is None) if cfg.prefetch_pre is None else bool(cfg.prefetch_pre)
+        self.prefetch = want_prefetch and len(self._chunks(B)) == 1 and self.steps_per_epoch_full > 0
+        # world == 1: the prefetch runs on a side stream UNDER the wgrad GEMMs (see _enqueue)
+        self.overlap_pre = self.prefetch and cfg.world == 1 and self.peer is None
+        self.pre_stream = torch.cuda.Stream(device=dev)
+        self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
         self._pre_ready = False   # x0 / y / idx already hold the batch at the current cursor (prefetch mode)
 
         torch.cuda.synchronize(dev)  # allocations/fills above ran on torch's default stream
@@ -237,6 +251,11 @@ class TrainStep:
         seg = self.layout.bias(li)
         return (self.g if grad else self.p)[seg.offset: seg.offset + seg.cols]
 
+    @property
+    def x0(self) -> torch.Tensor:
+        """The preprocessed batch the step computes on."""
+        return self.x0s[self.cur]
+
     def _chunks(self, batch: int) -> List[tuple]:
         """Row chunks a step is processed in (`StepConfig.micro_rows`; 0 = the whole batch at once, the default).
         Chunking keeps a chunk's activations L2-resident between producer and consumer kernels, but every extra
@@ -252,16 +271,20 @@ class TrainStep:
         return out
 
     def _pre(self, batch: int, ds: TabularDataset, row_idx: torch.Tensor, cursor: Optional[torch.Tensor],
-             r0: int = 0, rows: Optional[int] = None) -> int:
-        """K-pre for rows [r0, r0 + rows) of the batch the cursor points at: x0, y, idx."""
+             r0: int = 0, rows: Optional[int] = None, *, into_next: bool = False, stream=None,
+             max_ctas: int = 0) -> int:
+        """K-pre for rows [r0, r0 + rows) of the batch the cursor points at: x0, y, idx.  `into_next`: fill the OTHER
+        x0 buffer (the prefetched next batch)."""
         spec = self.spec
         rows = batch if rows is None else rows
         sl = slice(r0, r0 + rows)
+        x0 = self.x0s[self.cur ^ 1] if into_next else self.x0s[self.cur]
         ops.preprocess(ds.dense, ds.cat, ds.label, row_idx[r0:], cursor, ds.mean, ds.std,
-                       self.tables if spec.num_cat else None, self.x0[sl], self.y[sl], self.idx[sl], batch=rows,
+                       self.tables if spec.num_cat else None, x0[sl], self.y[sl], self.idx[sl], batch=rows,
                        num_dense=spec.num_dense, num_cat=spec.num_cat, table_rows=spec.cardinality,
                        embed_dim=spec.embed_dim, cursor_stride=batch,
-                       label_stats=self.label_stats if rows == batch else None, stream=self.main)
+                       label_stats=self.label_stats if rows == batch else None, max_ctas=max_ctas,
+                       stream=stream or self.main)
         return 1
 
     def _forward(self, batch: int, src: Optional[TabularDataset], row_idx: torch.Tensor,
@@ -385,6 +408,22 @@ class TrainStep:
                     for bi in bucket_of.get(-1, []):
                         n += self._reduce_bucket(bi)
                         comm_live = True
+            overlap = prefetch and self.overlap_pre
+            if overlap:
+                # Fork: the table gradients are final, the wgrad GEMMs below neither read nor write the tables.  The
+                # side stream updates the tables (its own step counter / ticket: it runs beside the dense optimizer),
+                # moves the batch cursor and gathers the NEXT batch into the other x0 buffer, all under the wgrads.
+                ps, spe_ = self.pre_stream, max(self.steps_per_epoch_full, 1)
+                self._ev_fork.record(st)
+                ps.wait_event(self._ev_fork)
+                if lay.tables_numel:
+                    self._opt_range(lay.tables_offset, lay.total, (cursor, self.step_ctr2, spe_, self.ticket2),
+                                    self.step_ctr2, ps)
+                else:
+                    ops.advance_step(cursor, self.step_ctr2, spe_, stream=ps)
+                n += 1 + self._pre(batch, self.ds, row_idx, cursor, into_next=True, stream=ps,
+                                   max_ctas=cfg.prefetch_ctas_per_sm * self.sms)
+                self._ev_join.record(ps)
             grouped = cfg.grouped_wgrad if cfg.grouped_wgrad is not None else cfg.world == 1
             xs = [self.x0[sl] if li == 0 else self.acts[li - 1][sl] for li in range(L)]
             # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
@@ -417,8 +456,9 @@ class TrainStep:
                             comm_live = True
         # optimizer ----------------------------------------------------------------------------------------
         # world > 1: one launch per bucket, each gated only by that bucket's all-reduce, so the update of the early
-        # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer.
-        n_shadow = lay.n_shadow if self.shadow is not None else 0
+        # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer (or,
+        # with the overlapped prefetch, over the Linear layers only: the tables were updated on the side stream).
+        spe = max(self.steps_per_epoch_full, 1)
         if self.peer is not None:
             # every bucket was reduced, updated and broadcast by its own kernel on the side stream (_reduce_bucket);
             # what is left: wait for all ranks' slices, zero the local gradients, advance cursor / step
@@ -426,9 +466,13 @@ class TrainStep:
                 st.wait_event(ev)
             ops.peer_finish(self.peer, [2 * bi + 1 for bi in range(len(self.buckets))],
                             cursor=self.cursor if advance else None, step=self.step_ctr,
-                            steps_per_epoch=max(self.steps_per_epoch_full, 1), stream=st)
+                            steps_per_epoch=spe, stream=st)
             if prefetch:
-                n += self._pre(batch, src or self.ds, row_idx, cursor)
+                n += self._pre(batch, src or self.ds, row_idx, cursor, into_next=True)
+            return n + 1
+        if prefetch and self.overlap_pre:
+            self._opt_range(0, lay.tables_offset, (None, self.step_ctr, spe, self.ticket), self.step_ctr, st)
+            st.wait_event(self._ev_join)   # join: tables updated, cursor moved, next batch gathered
             return n + 1
         if cfg.world > 1 and cfg.overlap_comm:
             ranges = [(self._ev_done[bi], s_, e_) for bi, (s_, e_, _) in enumerate(self.buckets)]
@@ -441,7 +485,6 @@ class TrainStep:
         # With `prefetch` the batch cursor moves in the FIRST launch (the range that holds the embedding tables, whose
         # all-reduce was issued first), K-pre of the next batch follows it and runs under the all-reduces that are
         # still in flight; the step counter (dropout stream, Adam's t) still moves in the last launch.
-        spe = max(self.steps_per_epoch_full, 1)
         cur = self.cursor if advance else None
         for ri, (ev, s_, e_) in enumerate(ranges):
             first_range, last_range = ri == 0, ri == len(ranges) - 1
@@ -450,26 +493,38 @@ class TrainStep:
             adv = (adv_cursor, adv_step, spe, self.ticket) if (adv_cursor is not None or adv_step is not None) else None
             if ev is not None:
                 st.wait_event(ev)
-            ns = max(0, min(n_shadow, e_) - s_)
-            sh = self.shadow[s_:] if (self.shadow is not None and ns > 0) else None
-            if cfg.optimizer == "sgd":
-                ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
-                             momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True,
-                             advance=adv, stream=st)
-            else:
-                ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, self.step_ctr,
-                              n_shadow=ns, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                              weight_decay=cfg.weight_decay, zero_grad=True, advance=adv, stream=st)
+            self._opt_range(s_, e_, adv, self.step_ctr, st)
             n += 1
             if prefetch and first_range:
                 # K-pre is a persistent grid too: leave SMs to the all-reduces it is meant to run under
                 pre_reserve = cfg.prefetch_sm_reserve if not last_range else 0
                 if pre_reserve:
                     ops.set_sm_budget(self.sms - pre_reserve)
-                n += self._pre(batch, src or self.ds, row_idx, cursor)
+                n += self._pre(batch, src or self.ds, row_idx, cursor, into_next=True)
                 if pre_reserve:
                     ops.set_sm_budget(0)
+        if self.overlap_pre:
+            # a step outside the overlapped schedule (tail batch, host-fed batch, profiling): the table optimizer's own
+            # step counter has to keep pace
+            ops.advance_step(None, self.step_ctr2, spe, stream=st)
+            n += 1
         return n
+
+    def _opt_range(self, s_: int, e_: int, adv, step_ptr: torch.Tensor, stream) -> None:
+        """K-opt over [s_, e_) of the flat buffers (task.py:312; the consumed gradients are left zeroed = the next
+        step's optimizer.zero_grad(), task.py:308)."""
+        cfg, lay = self.cfg, self.layout
+        n_shadow = lay.n_shadow if self.shadow is not None else 0
+        ns = max(0, min(n_shadow, e_) - s_)
+        sh = self.shadow[s_:] if (self.shadow is not None and ns > 0) else None
+        if cfg.optimizer == "sgd":
+            ops.sgd_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], sh, n_shadow=ns, lr=cfg.lr,
+                         momentum=cfg.momentum, weight_decay=cfg.weight_decay, zero_grad=True, advance=adv,
+                         stream=stream)
+        else:
+            ops.adam_step(self.p[s_:e_], self.g[s_:e_], self.s1[s_:e_], self.s2[s_:e_], sh, step_ptr, n_shadow=ns,
+                          lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps, weight_decay=cfg.weight_decay,
+                          zero_grad=True, advance=adv, stream=stream)
 
     def _reduce_bucket(self, bi: int) -> int:
         """DDP's bucket all-reduce (task.py:189 hooks): SUM over ranks; 1/world is already in grad_scale."""
@@ -508,14 +563,15 @@ class TrainStep:
 
     # ---------------------------------------------------------------------------------------- public API
     def capture(self) -> None:
-        """Capture the steady-state (full-batch) step into a CUDA graph.  One eager step must have run before
-        (it configures the kernels and warms NCCL), which `step()` guarantees."""
-        if self.graph is not None:
+        """Capture the steady-state (full-batch) step into a CUDA graph, one per x0 buffer.  One eager step must have
+        run before (it configures the kernels and warms NCCL), which `step()` guarantees."""
+        if self.graphs[self.cur] is not None:
             return
         import ctypes as C
 
         self.main.synchronize()
         self.comm_stream.synchronize()
+        self.pre_stream.synchronize()
         self.lib.graph_begin(self.main.cuda_stream)
         try:
             self.kernels_per_step = self._enqueue(self.cfg.batch_size, None, self.row_idx, self.cursor, True,
@@ -523,7 +579,7 @@ class TrainStep:
         finally:
             out = C.c_void_p()
             self.lib.graph_end(self.main.cuda_stream, C.byref(out))
-        self.graph = out
+        self.graphs[self.cur] = out
 
     def step(self) -> None:
         """One optimizer step on the next full batch of this rank (asynchronous; see `loss_value`)."""
@@ -534,11 +590,13 @@ class TrainStep:
             # first step, or x0 / y / idx were overwritten by a tail batch, an evaluation or a host-fed step
             self._pre(bs, self.ds, self.row_idx, self.cursor)
         if self.cfg.use_graph and self.host_steps > 0:
-            if self.graph is None:
+            if self.graphs[self.cur] is None:
                 self.capture()
-            self.lib.graph_launch(self.graph, self.main.cuda_stream)
+            self.lib.graph_launch(self.graphs[self.cur], self.main.cuda_stream)
         else:
             self.kernels_per_step = self._enqueue(bs, None, self.row_idx, self.cursor, True, prefetch=self.prefetch)
+        if self.prefetch:
+            self.cur ^= 1          # the batch gathered during this step sits in the other buffer
         self._pre_ready = self.prefetch
         self.host_steps += 1
 
@@ -663,6 +721,7 @@ class TrainStep:
     def synchronize(self) -> None:
         self.main.synchronize()
         self.comm_stream.synchronize()
+        self.pre_stream.synchronize()
         bits = int(self.status.item())
         if bits:
             self.status.zero_()
@@ -690,9 +749,10 @@ class TrainStep:
         self.synchronize()
         if self.peer is not None:
             self.peer.close()
-        if self.graph is not None:
-            self.lib.graph_destroy(self.graph)
-            self.graph = None
+        for i, g in enumerate(self.graphs):
+            if g is not None:
+                self.lib.graph_destroy(g)
+                self.graphs[i] = None
         for g in getattr(self, "_host_graphs", []):
             if g is not None:
                 self.lib.graph_destroy(g)

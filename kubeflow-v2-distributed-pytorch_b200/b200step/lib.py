@@ -31,7 +31,7 @@ SIGNATURES = {
     "b200_set_sm_budget": (_i, [_i]),
     "b200_set_status_word": (_i, [_p]),
     "b200_preprocess": (_i, [_p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _i, _i, _i64, _i, _i64, _i, _i64, _p,
-                             _i64, _p]),
+                             _i64, _i, _p]),
     "b200_linear_fwd": (_i, [_p, _i64, _p, _i64, _p, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _u64, _p, _i, _i64, _p, _i64,
                              _p]),
     "b200_linear_dgrad": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i64, _i64, _i64, _i, _i, _f, _p, _i64, _p,

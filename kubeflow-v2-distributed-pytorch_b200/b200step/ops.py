@@ -43,13 +43,13 @@ def _cuda(*ts):
 
 def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x_out, y_out, idx_out, *,
                batch: int, num_dense: int, num_cat: int, table_rows: int, embed_dim: int, cursor_stride: int = 0,
-               label_stats=None, ignore_index: int = -100, stream=None):
+               label_stats=None, ignore_index: int = -100, max_ctas: int = 0, stream=None):
     _cuda(ds_dense, ds_cat, ds_label, row_idx, mean, std, x_out, y_out, idx_out, label_stats)
     get_lib().preprocess(ptr(ds_dense), ptr(ds_cat), ds_cat.element_size() if ds_cat is not None else 8,
                          ptr(ds_label), ptr(row_idx), ptr(cursor), ptr(mean),
                          ptr(std), ptr(tables), ptr(x_out), ptr(y_out), ptr(idx_out), batch, num_dense,
                          num_cat, table_rows, embed_dim, x_out.stride(0), dtype_code(x_out.dtype),
-                         cursor_stride, ptr(label_stats), int(ignore_index), _stream(stream))
+                         cursor_stride, ptr(label_stats), int(ignore_index), int(max_ctas), _stream(stream))
 
 
 def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,

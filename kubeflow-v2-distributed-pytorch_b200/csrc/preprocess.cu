@@ -180,7 +180,7 @@ extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int ca
                                const float* stdv, const float* tables, void* x_out, int64_t* y_out,
                                int32_t* idx_out, int64_t batch, int num_dense, int num_cat,
                                int64_t table_rows, int embed_dim, int64_t ldx, int x_dtype,
-                               int64_t cursor_stride, int32_t* label_stats, int64_t ignore_index,
+                               int64_t cursor_stride, int32_t* label_stats, int64_t ignore_index, int max_ctas,
                                b200_stream_t stream) {
   if (cursor_stride <= 0) cursor_stride = batch;
   uint32_t* status = status_word();
@@ -206,7 +206,8 @@ extern "C" int b200_preprocess(const float* ds_dense, const void* ds_cat, int ca
   const bool fat = sm_count() < sm_count_physical();
   const int warps = (fat ? PRE_FAT_THREADS : PRE_THREADS) / 32;
   long long blocks = (batch + warps - 1) / warps;
-  const long long cap = fat ? (long long)sm_count() : (long long)sm_count() * 8;
+  long long cap = fat ? (long long)sm_count() : (long long)sm_count() * 8;
+  if (!fat && max_ctas > 0 && max_ctas < cap) cap = max_ctas;   // a launch meant to share the SMs with another grid
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   B200_REQUIRE(cat_id_bytes == 8 || cat_id_bytes == 4, "categorical ids must be int64 or int32 (cat_id_bytes=%d)",

@@ -43,7 +43,7 @@ def test_two_full_size_steps_against_the_oracle(dataset):
 
 def test_full_size_properties(dataset):
     eng = TrainStep(SPEC, init_parameters(SPEC, 0), dataset, rank_indices(2 * B, 1, 0),
-                    StepConfig(batch_size=B, precision="bf16", use_graph=False))
+                    StepConfig(batch_size=B, precision="bf16", use_graph=False, prefetch_pre=False))
     eng.step()
     eng.synchronize()
     # (1) preprocessing at full size: bit-exact against the torch restatement of the rule (sub then div)

@@ -28,15 +28,21 @@ def test_cuda_path_reproduces_golden_vectors(name):
     eng = TrainStep(spec, init_parameters(spec, 0), ds, idx,
                     StepConfig(batch_size=case["batch"], precision=case["precision"], optimizer=case["optimizer"],
                                lr=case["lr"]))
+    # preprocessing: bit-exact.  Checked on a second engine without the prefetch (the default schedule leaves the
+    # NEXT batch in x0 after a step)
+    probe = TrainStep(spec, init_parameters(spec, 0), ds, idx,
+                      StepConfig(batch_size=case["batch"], precision=case["precision"], prefetch_pre=False))
+    probe.step()
+    probe.synchronize()
+    got = torch.empty(case["batch"], spec.in_features, dtype=probe.dt)
+    got[:, probe.layout.input_perm()] = probe.x0[:, : spec.in_features].cpu()
+    view = torch.int16 if probe.dt == torch.bfloat16 else torch.int32
+    assert torch.equal(got.view(view), blob["x0_bits"])
+    probe.close()
     losses = []
     for s in range(case["steps"]):
         eng.step()
         losses.append(eng.loss_value())
-        if s == 0:                                                             # preprocessing: bit-exact
-            got = torch.empty(case["batch"], spec.in_features, dtype=eng.dt)
-            got[:, eng.layout.input_perm()] = eng.x0[:, : spec.in_features].cpu()
-            view = torch.int16 if eng.dt == torch.bfloat16 else torch.int32
-            assert torch.equal(got.view(view), blob["x0_bits"])
     # per-step loss: rel 2e-3 (TF32 vs the fp32 fixture; bf16 vs the bf16-storage fixture)
     ref = blob["losses"]
     for a, b in zip(ref.tolist(), losses):

@@ -30,7 +30,7 @@ SMALL = dataclasses.replace(ARCHS["tabular_mlp"], cardinality=50, hidden=(64, 32
 
 
 def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, lr=0.1, use_graph=True,
-              micro_rows=0, fused_ce=True):
+              micro_rows=0, fused_ce=True, prefetch_pre=None):
     """fused_ce=True: output layer + loss in one kernel (logits never stored; the default schedule) and, opt-in,
     layer-0 dgrad + embedding scatter in one kernel (input gradient never stored); False: the unfused kernels with
     stored (bf16-rounded) logits and input gradient, which the oracle mirrors with logits_rounded / dx0_rounded."""
@@ -38,7 +38,8 @@ def _run_pair(spec, *, rows, batch, steps, precision, optimizer="sgd", seed=0, l
     oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, seed=seed, optimizer=optimizer,
                            precision=precision, lr=lr, logits_rounded=not fused_ce, dx0_rounded=not fused_ce)
     cfg = StepConfig(batch_size=batch, precision=precision, optimizer=optimizer, lr=lr, use_graph=use_graph,
-                     keep_logits=not fused_ce, fused_ce=fused_ce, fused_emb_bwd=fused_ce, micro_rows=micro_rows)
+                     keep_logits=not fused_ce, fused_ce=fused_ce, fused_emb_bwd=fused_ce, micro_rows=micro_rows,
+                     prefetch_pre=prefetch_pre)
     eng = TrainStep(spec, init_parameters(spec, seed), ds, rank_indices(rows, 1, 0), cfg)
     o_losses, g_losses = [], []
     for _ in range(steps):
@@ -69,7 +70,8 @@ def _param_err(oracle, eng):
 def test_preprocess_bit_exact_vs_oracle(precision):
     spec = SMALL
     rows, batch = 1024, 256
-    ds, oracle, eng, _, _ = _run_pair(spec, rows=rows, batch=batch, steps=1, precision=precision)
+    # (prefetch off: with it the step leaves the NEXT batch, gathered from the updated tables, in x0)
+    ds, oracle, eng, _, _ = _run_pair(spec, rows=rows, batch=batch, steps=1, precision=precision, prefetch_pre=False)
     # the oracle's features for batch 0 from the *initial* embedding tables
     init = init_parameters(spec, 0)
     r = rank_indices(rows, 1, 0)[:batch]
@@ -221,7 +223,20 @@ def test_prefetched_preprocess_schedule(optimizer):
                 lg = eng.loss_value()
             assert abs(lo - lg) <= 2e-3 * max(1.0, abs(lo)), (epoch, b, lo, lg)
     assert int(eng.cursor.item()) == 0 and int(eng.step_ctr.item()) == 18
+    assert int(eng.step_ctr2.item()) == 18          # the side-stream table optimizer counts the same steps
     assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
+
+
+def test_prefetch_is_the_default_on_one_gpu_and_equals_the_plain_schedule():
+    """world == 1: K-pre of the next batch + the table optimizer run on a side stream under the wgrad GEMMs.  Same
+    kernels on the same data as the plain schedule, so losses agree to summation-order noise."""
+    def run(prefetch):
+        return _run_pair(SMALL, rows=2048, batch=256, steps=12, precision="bf16", prefetch_pre=prefetch)
+    a, b = run(None), run(False)
+    assert a[2].prefetch and a[2].overlap_pre and not b[2].prefetch
+    for x, y in zip(a[4], b[4]):
+        assert abs(x - y) <= 1e-5 * max(1.0, abs(x))
+    assert a[2].kernels_per_step == b[2].kernels_per_step + 1     # the table optimizer became its own launch
 
 
 @pytest.mark.parametrize("optimizer", ["sgd", "adam"])
