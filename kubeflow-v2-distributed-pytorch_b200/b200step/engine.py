@@ -64,8 +64,8 @@ class StepConfig:
                                          # UNDER the wgrad launch (x0 is double-buffered: wgrad still reads this
                                          # batch's).  world > 1: K-pre follows the embedding tables' optimizer launch,
                                          # under the all-reduces still in flight (+0.6 % at 2 GPUs, -2 % at 8 GPUs on
-                                         # T0, profiles/r01_comm_overlap_experiments.md).  None = on when world == 1
-    prefetch_ctas_per_sm: int = 2        # CTA slots per SM the overlapped K-pre takes (the GEMM grid needs the rest)
+                                         # T0, profiles/r01_comm_overlap_experiments.md).  None / False = off
+    prefetch_ctas_per_sm: int = 4        # CTA slots per SM the overlapped K-pre takes (the GEMM grid needs the rest)
     fused_ce: Optional[bool] = None      # output layer + cross-entropy as one kernel (K-gemm-ce): the logits never go to
                                          # HBM.  None = whenever it applies (<= 1024 classes, logits not kept)
     fused_emb_bwd: bool = False          # layer-0 dgrad adds its output straight onto the table gradients (no dx0
@@ -219,7 +219,9 @@ class TrainStep:
         self.graphs = [None, None]     # one captured step per x0 buffer (the prefetch schedule alternates them)
         self.kernels_per_step = 0
         self.host_steps = 0
-        want_prefetch = (cfg.world == 1 and self.peer is None) if cfg.prefetch_pre is None else bool(cfg.prefetch_pre)
+        # opt-in: measured on T0 (profiles/r02_prefetch_overlap.md) the overlapped K-pre gains 0-2 %: its CTAs and the
+        # persistent wgrad grid compete for registers, so little of it actually runs under the GEMMs
+        want_prefetch = bool(cfg.prefetch_pre)
         self.prefetch = want_prefetch and len(self._chunks(B)) == 1 and self.steps_per_epoch_full > 0
         # world == 1: the prefetch runs on a side stream UNDER the wgrad GEMMs (see _enqueue)
         self.overlap_pre = self.prefetch and cfg.world == 1 and self.peer is None

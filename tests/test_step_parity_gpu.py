@@ -227,12 +227,12 @@ def test_prefetched_preprocess_schedule(optimizer):
     assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
 
 
-def test_prefetch_is_the_default_on_one_gpu_and_equals_the_plain_schedule():
+def test_overlapped_prefetch_equals_the_plain_schedule():
     """world == 1: K-pre of the next batch + the table optimizer run on a side stream under the wgrad GEMMs.  Same
     kernels on the same data as the plain schedule, so losses agree to summation-order noise."""
     def run(prefetch):
         return _run_pair(SMALL, rows=2048, batch=256, steps=12, precision="bf16", prefetch_pre=prefetch)
-    a, b = run(None), run(False)
+    a, b = run(True), run(None)
     assert a[2].prefetch and a[2].overlap_pre and not b[2].prefetch
     for x, y in zip(a[4], b[4]):
         assert abs(x - y) <= 1e-5 * max(1.0, abs(x))
