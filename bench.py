@@ -307,6 +307,8 @@ def run_b200(args, rank, local_rank, world):
         cfg.peer_optimizer = True
     if os.environ.get("B200STEP_PREFETCH_RESERVE"):
         cfg.prefetch_sm_reserve = int(os.environ["B200STEP_PREFETCH_RESERVE"])
+    if os.environ.get("B200STEP_GROUPED_WGRAD"):          # A/B at world > 1: one wgrad launch, buckets reduced after it
+        cfg.grouped_wgrad = os.environ["B200STEP_GROUPED_WGRAD"] != "0"
     if os.environ.get("B200STEP_PREFETCH_CTAS"):          # A/B: CTA slots per SM of the overlapped K-pre
         cfg.prefetch_ctas_per_sm = int(os.environ["B200STEP_PREFETCH_CTAS"])
     if os.environ.get("B200STEP_PREFETCH_PRE"):           # A/B: K-pre of the next batch under wgrad / the all-reduces
