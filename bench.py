@@ -114,7 +114,7 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------- CPU arms
-def _cpu_oracle_throughput(spec, ds_rows, batch, world, steps, warmup, threads=None):
+def _cpu_oracle_throughput(spec, ds_rows, batch, world, steps, warmup, threads=None, time_budget_s=None):
     """Times the oracle port (oracle/reference_step.py: the reference's step with .cuda() removed, true fp32)
     on the host cores.  `batch` rows per step (a bounded sample of the GPU arm's per-step work)."""
     import torch
@@ -135,8 +135,11 @@ def _cpu_oracle_throughput(spec, ds_rows, batch, world, steps, warmup, threads=N
         t0 = time.perf_counter()
         tr.step()
         times.append(time.perf_counter() - t0)
+        if time_budget_s is not None and sum(times) > time_budget_s:   # bounded: the arm must end within minutes
+            break
+    steps = len(times)
     return {"samples_per_s": batch * steps / sum(times), "ms_per_step": 1e3 * sum(times) / steps,
-            "cores": torch.get_num_threads(), "min_ms": 1e3 * min(times)}
+            "cores": torch.get_num_threads(), "min_ms": 1e3 * min(times), "steps": steps}
 
 
 def run_reference(args, rank):
@@ -150,19 +153,24 @@ def run_reference(args, rank):
 
     wl = WORKLOADS[args.workload]
     spec = ARCHS[wl["arch"]]
-    steps = max(1, min(args.steps, 8))
-    warm = max(1, min(args.warmup, 2))
+    # --steps / --warmup are honoured up to a time budget (a 65536-row CPU step takes ~0.3 s on 32 threads)
+    steps = max(1, args.steps)
+    warm = max(1, min(args.warmup, 3))
     if wl.get("cpu_gloo"):
         _run_reference_gloo(args, wl, spec, steps, warm)
         return
     sample = min(wl["batch"] * args.gpus, REF_SAMPLE_CAP)
-    r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, steps, warm, threads=os.cpu_count())
+    r = _cpu_oracle_throughput(spec, sample * 2, sample, 1, steps, warm, threads=os.cpu_count(), time_budget_s=60.0)
+    steps = r["steps"]
     out = {
         "impl": "reference", "metric": "train samples/sec", "value": r["samples_per_s"], "unit": "samples/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "arch": wl["arch"], "per_gpu_batch": wl["batch"],
-                   "optimizer": wl["optimizer"]},
+                   "optimizer": wl["optimizer"],
+                   "arm": "ONE process, all host threads, oracle port, at every --gpus value (task.py has no CPU path; "
+                          "BASELINE config 1, DDP over gloo with 2 CPU processes, is --workload "
+                          "t0_fp32_b4096_cpu_gloo2)"},
         "cpu_baseline": {"value": r["samples_per_s"], "unit": "samples/s", "cores": r["cores"], "kind": "port",
                          "sample": f"{steps} steps of {sample} rows (global batch capped at {REF_SAMPLE_CAP}), "
                                    f"fp32 torch CPU, host threads={r['cores']} of {os.cpu_count()} logical cpus"},
@@ -348,6 +356,30 @@ def run_b200(args, rank, local_rank, world):
         ms = float(t.item())
     value = world * B * args.steps / (ms / 1e3)
 
+    # ---- sustained leg: the same graph-replayed step for >= --sustain-seconds, with its own clock record ---------
+    # (`value` above is a burst of --steps steps, a few ms at boost clocks; a training run settles under the power cap)
+    sustained = None
+    if args.sustain_seconds > 0:
+        n_sus = max(args.steps, int(args.sustain_seconds * 1e3 / (ms / args.steps)) + 1)
+        sampler2 = ClockSampler(local_rank)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        sampler2.start()
+        s0.record(eng.main)
+        for _ in range(n_sus):
+            eng.step()
+        s1.record(eng.main)
+        eng.synchronize()
+        barrier()
+        clocks2 = sampler2.stop()
+        sus_ms = s0.elapsed_time(s1)
+        if dist is not None:
+            t = torch.tensor([sus_ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            sus_ms = float(t.item())
+        sustained = {"seconds": sus_ms / 1e3, "steps": n_sus, "ms_per_step": sus_ms / n_sus,
+                     "value": world * B * n_sus / (sus_ms / 1e3), "unit": "samples/s", "clocks": clocks2}
+
     # ---- end-to-end measurement: host batches, H2D inside the timed region, loss read back every step --------
     nb = min(BATCHES_PER_RANK, 4)
     host = [eng.pack_host_batch(host_local.dense[i * B:(i + 1) * B], host_local.cat[i * B:(i + 1) * B],
@@ -389,9 +421,15 @@ def run_b200(args, rank, local_rank, world):
     # wgrad twin) and together the largest share of the step: achieved = their algorithmic FLOPs / their summed
     # device time (CUDA events around each launch, measured in this run).  The largest memory-bound launch is
     # reported next to it as `roofline_hbm`.
+    # `ms` of a kernel = CUDA events around its launch in EAGER steps; their sum exceeds the graph-replayed step
+    # (`ms_per_step`) because in the graph each kernel's prologue overlaps its predecessor's tail (programmatic
+    # dependent launch) and no event records sit between launches.  `share` = ms / sum of the kernels' ms;
+    # `share_of_step_ms` = ms / ms_per_step (these add up to kernel_ms_sum / ms_per_step > 1).
     total_ms = sum(r["ms"] * r["per_step"] for r in prof)
+    step_ms = ms / args.steps
     for r in prof:
         r["share"] = r["ms"] * r["per_step"] / total_ms
+        r["share_of_step_ms"] = r["ms"] * r["per_step"] / step_ms
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")  # dram bytes per launch from `ncu --set full` captures
     traffic_tab = {}
     if os.path.exists(tpath):
@@ -406,7 +444,9 @@ def run_b200(args, rank, local_rank, world):
     roof_tensor = {"bound": "tensor", "kernel": "gemm_kernel (fwd + dgrad + wgrad launches of the step)",
                    "achieved": gem_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": gem_tflops / tensor_peak,
                    "traffic": (sum(gem_traffic) / len(gem_traffic)) if gem_traffic and all(v is not None for v in gem_traffic) else None,
-                   "share_of_step": gem_ms / total_ms, "launches_per_step": sum(r["per_step"] for r in gem),
+                   "share_of_step": gem_ms / total_ms, "share_of_step_ms": gem_ms / step_ms,
+                   "kernel_ms": gem_ms, "flops_basis": "2*M*N*K on unpadded dims (SURVEY.md 8d)",
+                   "launches_per_step": sum(r["per_step"] for r in gem),
                    "peak_source": peaks["source"] + (" bf16 burst" if wl["precision"] == "bf16"
                                                      else " bf16 burst / 2 (tf32 runs at half the bf16 rate)")}
     topm = max(mem, key=lambda r: r["ms"])
@@ -427,9 +467,12 @@ def run_b200(args, rank, local_rank, world):
                    "cuda_graph": True, "prefetch_pre": eng.prefetch, "peer_optimizer": eng.peer is not None,
                    "categorical_ids": "uniform" if args.zipf_alpha is None else f"zipf(alpha={args.zipf_alpha})"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": eng.kernels_per_step * args.steps,
-        "roofline": roof, "roofline_hbm": roof_hbm, "kernels": prof, "step_tflops_per_gpu": step_tflops,
+        "roofline": roof, "roofline_hbm": roof_hbm, "kernels": prof, "kernel_ms_sum": total_ms,
+        "step_tflops_per_gpu": step_tflops,
         "final_loss": loss_after,
     }
+    if sustained is not None:
+        out["sustained"] = sustained
     if parity is not None:
         out["parity"] = parity
     if world == 1 and not args.no_cpu_baseline:
@@ -467,9 +510,12 @@ def profile_kernels(eng, spec, B, world):
             r = fn(*a, **k)
             a1.record(st)
             label, work = name, {}
+            # FLOPs follow SURVEY.md §8(d): 2*M*N*K on UNPADDED dims (the first layer's K is stored padded to a
+            # whole number of 128-byte rows), and the layer-0 dgrad only for the embedding columns
+            unpad = lambda kk: spec.in_features if (kk == eng.k0 and eng.k0 != spec.in_features) else kk
             if name == "linear_wgrad_grouped":
                 label = f"linear_wgrad_grouped[{k['M']}x{len(k['Ns'])} layers]"
-                work = {"flops": sum(2.0 * k["M"] * n_ * k_ for n_, k_ in zip(k["Ns"], k["Ks"]))}
+                work = {"flops": sum(2.0 * k["M"] * n_ * unpad(k_) for n_, k_ in zip(k["Ns"], k["Ks"]))}
             elif name == "linear_dgrad_emb":
                 kk = k["num_cat"] * k["embed_dim"]
                 label = f"linear_dgrad_emb[{k['M']}x{k['N']}x{kk}]"
@@ -477,10 +523,16 @@ def profile_kernels(eng, spec, B, world):
             elif name.startswith("linear_"):
                 M, N, K = k["M"], k["N"], k["K"]
                 label = f"{name}[{M}x{N}x{K}]" + ("+dbias" if k.get("dbias") is not None else "")
-                work = {"flops": 2.0 * M * N * K}    # linear_ce: the output layer's GEMM; the loss rides along
+                keff = unpad(K)
+                if name == "linear_dgrad" and K == eng.k0 and spec.num_cat:
+                    keff = spec.num_cat * spec.embed_dim          # input gradient of the embedding columns only
+                work = {"flops": 2.0 * M * N * keff}  # linear_ce: the output layer's GEMM; the loss rides along
             elif name == "preprocess":
                 raw = 4 * spec.num_dense + 8 * spec.num_cat + 8 + 8
-                work = {"bytes": B * (raw + 4 * spec.num_cat * spec.embed_dim + es * eng.k0 + 8 + 4 * spec.num_cat)}
+                # `bytes` = SURVEY.md §8(d)'s per-sample figure (it counts the gathered table rows, which on T0 come
+                # from the L2-resident 1.7 MB tables); `dram_bytes` = what has to cross HBM: raw row in, x0/y/idx out
+                work = {"bytes": B * (raw + 4 * spec.num_cat * spec.embed_dim + es * eng.k0 + 8 + 4 * spec.num_cat),
+                        "dram_bytes": B * (raw + es * eng.k0 + 8 + 4 * spec.num_cat)}
             elif name == "ce_loss_grad":
                 work = {"bytes": B * (2 * es * spec.num_classes + 8)}
             elif name == "colsum":
@@ -522,6 +574,8 @@ def profile_kernels(eng, spec, B, world):
             rec.update(bound="tensor", tflops=d["work"]["flops"] / (per / 1e3) / 1e12)
         else:
             rec.update(bound="hbm", gbs=d["work"]["bytes"] / (per / 1e3) / 1e9)
+            if "dram_bytes" in d["work"]:
+                rec["dram_gbs"] = d["work"]["dram_bytes"] / (per / 1e3) / 1e9
         out.append(rec)
     return out
 
@@ -534,6 +588,9 @@ def main():
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="t0_bf16_b65536")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--sustain-seconds", dest="sustain_seconds", type=float, default=2.0,
+                    help="after the timed --steps burst, run the same step back to back for this long and report it as "
+                         "`sustained` with its own clock / throttle record (0 = skip)")
     ap.add_argument("--no-parity", dest="no_parity", action="store_true",
                     help="skip the parity leg (4 small steps against the CPU oracle, outside the timed region)")
     ap.add_argument("--zipf-alpha", dest="zipf_alpha", type=float, default=None,
