@@ -311,8 +311,6 @@ def run_b200(args, rank, local_rank, world):
         cfg.first_bucket_bytes = min(cfg.first_bucket_bytes, cfg.bucket_cap_bytes)
     if os.environ.get("B200STEP_SM_RESERVE"):             # experiments: SMs the wgrads leave to the all-reduce
         cfg.comm_sm_reserve = int(os.environ["B200STEP_SM_RESERVE"])
-    if os.environ.get("B200STEP_PEER_OPT") == "1":        # A/B: K-opt-peer instead of NCCL all-reduce + optimizer
-        cfg.peer_optimizer = True
     if os.environ.get("B200STEP_PREFETCH_RESERVE"):
         cfg.prefetch_sm_reserve = int(os.environ["B200STEP_PREFETCH_RESERVE"])
     if os.environ.get("B200STEP_GROUPED_WGRAD"):          # A/B at world > 1: one wgrad launch, buckets reduced after it
@@ -464,7 +462,7 @@ def run_b200(args, rank, local_rank, world):
                    "optimizer": wl["optimizer"], "params": spec.num_params, "parallelism": f"dp{world}",
                    "l2": "per-step working set > 126 MB L2 (no flush needed)" if B >= 32768 else
                          "working set fits L2: dataset cycles 8 batches",
-                   "cuda_graph": True, "prefetch_pre": eng.prefetch, "peer_optimizer": eng.peer is not None,
+                   "cuda_graph": True, "prefetch_pre": eng.prefetch,
                    "categorical_ids": "uniform" if args.zipf_alpha is None else f"zipf(alpha={args.zipf_alpha})"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": eng.kernels_per_step * args.steps,
         "roofline": roof, "roofline_hbm": roof_hbm, "kernels": prof, "kernel_ms_sum": total_ms,

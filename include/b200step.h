@@ -236,44 +236,6 @@ int b200_comm_allreduce_sum(float* buf, int64_t count, b200_stream_t stream);
 int b200_comm_broadcast(float* buf, int64_t count, int root, b200_stream_t stream); /* DDP ctor param sync */
 int b200_comm_destroy(void);
 
-/* ---- K-opt-peer: gradient reduction + optimizer + parameter broadcast over NVLink peer memory ----
- * EXPERIMENTAL (StepConfig.peer_optimizer, off by default).  Replaces, per gradient bucket, the pair
- * b200_comm_allreduce_sum + b200_sgd_step / b200_adam_step (DistributedDataParallel's bucket all-reduce at
- * task.py:189 followed by optimizer.step() at task.py:312) by ONE kernel: rank r owns the r-th of `world` equal
- * slices of the bucket, sums that slice of every rank's gradient buffer in rank order over peer loads, applies the
- * optimizer to its slice and stores the new parameters (+ bf16 operand copy) into every rank's buffers.
- *
- * Buffers that peers touch (gradients, parameters, bf16 copy, flags) must come from b200_peer_alloc; the 64-byte
- * handle it returns is a cudaIpcMemHandle_t that the host ships to the other ranks (torch.distributed store),
- * which map it with b200_peer_open.  The pointer tables `g`, `p`, `shadow`, `flags` are HOST arrays of `world`
- * device pointers indexed by rank (entry `rank` = the local buffer).  `flags`: b200_peer_flag_words() uint32 per
- * rank, zero-initialised; slot s of rank q is written by the other ranks only.  Every bucket uses two slots
- * (gradients ready / slice done).  `step` is the device-side step counter shared with the rest of the step; flags
- * carry step+1.  `err` (device uint32, zero-initialised) receives 1+slot when a wait timed out (120 s; B200STEP_PEER_TIMEOUT_S).
- *   b200_peer_signal   after the bucket's last gradient kernel: "my gradients of this bucket are complete"
- *   b200_peer_*_step   wait for every rank's ready flag, reduce + update + broadcast this rank's slice, flag done
- *   b200_peer_finish   wait for the done flags of all listed slots from all ranks, zero the local gradient buffer
- *                      g[0, n) and advance cursor / step (the optimizer.zero_grad() + bookkeeping of the step)
- * The library allocates here (b200_peer_alloc only): peer-mapped memory cannot come from the framework's pool. */
-int b200_peer_alloc(int64_t bytes, void** ptr_out_host, void* handle_out_host_64);
-int b200_peer_open(const void* handle_host_64, void** ptr_out_host);
-int b200_peer_enable_access(int peer_device); /* kernels of the current device may dereference peer_device's memory */
-int b200_peer_close(void* ptr);  /* unmap a pointer obtained from b200_peer_open */
-int b200_peer_free(void* ptr);   /* free a pointer obtained from b200_peer_alloc */
-int b200_peer_flag_words(void);
-int b200_peer_signal(void* const* flags, int world, int rank, int slot, const int32_t* step, b200_stream_t stream);
-int b200_peer_sgd_step(void* const* g, void* const* p, void* const* shadow, void* const* flags, int world, int rank,
-                       float* momentum_buf, int64_t start, int64_t end, int64_t n_shadow, int slot_ready,
-                       int slot_done, const int32_t* step, float lr, float momentum, float weight_decay,
-                       uint32_t* ticket, uint32_t* err, b200_stream_t stream);
-int b200_peer_adam_step(void* const* g, void* const* p, void* const* shadow, void* const* flags, int world, int rank,
-                        float* exp_avg, float* exp_avg_sq, int64_t start, int64_t end, int64_t n_shadow,
-                        int slot_ready, int slot_done, const int32_t* step, double lr, double beta1, double beta2,
-                        float eps, float weight_decay, uint32_t* ticket, uint32_t* err, b200_stream_t stream);
-int b200_peer_finish(const void* flags_local, int world, const int32_t* slots_host, int n_slots, float* g, int64_t n,
-                     int32_t* cursor, int32_t* step, int steps_per_epoch, uint32_t* ticket, uint32_t* err,
-                     b200_stream_t stream);
-
 /* ---- streams / events / graphs (host plumbing for the step schedule) ------------------------ */
 int b200_stream_create(b200_stream_t* out_host, int high_priority);
 int b200_stream_destroy(b200_stream_t s);

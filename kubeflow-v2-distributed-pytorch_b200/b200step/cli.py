@@ -245,10 +245,7 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
 
     cfg = StepConfig(batch_size=batch_size, world=world, rank=rank, precision=args.precision,
                      optimizer=args.optimizer, lr=args.learning_rate, momentum=args.momentum,
-                     weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph,
-                     # K-opt-peer stays behind an environment variable until its multi-rank parity test has passed
-                     # on hardware
-                     peer_optimizer=os.environ.get("B200STEP_PEER_OPT") == "1")
+                     weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph)
     step = TrainStep(spec, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
 
     for epoch in range(num_epochs):
@@ -286,7 +283,7 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
                 step.step()
             else:
                 step.step_tail()                                    # drop_last=False: the partial last batch
-        # once per epoch, on every rank: surface device-side reports (bad ids / labels, peer-flag time-outs) instead
+        # once per epoch, on every rank: surface device-side reports (bad ids / labels) instead
         # of training on for epochs with neutralised input
         step.synchronize()
 

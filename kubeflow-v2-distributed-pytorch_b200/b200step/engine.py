@@ -54,10 +54,6 @@ class StepConfig:
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
     comm_sm_reserve: Optional[int] = None  # None = DEFAULT_COMM_SM_RESERVE when world > 1 and comm overlaps
     prefetch_sm_reserve: int = 32        # SMs the prefetched K-pre leaves to the all-reduces it runs under
-    peer_optimizer: bool = False         # EXPERIMENTAL: per bucket, ONE kernel that sums every rank's gradient slice
-                                         # over NVLink peer memory, applies the optimizer and writes the new
-                                         # parameters to every rank (csrc/peer.cu) instead of NCCL all-reduce +
-                                         # optimizer launch.  Single node, world <= 8
     prefetch_pre: Optional[bool] = None  # run K-pre of the NEXT batch inside this step (device-resident `step()`
                                          # path only).  world == 1: the table gradients are complete before the wgrad
                                          # GEMMs start, so a side stream updates the tables and gathers the next batch
@@ -142,23 +138,11 @@ class TrainStep:
             raise ValueError("empty sample list")
 
         # ---- flat parameter / gradient / optimizer-state buffers
-        self.peer = None
-        if cfg.peer_optimizer:
-            # parameters, gradients and the bf16 copy live in one allocation that every rank of the node maps
-            from .peer import PeerBuffers
-
-            if not cfg.overlap_comm:
-                raise ValueError("peer_optimizer runs its kernels on the side stream: overlap_comm must stay on")
-            self.peer = PeerBuffers(lay.total, lay.n_shadow if self.dt == torch.bfloat16 else 0, cfg.rank, cfg.world,
-                                    dev)
-            self.p, self.g, self.shadow = self.peer.p, self.peer.g, self.peer.shadow
-            self.p.copy_(lay.flatten(init_params))
-        else:
-            self.p = lay.flatten(init_params).to(dev)
-            self.g = torch.zeros_like(self.p)
-            self.shadow = None
-            if self.dt == torch.bfloat16:
-                self.shadow = torch.zeros(lay.n_shadow, dtype=torch.bfloat16, device=dev)
+        self.p = lay.flatten(init_params).to(dev)
+        self.g = torch.zeros_like(self.p)
+        self.shadow = None
+        if self.dt == torch.bfloat16:
+            self.shadow = torch.zeros(lay.n_shadow, dtype=torch.bfloat16, device=dev)
         self.s1 = torch.zeros_like(self.p)                    # SGD momentum buffer | Adam exp_avg
         self.s2 = torch.zeros_like(self.p) if cfg.optimizer == "adam" else None
         self.wsrc = self.shadow if self.shadow is not None else self.p   # GEMM weight operands
@@ -212,8 +196,6 @@ class TrainStep:
         self.main = torch.cuda.Stream(device=dev)
         self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.buckets = lay.buckets(cfg.first_bucket_bytes, cfg.bucket_cap_bytes)
-        if self.peer is not None and 2 * len(self.buckets) > self.peer.flag_words // 8:
-            raise ValueError(f"peer_optimizer: {len(self.buckets)} buckets need more flag slots than the library has")
         self._ev_ready = [torch.cuda.Event() for _ in self.buckets]
         self._ev_done = [torch.cuda.Event() for _ in self.buckets]
         self.graphs = [None, None]     # one captured step per x0 buffer (the prefetch schedule alternates them)
@@ -224,7 +206,7 @@ class TrainStep:
         want_prefetch = bool(cfg.prefetch_pre)
         self.prefetch = want_prefetch and len(self._chunks(B)) == 1 and self.steps_per_epoch_full > 0
         # world == 1: the prefetch runs on a side stream UNDER the wgrad GEMMs (see _enqueue)
-        self.overlap_pre = self.prefetch and cfg.world == 1 and self.peer is None
+        self.overlap_pre = self.prefetch and cfg.world == 1
         self.pre_stream = torch.cuda.Stream(device=dev)
         self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
         self._pre_ready = False   # x0 / y / idx already hold the batch at the current cursor (prefetch mode)
@@ -461,17 +443,6 @@ class TrainStep:
         # buckets overlaps the all-reduce of the last one; world == 1: a single pass over the whole flat buffer (or,
         # with the overlapped prefetch, over the Linear layers only: the tables were updated on the side stream).
         spe = max(self.steps_per_epoch_full, 1)
-        if self.peer is not None:
-            # every bucket was reduced, updated and broadcast by its own kernel on the side stream (_reduce_bucket);
-            # what is left: wait for all ranks' slices, zero the local gradients, advance cursor / step
-            for ev in self._ev_done:
-                st.wait_event(ev)
-            ops.peer_finish(self.peer, [2 * bi + 1 for bi in range(len(self.buckets))],
-                            cursor=self.cursor if advance else None, step=self.step_ctr,
-                            steps_per_epoch=spe, stream=st)
-            if prefetch:
-                n += self._pre(batch, src or self.ds, row_idx, cursor, into_next=True)
-            return n + 1
         if prefetch and self.overlap_pre:
             self._opt_range(0, lay.tables_offset, (None, self.step_ctr, spe, self.ticket), self.step_ctr, st)
             st.wait_event(self._ev_join)   # join: tables updated, cursor moved, next batch gathered
@@ -530,8 +501,6 @@ class TrainStep:
 
     def _reduce_bucket(self, bi: int) -> int:
         """DDP's bucket all-reduce (task.py:189 hooks): SUM over ranks; 1/world is already in grad_scale."""
-        if self.peer is not None:
-            return self._peer_bucket(bi)
         if self.cfg.world <= 1:
             return 0
         s, e, _ = self.buckets[bi]
@@ -543,25 +512,6 @@ class TrainStep:
         else:
             self.comm.allreduce_sum(self.g[s:e], self.main)
         return 1
-
-    def _peer_bucket(self, bi: int) -> int:
-        """K-opt-peer for bucket `bi` on the side stream: flag this rank's gradients ready, then reduce every rank's
-        slice over peer memory, apply the optimizer and store the new parameters to every rank (csrc/peer.cu)."""
-        cfg, s_ = self.cfg, self.comm_stream
-        lo, hi, _ = self.buckets[bi]
-        self._ev_ready[bi].record(self.main)
-        s_.wait_event(self._ev_ready[bi])
-        ops.peer_signal(self.peer, 2 * bi, self.step_ctr, stream=s_)
-        if cfg.optimizer == "sgd":
-            ops.peer_sgd_step(self.peer, self.s1, start=lo, end=hi, slot_ready=2 * bi, slot_done=2 * bi + 1,
-                              step=self.step_ctr, lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay,
-                              stream=s_)
-        else:
-            ops.peer_adam_step(self.peer, self.s1, self.s2, start=lo, end=hi, slot_ready=2 * bi, slot_done=2 * bi + 1,
-                               step=self.step_ctr, lr=cfg.lr, beta1=cfg.beta1, beta2=cfg.beta2, eps=cfg.eps,
-                               weight_decay=cfg.weight_decay, stream=s_)
-        self._ev_done[bi].record(s_)
-        return 2
 
     # ---------------------------------------------------------------------------------------- public API
     def capture(self) -> None:
@@ -735,11 +685,6 @@ class TrainStep:
                             "(nn.CrossEntropyLoss raises)")
             raise B200Error("the step met " + " and ".join(what) + "; the offending rows were neutralised on the "
                             "device (id -> row 0, label -> ignored) but the input is invalid")
-        if self.peer is not None:
-            code = self.peer.error_code()
-            if code:
-                raise B200Error(f"peer optimizer: a wait on flag slot {code - 1} timed out (a rank of the node died or "
-                                "fell further behind than B200STEP_PEER_TIMEOUT_S, default 120 s)")
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """Same keys/shapes as the reference's `model.state_dict()` under DDP (task.py:283/287)."""
@@ -749,8 +694,6 @@ class TrainStep:
 
     def close(self) -> None:
         self.synchronize()
-        if self.peer is not None:
-            self.peer.close()
         for i, g in enumerate(self.graphs):
             if g is not None:
                 self.lib.graph_destroy(g)

@@ -59,17 +59,6 @@ SIGNATURES = {
     "b200_comm_allreduce_sum": (_i, [_p, _i64, _p]),
     "b200_comm_broadcast": (_i, [_p, _i64, _i, _p]),
     "b200_comm_destroy": (_i, []),
-    "b200_peer_alloc": (_i, [_i64, C.POINTER(_p), _p]),
-    "b200_peer_open": (_i, [_p, C.POINTER(_p)]),
-    "b200_peer_enable_access": (_i, [_i]),
-    "b200_peer_close": (_i, [_p]),
-    "b200_peer_free": (_i, [_p]),
-    "b200_peer_flag_words": (_i, []),
-    "b200_peer_signal": (_i, [_p, _i, _i, _i, _p, _p]),
-    "b200_peer_sgd_step": (_i, [_p, _p, _p, _p, _i, _i, _p, _i64, _i64, _i64, _i, _i, _p, _f, _f, _f, _p, _p, _p]),
-    "b200_peer_adam_step": (_i, [_p, _p, _p, _p, _i, _i, _p, _p, _i64, _i64, _i64, _i, _i, _p, _d, _d, _d, _f, _f,
-                                 _p, _p, _p]),
-    "b200_peer_finish": (_i, [_p, _i, _p, _i, _p, _i64, _p, _p, _i, _p, _p, _p]),
     "b200_stream_create": (_i, [C.POINTER(_p), _i]),
     "b200_stream_destroy": (_i, [_p]),
     "b200_stream_sync": (_i, [_p]),
@@ -87,7 +76,7 @@ SIGNATURES = {
 # functions whose int return value is NOT an error code
 _NO_CHECK = {"b200_last_error", "b200_abi_version", "b200_ce_scratch_floats", "b200_colsum_scratch_floats",
              "b200_linear_ce_scratch_floats",
-             "b200_dgrad_scratch_floats", "b200_peer_flag_words"}
+             "b200_dgrad_scratch_floats"}
 
 
 class B200Error(RuntimeError):

@@ -208,36 +208,6 @@ def set_sm_budget(sms: int) -> None:
     get_lib().set_sm_budget(int(sms))
 
 
-# ---- K-opt-peer (EXPERIMENTAL): `pb` is a peer.PeerBuffers ------------------------------------------------------
-def peer_signal(pb, slot: int, step, stream=None):
-    get_lib().peer_signal(pb.flags_tab, pb.world, pb.rank, int(slot), ptr(step), _stream(stream))
-
-
-def peer_sgd_step(pb, buf, *, start: int, end: int, slot_ready: int, slot_done: int, step, lr: float,
-                  momentum: float, weight_decay: float, stream=None):
-    get_lib().peer_sgd_step(pb.g_tab, pb.p_tab, pb.shadow_tab, pb.flags_tab, pb.world, pb.rank, ptr(buf), int(start),
-                            int(end), int(pb.n_shadow), int(slot_ready), int(slot_done), ptr(step), float(lr),
-                            float(momentum), float(weight_decay), pb.words[0:].data_ptr(), pb.words[2:].data_ptr(),
-                            _stream(stream))
-
-
-def peer_adam_step(pb, m, v, *, start: int, end: int, slot_ready: int, slot_done: int, step, lr: float, beta1: float,
-                   beta2: float, eps: float, weight_decay: float, stream=None):
-    get_lib().peer_adam_step(pb.g_tab, pb.p_tab, pb.shadow_tab, pb.flags_tab, pb.world, pb.rank, ptr(m), ptr(v),
-                             int(start), int(end), int(pb.n_shadow), int(slot_ready), int(slot_done), ptr(step),
-                             float(lr), float(beta1), float(beta2), float(eps), float(weight_decay),
-                             pb.words[0:].data_ptr(), pb.words[2:].data_ptr(), _stream(stream))
-
-
-def peer_finish(pb, slots, *, cursor, step, steps_per_epoch: int, stream=None):
-    import ctypes as C
-
-    arr = (C.c_int32 * len(slots))(*[int(s) for s in slots])
-    get_lib().peer_finish(pb.flags.data_ptr(), pb.world, arr, len(slots), pb.g.data_ptr(), int(pb.total), ptr(cursor),
-                          ptr(step), int(steps_per_epoch), pb.words[1:].data_ptr(), pb.words[2:].data_ptr(),
-                          _stream(stream))
-
-
 def zero(t, stream=None):
     _cuda(t)
     get_lib().zero(ptr(t), t.numel() * t.element_size(), _stream(stream))

@@ -1,12 +1,10 @@
 #!/bin/bash
-# 2-GPU verification: task.py tests (NCCL path and, opt-in, the peer-memory optimizer), then bench A/B lines.
+# 2-GPU verification: task.py tests (NCCL path), then bench A/B lines.
 cd "$(dirname "$0")/.."
-export B200STEP_TEST_PEER=1
 timeout 900 python -m pytest tests/test_task_gpu.py -m gpu -q -x > gpurun_out/w2_tests.log 2>&1; echo rc=$? >> gpurun_out/w2_tests.log
 run() { name=$1; shift; env "$@" python bench.py --gpus 2 --steps 30 --warmup 5 > gpurun_out/w2_$name.json 2> gpurun_out/w2_$name.err; echo "$name rc=$?"; }
 run default X=1
 run grouped B200STEP_GROUPED_WGRAD=1
-run peer B200STEP_PEER_OPT=1
 python - <<'PY'
 import json,glob
 for f in sorted(glob.glob('gpurun_out/w2_*.json')):

@@ -49,7 +49,6 @@ def test_additive_flags_default_to_reference_behaviour():
     assert a.arch == "resnet18" and a.optimizer == "sgd" and a.dropout == 0.0 and a.synthetic_rows == 10000
     assert a.learning_rate == 0.1 and a.momentum == 0.9 and a.weight_decay == 1e-4 and a.batch_size == 1024
     assert a.precision == "fp32"            # the reference's nn.Linear arithmetic (task.py:309); bf16 / tf32 are opt-in
-    assert not hasattr(a, "peer_optimizer")  # experimental paths carry no CLI flag
     a = parser.parse_args(["--dist-url=env://", "--multiprocessing-distributed", "--num_epochs=2"])  # notebook ARGS
     assert a.dist_url == "env://" and a.multiprocessing_distributed and a.num_epochs == 2
     a = parser.parse_args(["--arch", "tabular_mlp_wide", "--weight-decay", "0.01", "-a", "tabular_mlp"])

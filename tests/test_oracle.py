@@ -167,27 +167,6 @@ def test_bucket_plan_covers_flat_buffer_and_respects_cap():
         assert readies.count(-1) == 1
 
 
-def test_peer_slices_partition_every_bucket():
-    """K-opt-peer (csrc/peer.cu): the per-rank slices of a bucket are disjoint, 4-element aligned and cover it, for
-    every world size the kernel supports and for the real bucket plans of both architectures."""
-    from b200step.model import ARCHS, FlatLayout
-    from b200step.peer import slice_bounds
-
-    ranges = [(0, 64), (64, 64 * 5), (128, 128 + 64 * 1001)]
-    for arch in ARCHS.values():
-        ranges += [(s, e) for s, e, _ in FlatLayout(arch).buckets()]
-    for start, end in ranges:
-        assert start % 4 == 0 and (end - start) % 4 == 0
-        for world in range(1, 9):
-            pos = start
-            for rank in range(world):
-                lo, hi = slice_bounds(start, end, world, rank)
-                assert lo == pos or lo == hi == end, (start, end, world, rank)
-                assert lo % 4 == 0 and (hi - lo) % 4 == 0 and lo <= hi <= end
-                pos = hi if hi > lo else pos
-            assert pos == end
-
-
 def test_bench_reference_arm_config1_line():
     """`bench.py --impl reference --workload t0_fp32_b4096_cpu_gloo2` (BASELINE config 1: the oracle under real DDP over
     gloo, 2 CPU processes) prints one JSON line with the reference arm's keys."""

@@ -239,30 +239,6 @@ def test_overlapped_prefetch_equals_the_plain_schedule():
     assert a[2].kernels_per_step == b[2].kernels_per_step + 1     # the table optimizer became its own launch
 
 
-@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
-@pytest.mark.parametrize("precision", ["bf16", "fp32"])
-def test_peer_optimizer_single_rank(optimizer, precision):
-    """StepConfig.peer_optimizer with world = 1: the peer kernels (flags, slice reduce, update, parameter + bf16
-    store, gradient zeroing, bookkeeping) on one GPU, eager + graph replay + tail batch, against the oracle."""
-    spec = SMALL
-    rows, batch = 1400, 256
-    ds = make_synthetic(rows, spec)
-    lr = 0.1 if optimizer == "sgd" else 1e-3
-    oracle = OracleTrainer(_spec_dict(spec), ds, world=1, batch_size=batch, precision=precision, optimizer=optimizer,
-                           lr=lr)
-    eng = TrainStep(spec, init_parameters(spec, 0), ds, rank_indices(rows, 1, 0),
-                    StepConfig(batch_size=batch, precision=precision, optimizer=optimizer, lr=lr, peer_optimizer=True))
-    for epoch in range(2):
-        for b in range(6):
-            lo = oracle.step()[0]
-            eng.step() if b < 5 else eng.step_tail()
-            assert abs(lo - eng.loss_value()) <= 2e-3 * max(1.0, abs(lo)), (epoch, b)
-    eng.synchronize()                                   # raises if a flag wait timed out
-    assert int(eng.cursor.item()) == 0 and int(eng.step_ctr.item()) == 12
-    assert float(eng.g.abs().max().item()) == 0.0       # the finishing kernel left the gradients zeroed
-    assert _param_err(oracle, eng) <= (1e-2 if optimizer == "sgd" else 5e-2)
-
-
 def test_set_row_order_reshuffles_between_epochs():
     """TrainStep.set_row_order (task.py --set_epoch): the graph-replayed step follows the new order."""
     spec = SMALL

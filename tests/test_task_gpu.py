@@ -85,26 +85,3 @@ def test_task_py_two_gpus_matches_ddp_oracle(tmp_path):
     lg = float(re.search(r"final local loss \(rank 0\): ([0-9.eE+-]+)", r.stdout).group(1))
     assert abs(l0 - lg) <= 2e-3 * max(1.0, abs(l0))
     _compare(torch.load(os.path.join(tmp_path, "resnet_distributed.pth.final")), oracle, 1e-2)
-
-
-@pytest.mark.skipif(torch.cuda.device_count() < 2 or os.environ.get("B200STEP_TEST_PEER") != "1",
-                    reason="EXPERIMENTAL path: needs 2 GPUs and B200STEP_TEST_PEER=1 (the 2-rank run has not passed on "
-                           "hardware yet; the single-rank path is covered by test_peer_optimizer_single_rank)")
-@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
-def test_task_py_two_gpus_peer_optimizer(tmp_path, optimizer):
-    """B200STEP_PEER_OPT=1 (EXPERIMENTAL, no CLI flag until this test has passed on hardware): the NVLink peer-memory reduce + update + broadcast kernel instead of NCCL
-    all-reduce + optimizer; same DDP semantics, same oracle, same tolerances."""
-    rows, batch, epochs = 2048 + 100, 256, 3          # 4 full batches + a partial one per rank and epoch
-    lr = "0.1" if optimizer == "sgd" else "0.001"
-    r = _launch(2, tmp_path, rows, batch, epochs, 29563 + (optimizer == "adam"),
-                extra=("--optimizer", optimizer, "--learning_rate", lr), env_extra={"B200STEP_PEER_OPT": "1"})
-    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
-    ds = make_synthetic(rows, SPEC)
-    oracle = OracleTrainer(_sd(SPEC), ds, world=2, batch_size=batch, precision="bf16", optimizer=optimizer,
-                           lr=float(lr))
-    for _ in range(epochs * oracle.steps_per_epoch):
-        l0 = oracle.step()[0]
-    lg = float(re.search(r"final local loss \(rank 0\): ([0-9.eE+-]+)", r.stdout).group(1))
-    assert abs(l0 - lg) <= 2e-3 * max(1.0, abs(l0))
-    _compare(torch.load(os.path.join(tmp_path, "resnet_distributed.pth.final")), oracle,
-             1e-2 if optimizer == "sgd" else 5e-2)
