@@ -235,6 +235,14 @@ int b200_comm_init(const void* unique_id_host_128, int rank, int world);
 int b200_comm_allreduce_sum(float* buf, int64_t count, b200_stream_t stream);
 int b200_comm_broadcast(float* buf, int64_t count, int root, b200_stream_t stream); /* DDP ctor param sync */
 int b200_comm_destroy(void);
+/* Optional: gradient memory that NCCL can reduce in place.  b200_comm_mem_alloc returns device memory from
+ * ncclMemAlloc (the one allocation this library makes for the caller: NVSwitch multicast / in-switch reduction only
+ * maps memory NCCL allocated itself); b200_comm_register registers a buffer with the communicator (after
+ * b200_comm_init; deregistered by b200_comm_destroy).  The flat gradient buffer is the intended tenant:
+ * DistributedDataParallel's buckets (task.py:189) are copies, here the all-reduce runs on the gradients themselves. */
+int b200_comm_mem_alloc(int64_t bytes, void** out_host);
+int b200_comm_mem_free(void* ptr);
+int b200_comm_register(void* buf, int64_t bytes);
 
 /* ---- streams / events / graphs (host plumbing for the step schedule) ------------------------ */
 int b200_stream_create(b200_stream_t* out_host, int high_priority);

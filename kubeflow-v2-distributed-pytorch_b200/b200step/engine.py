@@ -54,6 +54,7 @@ class StepConfig:
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
     comm_sm_reserve: Optional[int] = None  # None = DEFAULT_COMM_SM_RESERVE when world > 1 and comm overlaps
     prefetch_sm_reserve: int = 32        # SMs the prefetched K-pre leaves to the all-reduces it runs under
+    nccl_registered_grads: bool = False  # world > 1: flat gradient buffer from ncclMemAlloc + ncclCommRegister
     prefetch_pre: Optional[bool] = None  # run K-pre of the NEXT batch inside this step (device-resident `step()`
                                          # path only).  world == 1: the table gradients are complete before the wgrad
                                          # GEMMs start, so a side stream updates the tables and gathers the next batch
@@ -102,10 +103,34 @@ class Communicator:
     def broadcast(self, t: torch.Tensor, root: int, stream: torch.cuda.Stream) -> None:
         get_lib().comm_broadcast(t.data_ptr(), t.numel(), root, stream.cuda_stream)
 
+    def alloc_registered(self, numel: int, device: torch.device) -> torch.Tensor:
+        """A zeroed fp32 buffer from ncclMemAlloc, registered with the communicator: all-reduces on it run in place
+        (no staging copies) and may use NVSwitch in-network reduction."""
+        import ctypes as C
+
+        out = C.c_void_p()
+        get_lib().comm_mem_alloc(4 * numel, C.byref(out))
+        get_lib().comm_register(out.value, 4 * numel)
+        t = torch.as_tensor(_DevicePtr(out.value, numel), device=device)
+        t.zero_()
+        self._owned = getattr(self, "_owned", []) + [out.value]
+        return t
+
     def close(self) -> None:
         if self._alive:
             get_lib().comm_destroy()
+            for ptr_ in getattr(self, "_owned", []):
+                get_lib().comm_mem_free(ptr_)
+            self._owned = []
             self._alive = False
+
+
+class _DevicePtr:
+    """Lets torch wrap raw device memory (here: an ncclMemAlloc allocation) as a tensor."""
+
+    def __init__(self, ptr: int, numel: int):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": "<f4", "data": (ptr, False), "version": 3,
+                                         "strides": None}
 
 
 class TrainStep:
@@ -139,7 +164,10 @@ class TrainStep:
 
         # ---- flat parameter / gradient / optimizer-state buffers
         self.p = lay.flatten(init_params).to(dev)
-        self.g = torch.zeros_like(self.p)
+        if cfg.world > 1 and cfg.nccl_registered_grads:
+            self.g = comm.alloc_registered(lay.total, dev)     # the all-reduce works on the gradients in place
+        else:
+            self.g = torch.zeros_like(self.p)
         self.shadow = None
         if self.dt == torch.bfloat16:
             self.shadow = torch.zeros(lay.n_shadow, dtype=torch.bfloat16, device=dev)

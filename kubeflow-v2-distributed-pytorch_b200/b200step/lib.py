@@ -59,6 +59,9 @@ SIGNATURES = {
     "b200_comm_allreduce_sum": (_i, [_p, _i64, _p]),
     "b200_comm_broadcast": (_i, [_p, _i64, _i, _p]),
     "b200_comm_destroy": (_i, []),
+    "b200_comm_mem_alloc": (_i, [_i64, C.POINTER(_p)]),
+    "b200_comm_mem_free": (_i, [_p]),
+    "b200_comm_register": (_i, [_p, _i64]),
     "b200_stream_create": (_i, [C.POINTER(_p), _i]),
     "b200_stream_destroy": (_i, [_p]),
     "b200_stream_sync": (_i, [_p]),

@@ -23,11 +23,19 @@ struct NcclApi {
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  // user-buffer registration (NCCL >= 2.19; optional: resolved lazily, absent symbols just disable the feature)
+  ncclResult_t (*MemAlloc)(void**, size_t) = nullptr;
+  ncclResult_t (*MemFree)(void*) = nullptr;
+  ncclResult_t (*CommRegister)(const ncclComm_t, void*, size_t, void**) = nullptr;
+  ncclResult_t (*CommDeregister)(const ncclComm_t, void*) = nullptr;
 };
 
 static NcclApi g_nccl;
 static ncclComm_t g_comm = nullptr;
 static int g_world = 0;
+constexpr int MAX_REG = 16;
+static void* g_reg_handles[MAX_REG];
+static int g_num_reg = 0;
 
 static int load_nccl() {
   if (g_nccl.handle) return 0;
@@ -47,6 +55,10 @@ static int load_nccl() {
   B200_NCCL_SYM(Broadcast, "ncclBroadcast");
   B200_NCCL_SYM(GetErrorString, "ncclGetErrorString");
 #undef B200_NCCL_SYM
+  *reinterpret_cast<void**>(&g_nccl.MemAlloc) = dlsym(h, "ncclMemAlloc");
+  *reinterpret_cast<void**>(&g_nccl.MemFree) = dlsym(h, "ncclMemFree");
+  *reinterpret_cast<void**>(&g_nccl.CommRegister) = dlsym(h, "ncclCommRegister");
+  *reinterpret_cast<void**>(&g_nccl.CommDeregister) = dlsym(h, "ncclCommDeregister");
   g_nccl.handle = h;
   return 0;
 }
@@ -102,8 +114,39 @@ extern "C" int b200_comm_broadcast(float* buf, int64_t count, int root, b200_str
   return 0;
 }
 
+// Memory NCCL can use in place (ncclMemAlloc: a cuMem allocation that NVSwitch multicast / in-switch reduction can
+// map) and its registration with the communicator: an all-reduce on a registered buffer skips NCCL's staging copies
+// and, on an NVSwitch node, may run as an NVLS (in-network) reduction.
+extern "C" int b200_comm_mem_alloc(int64_t bytes, void** out_host) {
+  B200_REQUIRE(out_host != nullptr && bytes > 0, "bad arguments to b200_comm_mem_alloc");
+  if (int r = load_nccl()) return r;
+  B200_REQUIRE(g_nccl.MemAlloc != nullptr, "this libnccl has no ncclMemAlloc");
+  B200_CHECK_NCCL(g_nccl.MemAlloc(out_host, (size_t)bytes));
+  return 0;
+}
+
+extern "C" int b200_comm_mem_free(void* ptr) {
+  if (ptr == nullptr) return 0;
+  B200_REQUIRE(g_nccl.MemFree != nullptr, "this libnccl has no ncclMemFree");
+  B200_CHECK_NCCL(g_nccl.MemFree(ptr));
+  return 0;
+}
+
+extern "C" int b200_comm_register(void* buf, int64_t bytes) {
+  B200_REQUIRE(g_comm != nullptr, "b200_comm_init has not been called");
+  B200_REQUIRE(buf != nullptr && bytes > 0, "bad arguments to b200_comm_register");
+  B200_REQUIRE(g_nccl.CommRegister != nullptr, "this libnccl has no ncclCommRegister");
+  B200_REQUIRE(g_num_reg < MAX_REG, "too many registered buffers");
+  B200_CHECK_NCCL(g_nccl.CommRegister(g_comm, buf, (size_t)bytes, &g_reg_handles[g_num_reg]));
+  ++g_num_reg;
+  return 0;
+}
+
 extern "C" int b200_comm_destroy(void) {
   if (g_comm) {
+    for (int i = 0; i < g_num_reg; ++i)
+      if (g_nccl.CommDeregister) g_nccl.CommDeregister(g_comm, g_reg_handles[i]);
+    g_num_reg = 0;
     B200_CHECK_NCCL(g_nccl.CommDestroy(g_comm));
     g_comm = nullptr;
     g_world = 0;
