@@ -54,7 +54,8 @@ class StepConfig:
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
     comm_sm_reserve: Optional[int] = None  # None = DEFAULT_COMM_SM_RESERVE when world > 1 and comm overlaps
     prefetch_sm_reserve: int = 32        # SMs the prefetched K-pre leaves to the all-reduces it runs under
-    nccl_registered_grads: bool = False  # world > 1: flat gradient buffer from ncclMemAlloc + ncclCommRegister
+    nccl_registered_grads: bool = True   # world > 1: flat gradient buffer from ncclMemAlloc + ncclCommRegister (in-place,
+                                         # NVLS-capable all-reduce; measured on 8 GPUs: T1 3.71 -> 3.37 ms/step, T0 equal)
     prefetch_pre: Optional[bool] = None  # run K-pre of the NEXT batch inside this step (device-resident `step()`
                                          # path only).  world == 1: the table gradients are complete before the wgrad
                                          # GEMMs start, so a side stream updates the tables and gathers the next batch
@@ -164,9 +165,13 @@ class TrainStep:
 
         # ---- flat parameter / gradient / optimizer-state buffers
         self.p = lay.flatten(init_params).to(dev)
+        self.g = None
         if cfg.world > 1 and cfg.nccl_registered_grads:
-            self.g = comm.alloc_registered(lay.total, dev)     # the all-reduce works on the gradients in place
-        else:
+            try:
+                self.g = comm.alloc_registered(lay.total, dev)     # the all-reduce works on the gradients in place
+            except B200Error as e:    # an older libnccl without ncclMemAlloc / ncclCommRegister: plain device memory
+                print(f"[b200step] NCCL buffer registration unavailable ({e}); using unregistered gradient memory")
+        if self.g is None:
             self.g = torch.zeros_like(self.p)
         self.shadow = None
         if self.dt == torch.bfloat16:
