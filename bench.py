@@ -313,6 +313,8 @@ def run_b200(args, rank, local_rank, world):
         cfg.comm_sm_reserve = int(os.environ["B200STEP_SM_RESERVE"])
     if os.environ.get("B200STEP_PREFETCH_RESERVE"):
         cfg.prefetch_sm_reserve = int(os.environ["B200STEP_PREFETCH_RESERVE"])
+    if os.environ.get("B200STEP_L2_ORDER"):               # A/B: alternating row-tile direction of consecutive GEMMs
+        cfg.l2_tile_order = os.environ["B200STEP_L2_ORDER"] != "0"
     if os.environ.get("B200STEP_NCCL_REG"):               # A/B: gradients in NCCL-registered memory (NVLS-capable)
         cfg.nccl_registered_grads = os.environ["B200STEP_NCCL_REG"] != "0"
     if os.environ.get("B200STEP_GROUPED_WGRAD"):          # A/B at world > 1: one wgrad launch, buckets reduced after it

@@ -30,6 +30,8 @@ typedef void* b200_stream_t; /* a cudaStream_t */
 
 #define B200_FLAG_RELU 1      /* fwd: y = max(y,0);  dgrad: dx *= (act > 0) */
 #define B200_FLAG_ACCUMULATE 2 /* wgrad: dw += ... instead of dw = ... */
+#define B200_FLAG_REVERSE_M 4  /* fwd / dgrad: process the row tiles last-to-first.  Same result; a consumer that starts
+                                  with the rows its producer wrote LAST finds them still in the 126 MB L2 */
 
 /* ---- errors / build info ------------------------------------------------------------------ */
 const char* b200_last_error(void);           /* host string, thread-local */

@@ -54,6 +54,8 @@ class StepConfig:
     micro_rows: int = 0                  # rows per chunk of a step (0 = whole batch; must be a multiple of 8)
     comm_sm_reserve: Optional[int] = None  # None = DEFAULT_COMM_SM_RESERVE when world > 1 and comm overlaps
     prefetch_sm_reserve: int = 32        # SMs the prefetched K-pre leaves to the all-reduces it runs under
+    l2_tile_order: bool = True           # alternate the row-tile direction of consecutive GEMMs (B200_FLAG_REVERSE_M) so
+                                         # that each one starts with the rows its producer wrote last (still in L2)
     nccl_registered_grads: bool = True   # world > 1: flat gradient buffer from ncclMemAlloc + ncclCommRegister (in-place,
                                          # NVLS-capable all-reduce; measured on 8 GPUs: T1 3.71 -> 3.37 ms/step, T0 equal)
     prefetch_pre: Optional[bool] = None  # run K-pre of the NEXT batch inside this step (device-resident `step()`
@@ -326,7 +328,10 @@ class TrainStep:
             ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li][sl], M=rows, N=o, K=kk, relu=not last,
                            dropout_p=spec.dropout if (training and not last) else 0.0, seed=cfg.dropout_seed,
                            step=self.step_ctr, layer_id=li,
-                           relu_mask=self.masks[li][sl] if (training and not last) else None, row0=r0, stream=st)
+                           relu_mask=self.masks[li][sl] if (training and not last) else None, row0=r0,
+                           # the loss kernel walks the rows upwards: the layer feeding it runs downwards, the one
+                           # before upwards, ...
+                           reverse_m=cfg.l2_tile_order and (self.L - 2 - li) % 2 == 0, stream=st)
             n += 1
             inp = self.acts[li][sl]
         return n
@@ -404,7 +409,8 @@ class TrainStep:
                 # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums += bias gradient of layer l-1
                 ops.linear_dgrad(dys[li], self._w(li), None, dx, M=rows, N=o, K=k, relu=True, dscale=inv_keep,
                                  relu_mask=self.masks[li - 1][sl], dbias=self._b(li - 1, grad=True),
-                                 scratch=self.dg_scratch if cfg.deterministic_bias_grad else None, stream=st)
+                                 scratch=self.dg_scratch if cfg.deterministic_bias_grad else None,
+                                 reverse_m=cfg.l2_tile_order and (L - 1 - li) % 2 == 0, stream=st)
                 n += 2 if cfg.deterministic_bias_grad else 1
                 dys[li - 1] = dx
             if spec.num_cat:
@@ -416,7 +422,7 @@ class TrainStep:
                     n += 1
                 else:
                     ops.linear_dgrad(dys[0], self._w(0), None, self.dx0[sl], M=rows, N=dims[0][1], K=self.k0,
-                                     relu=False, stream=st)
+                                     relu=False, reverse_m=cfg.l2_tile_order and (L - 1) % 2 == 0, stream=st)
                     ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
                                 num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim,
                                 stream=st)

@@ -10,7 +10,7 @@ from typing import Optional
 import torch
 
 from . import lib as _l
-from .lib import BF16, F32, FLAG_ACCUMULATE, FLAG_RELU, get_lib, ptr
+from .lib import BF16, F32, FLAG_ACCUMULATE, FLAG_RELU, FLAG_REVERSE_M, get_lib, ptr
 
 __all__ = [
     "dtype_code", "preprocess", "linear_fwd", "linear_dgrad", "linear_wgrad", "ce_loss_grad", "colsum",
@@ -53,10 +53,11 @@ def preprocess(ds_dense, ds_cat, ds_label, row_idx, cursor, mean, std, tables, x
 
 
 def linear_fwd(x, w, bias, y, *, M: int, N: int, K: int, relu: bool, dropout_p: float = 0.0, seed: int = 0,
-               step=None, layer_id: int = 0, row0: int = 0, relu_mask=None, stream=None):
+               step=None, layer_id: int = 0, row0: int = 0, relu_mask=None, reverse_m: bool = False, stream=None):
     _cuda(x, w, bias, y, relu_mask)
     get_lib().linear_fwd(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(y), y.stride(0), M, N, K,
-                         dtype_code(x.dtype), FLAG_RELU if relu else 0, float(dropout_p), int(seed),
+                         dtype_code(x.dtype), (FLAG_RELU if relu else 0) | (FLAG_REVERSE_M if reverse_m else 0),
+                         float(dropout_p), int(seed),
                          ptr(step), layer_id, int(row0), ptr(relu_mask),
                          relu_mask.stride(0) if relu_mask is not None else 0, _stream(stream))
 
@@ -66,11 +67,12 @@ def dgrad_scratch_floats(M: int, K: int) -> int:
 
 
 def linear_dgrad(dy, w, act, dx, *, M: int, N: int, K: int, relu: bool, dscale: float = 1.0, relu_mask=None,
-                 dbias=None, scratch=None, stream=None):
+                 dbias=None, scratch=None, reverse_m: bool = False, stream=None):
     _cuda(dy, w, act, dx, relu_mask, dbias, scratch)
     get_lib().linear_dgrad(ptr(dy), dy.stride(0), ptr(w), w.stride(0), ptr(act),
                            act.stride(0) if act is not None else 0, ptr(dx), dx.stride(0), M, N, K,
-                           dtype_code(dy.dtype), FLAG_RELU if relu else 0, float(dscale), ptr(relu_mask),
+                           dtype_code(dy.dtype), (FLAG_RELU if relu else 0) | (FLAG_REVERSE_M if reverse_m else 0),
+                           float(dscale), ptr(relu_mask),
                            relu_mask.stride(0) if relu_mask is not None else 0, ptr(dbias), ptr(scratch),
                            scratch.numel() if scratch is not None else 0, _stream(stream))
 

@@ -119,7 +119,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t ph = 0;
       for (int w = unit; w < total; w += nunits) {
         const int tile = w % tiles, split = w / tiles;
-        const int m0 = (tile / p.n_tiles) * TILE_M + rank * BLOCK_M;     // this CTA's rows of A
+        int mt = tile / p.n_tiles;
+        if (p.flags & B200_FLAG_REVERSE_M) mt = p.m_tiles - 1 - mt;       // walk the row tiles from the last one down
+        const int m0 = mt * TILE_M + rank * BLOCK_M;                      // this CTA's rows of A
         const int n0 = (tile % p.n_tiles) * BLOCK_N + rank * B_ROWS;     // this CTA's share of the B tile
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
@@ -223,7 +225,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     float csacc[4] = {0.f, 0.f, 0.f, 0.f};
     for (int w = unit; w < total; w += nunits, ++it) {
       const int tile = w % tiles;
-      const int m0 = (tile / p.n_tiles) * TILE_M + rank * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
+      int mt = tile / p.n_tiles;
+      if (p.flags & B200_FLAG_REVERSE_M) mt = p.m_tiles - 1 - mt;
+      const int m0 = mt * TILE_M + rank * BLOCK_M, n0 = (tile % p.n_tiles) * BLOCK_N;
       const int a = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       const int row0 = m0 + q * 32;
