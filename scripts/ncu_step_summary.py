@@ -26,8 +26,12 @@ BYTES = {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}
 TIME = {"ns": 1e-3, "us": 1, "ms": 1e3, "s": 1e6}
 names = [r[ix["Kernel Name"]] for r in rows]
 pre = [i for i, n in enumerate(names) if "preprocess" in n]
-assert len(pre) >= 2, "capture must hold at least one whole step (two K-pre launches)"
-step = rows[pre[-2]:pre[-1]]           # the last complete step in the capture
+assert pre, "capture holds no K-pre launch"
+if len(pre) >= 2:
+    step = rows[pre[-2]:pre[-1]]       # the last complete step in the capture
+else:                                  # one K-pre launch: the step runs to the optimizer launch that follows it
+    end = next(i for i in range(pre[0], len(names)) if "sgd_kernel" in names[i] or "adam_kernel" in names[i])
+    step = rows[pre[0]:end + 1]
 
 
 def short(n):
