@@ -36,7 +36,8 @@ for _p in (ROOT, PKG):
 
 WORKLOADS = {
     "t0_bf16_b65536": dict(arch="tabular_mlp", precision="bf16", batch=65536, optimizer="sgd"),
-    "t0_fp32_b4096": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd"),
+    "t0_fp32_b4096": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd"),   # 3xTF32 = fp32-grade
+    "t0_tf32_b4096": dict(arch="tabular_mlp", precision="tf32", batch=4096, optimizer="sgd"),   # single TF32 pass
     "t1_bf16_b65536": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="sgd"),
     "t1_bf16_b65536_adam": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="adam"),
     # BASELINE config 1 (CPU only, `--impl reference`): the oracle as real DistributedDataParallel over gloo,
@@ -45,6 +46,31 @@ WORKLOADS = {
 }
 BATCHES_PER_RANK = 8          # distinct batches per rank, cycled (N = W*B*8 rows)
 REF_SAMPLE_CAP = 65536        # rows per step of the CPU arms (bounded sample)
+
+
+def _measure_tf32_peak(dev):
+    """TF32 tensor-core peak measured the way MEASURED_PEAKS.json measures bf16: torch.matmul 8192^3 on fp32 operands
+    with TF32 allowed, best of 10 (CUDA events).  A library GEMM, used as the yardstick only."""
+    import torch
+
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev)
+        b = torch.randn(n, n, device=dev)
+        best = float("inf")
+        for i in range(13):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(a, b)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            if i >= 3:
+                best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best / 1e3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 def _peaks():
@@ -441,7 +467,16 @@ def run_b200(args, rank, local_rank, world):
     mem = [r for r in prof if r["bound"] == "hbm"]
     gem_ms = sum(r["ms"] * r["per_step"] for r in gem)
     gem_tflops = sum(r["tflops"] * r["ms"] * r["per_step"] for r in gem) / gem_ms      # = sum(flops) / sum(time)
-    tensor_peak = peaks["bf16_tflops"] if wl["precision"] == "bf16" else peaks["bf16_tflops"] / 2.0
+    if wl["precision"] == "bf16":
+        tensor_peak, peak_note = peaks["bf16_tflops"], peaks["source"] + " bf16 burst"
+    else:
+        # fp32 storage: the yardstick is the TF32 tensor-core rate, measured in this run.  "fp32" spends three TF32
+        # products per algorithmic multiply-add (error compensation), so its ceiling is a third of it.
+        tf32_peak = _measure_tf32_peak(dev)
+        passes = 3.0 if wl["precision"] == "fp32" else 1.0
+        tensor_peak = tf32_peak / passes
+        peak_note = (f"TF32 peak measured in this run (torch.matmul 8192^3, best of 10): {tf32_peak:.1f} TFLOP/s"
+                     + (" / 3 passes of the error-compensated product" if passes > 1 else ""))
     gem_traffic = [traffic_tab.get(r["name"]) for r in gem]
     roof_tensor = {"bound": "tensor", "kernel": "gemm_kernel (fwd + dgrad + wgrad launches of the step)",
                    "achieved": gem_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": gem_tflops / tensor_peak,
@@ -449,8 +484,7 @@ def run_b200(args, rank, local_rank, world):
                    "share_of_step": gem_ms / total_ms, "share_of_step_ms": gem_ms / step_ms,
                    "kernel_ms": gem_ms, "flops_basis": "2*M*N*K on unpadded dims (SURVEY.md 8d)",
                    "launches_per_step": sum(r["per_step"] for r in gem),
-                   "peak_source": peaks["source"] + (" bf16 burst" if wl["precision"] == "bf16"
-                                                     else " bf16 burst / 2 (tf32 runs at half the bf16 rate)")}
+                   "peak_source": peak_note}
     topm = max(mem, key=lambda r: r["ms"])
     roof_hbm = {"bound": "hbm", "kernel": topm["name"], "achieved": topm["gbs"], "peak": peaks["hbm_gbs"],
                 "unit": "GB/s", "frac": topm["gbs"] / peaks["hbm_gbs"], "traffic": traffic_tab.get(topm["name"]),
@@ -461,7 +495,7 @@ def run_b200(args, rank, local_rank, world):
     out = {
         "metric": "train samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16" if wl["precision"] == "bf16" else "tf32", "data": "synthetic",
+        "vs_baseline": None, "dtype": {"bf16": "bf16", "tf32": "tf32", "fp32": "f32"}[wl["precision"]], "data": "synthetic",
         "config": {"workload": args.workload, "arch": wl["arch"], "per_gpu_batch": B, "global_batch": B * world,
                    "optimizer": wl["optimizer"], "params": spec.num_params, "parallelism": f"dp{world}",
                    "l2": "per-step working set > 126 MB L2 (no flush needed)" if B >= 32768 else
@@ -499,7 +533,7 @@ def profile_kernels(eng, spec, B, world):
 
     names = ["preprocess", "linear_fwd", "linear_ce", "ce_loss_grad", "linear_dgrad", "linear_dgrad_emb", "linear_wgrad",
              "linear_wgrad_grouped",
-             "colsum", "emb_bwd", "zero", "sgd_step", "adam_step"]
+             "colsum", "emb_bwd", "zero", "sgd_step", "adam_step", "split_tf32"]
     records = []
     orig = {n: getattr(ops, n) for n in names}
     es = 2 if eng.dt == torch.bfloat16 else 4
@@ -515,15 +549,23 @@ def profile_kernels(eng, spec, B, world):
             # FLOPs follow SURVEY.md §8(d): 2*M*N*K on UNPADDED dims (the first layer's K is stored padded to a
             # whole number of 128-byte rows), and the layer-0 dgrad only for the embedding columns
             unpad = lambda kk: spec.in_features if (kk == eng.k0 and eng.k0 != spec.in_features) else kk
+            x3 = 3 if getattr(eng, "x3", False) else 1   # "fp32": contraction dimension 3x as long (hi/lo copies);
+            #                                               FLOPs stay the algorithmic ones
             if name == "linear_wgrad_grouped":
-                label = f"linear_wgrad_grouped[{k['M']}x{len(k['Ns'])} layers]"
-                work = {"flops": sum(2.0 * k["M"] * n_ * unpad(k_) for n_, k_ in zip(k["Ns"], k["Ks"]))}
+                label = f"linear_wgrad_grouped[{k['M'] // x3}x{len(k['Ns'])} layers]"
+                work = {"flops": sum(2.0 * (k["M"] // x3) * n_ * unpad(k_) for n_, k_ in zip(k["Ns"], k["Ks"]))}
             elif name == "linear_dgrad_emb":
                 kk = k["num_cat"] * k["embed_dim"]
                 label = f"linear_dgrad_emb[{k['M']}x{k['N']}x{kk}]"
                 work = {"flops": 2.0 * k["M"] * k["N"] * kk}   # embedding columns only; the scatter rides along
             elif name.startswith("linear_"):
                 M, N, K = k["M"], k["N"], k["K"]
+                if name in ("linear_fwd", "linear_ce"):
+                    K //= x3
+                elif name == "linear_dgrad":
+                    N //= x3
+                elif name == "linear_wgrad":
+                    M //= x3
                 label = f"{name}[{M}x{N}x{K}]" + ("+dbias" if k.get("dbias") is not None else "")
                 keff = unpad(K)
                 if name == "linear_dgrad" and K == eng.k0 and spec.num_cat:
@@ -537,6 +579,9 @@ def profile_kernels(eng, spec, B, world):
                         "dram_bytes": B * (raw + es * eng.k0 + 8 + 4 * spec.num_cat)}
             elif name == "ce_loss_grad":
                 work = {"bytes": B * (2 * es * spec.num_classes + 8)}
+            elif name == "split_tf32":
+                outs = (a[1] is not None) + (a[3] is not None)
+                work = {"bytes": 4.0 * k["rows"] * k["cols"] * (1 + 3 * outs)}
             elif name == "colsum":
                 work = {"bytes": k["M"] * k["N"] * es}
             elif name == "emb_bwd":

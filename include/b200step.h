@@ -221,6 +221,15 @@ int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg_sq, void* 
                    int64_t n, int64_t n_shadow, double lr, double beta1, double beta2, double eps,
                    double weight_decay, const int32_t* step, int zero_grad, int32_t* adv_cursor,
                    int32_t* adv_step, int32_t steps_per_epoch, uint32_t* adv_ticket, b200_stream_t stream);
+/* Operands for fp32-accurate linear layers on TF32 tensor cores ("3xTF32"; task.py:309 computes in IEEE fp32):
+ * every value is split into hi = tf32(x) and lo = x - hi, and three copies are laid out along the contraction
+ * dimension so that ONE TF32 GEMM over the 3x longer contraction computes a_hi.b_hi + a_hi.b_lo + a_lo.b_hi
+ * (relative error ~2^-22 instead of 2^-11).  src[rows, cols] (row stride ld) ->
+ *   kcat   [rows, 3*cols]  column block j = lo if bit j of kmask else hi     (contraction along the row)
+ *   rstack [3*rows, cols]  row block j    = lo if bit j of rmask else hi     (contraction over rows)
+ * either output may be NULL.  Pairings: left operand mask 0b100 (hi,hi,lo), right operand mask 0b010 (hi,lo,hi). */
+int b200_split_tf32(const float* src, int64_t ld, int64_t rows, int64_t cols, float* kcat, int kmask,
+                    float* rstack, int rmask, b200_stream_t stream);
 /* fp32 -> bf16 RNE copy (initial shadow weights) */
 int b200_cast_bf16(const float* src, void* dst_bf16, int64_t n, b200_stream_t stream);
 /* zero `bytes` bytes of device memory on the stream (gradient regions that are accumulated with atomics) */

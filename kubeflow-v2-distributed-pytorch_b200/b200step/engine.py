@@ -36,7 +36,10 @@ class StepConfig:
     batch_size: int                      # per process, like the reference's --batch_size
     world: int = 1
     rank: int = 0
-    precision: str = "bf16"              # "bf16" (bf16 storage, fp32 accumulate/master) | "fp32" (TF32 tensor cores)
+    precision: str = "bf16"              # "bf16" (bf16 storage, fp32 accumulate/master) | "tf32" (fp32 storage, one
+                                         # TF32 tensor-core pass, ~1e-3) | "fp32" (fp32 storage, three error-
+                                         # compensated TF32 passes per product = fp32-grade, ~1e-6: task.py:309's
+                                         # arithmetic)
     optimizer: str = "sgd"               # task.py:212-214 | additive "adam"
     lr: float = 0.1                      # task.py:59
     momentum: float = 0.9                # task.py:68
@@ -199,6 +202,8 @@ class TrainStep:
         ed = spec.embed_dim
         pow2 = ed >= 4 and (ed & (ed - 1)) == 0
         self.fused_emb = bool(cfg.fused_emb_bwd)
+        if self.fused_emb and cfg.precision == "fp32":
+            raise ValueError("fused_emb_bwd runs single-pass TF32 products: use precision tf32 or bf16 with it")
         if self.fused_emb and not (spec.num_cat > 0 and pow2):
             raise ValueError("fused_emb_bwd needs categorical features with a power-of-two embedding width >= 4")
         self.dx0 = None if self.fused_emb else torch.zeros(B, self.k0, dtype=self.dt, device=dev)
@@ -225,6 +230,21 @@ class TrainStep:
         self.masks = [torch.zeros(B, ((o + 31) // 32 + 3) // 4 * 4, dtype=torch.int32, device=dev)
                       for (_, o) in dims[:-1]]
         self.dg_scratch = torch.empty(max(ops.dgrad_scratch_floats(B, wmax), 4), dtype=torch.float32, device=dev)
+        # "fp32" = 3xTF32: every GEMM operand also exists as hi/lo copies laid out along the contraction dimension
+        # (ops.split_tf32), so that the TF32 kernels compute a_hi.b_hi + a_hi.b_lo + a_lo.b_hi in one pass over a 3x
+        # longer contraction.  k-concatenated copies feed fwd / dgrad, row-stacked copies feed wgrad.
+        self.x3 = cfg.precision == "fp32"
+        if self.x3:
+            if cfg.micro_rows:
+                raise ValueError("precision fp32 (3xTF32) does not support micro_rows")
+            f32 = dict(dtype=torch.float32, device=dev)
+            self.kin = [self.k0 if li == 0 else k for li, (k, _) in enumerate(dims)]
+            self.xk = [torch.zeros(B, 3 * kin, **f32) for kin in self.kin]          # layer input  [hi | hi | lo]
+            self.xr = [torch.zeros(3 * B * kin, **f32) for kin in self.kin]         # layer input  [hi ; lo ; hi]
+            self.dyk = [torch.zeros(B, 3 * o, **f32) for (_, o) in dims]            # output grad  [hi | hi | lo]
+            self.dyr = [torch.zeros(3 * B * o, **f32) for (_, o) in dims]           # output grad  [hi ; hi ; lo]
+            self.wk = [torch.zeros(o, 3 * kin, **f32) for kin, (_, o) in zip(self.kin, dims)]   # W [hi | lo | hi]
+            self.wr = [torch.zeros(3 * o, kin, **f32) for kin, (_, o) in zip(self.kin, dims)]   # W [hi ; lo ; hi]
         self.identity_idx = None  # lazily built for host-fed batches
 
         # ---- streams / events
@@ -255,9 +275,27 @@ class TrainStep:
                 comm.broadcast(self.p, 0, self.main)
                 if self.shadow is not None:
                     ops.cast_bf16(self.p[: lay.n_shadow], self.shadow, stream=self.main)
+            if self.x3:
+                self._split_weights()
         self.main.synchronize()
 
     # ------------------------------------------------------------------------------------------ helpers
+    def _split(self, src: torch.Tensor, kcat, kmask: int, rflat, rmask: int, rows: int, cols: int) -> int:
+        """hi/lo operand copies of src[rows, cols] for the 3xTF32 GEMMs (one launch)."""
+        r = rflat[: 3 * rows * cols].view(3 * rows, cols) if rflat is not None else None
+        ops.split_tf32(src, kcat[:rows] if kcat is not None else None, kmask, r, rmask, rows=rows, cols=cols,
+                       stream=self.main)
+        return 1
+
+    def _rstack(self, flat: torch.Tensor, rows: int, cols: int) -> torch.Tensor:
+        return flat[: 3 * rows * cols].view(3 * rows, cols)
+
+    def _split_weights(self) -> int:
+        """Refresh the hi/lo copies of every Linear weight (after the optimizer touched them)."""
+        for li, (_, o) in enumerate(self.spec.layer_dims):
+            ops.split_tf32(self._w(li), self.wk[li], ops.SPLIT_RIGHT, self.wr[li], ops.SPLIT_RIGHT, rows=o,
+                           cols=self.kin[li], stream=self.main)
+        return self.L
     def _w(self, li: int) -> torch.Tensor:
         seg = self.layout.weight(li)
         return self.wsrc[seg.offset: seg.offset + seg.numel_stored].view(seg.rows, seg.ld)
@@ -320,12 +358,16 @@ class TrainStep:
         if not skip_pre:
             n += self._pre(batch, ds, row_idx, cursor, r0, rows)
         inp = self.x0[sl]
+        if self.x3:
+            n += self._split(self.x0[sl], self.xk[0], ops.SPLIT_LEFT, self.xr[0], ops.SPLIT_RIGHT, rows, self.k0)
+            inp = self.xk[0][:rows]
         for li, (k, o) in enumerate(dims):
             kk = self.k0 if li == 0 else k
             last = li == self.L - 1
             if last and skip_last:      # the caller fuses the output layer with the loss (K-gemm-ce)
                 break
-            ops.linear_fwd(inp, self._w(li), self._b(li), self.acts[li][sl], M=rows, N=o, K=kk, relu=not last,
+            ops.linear_fwd(inp, self.wk[li] if self.x3 else self._w(li), self._b(li), self.acts[li][sl], M=rows, N=o,
+                           K=3 * kk if self.x3 else kk, relu=not last,
                            dropout_p=spec.dropout if (training and not last) else 0.0, seed=cfg.dropout_seed,
                            step=self.step_ctr, layer_id=li,
                            relu_mask=self.masks[li][sl] if (training and not last) else None, row0=r0,
@@ -334,6 +376,9 @@ class TrainStep:
                            reverse_m=cfg.l2_tile_order and (self.L - 2 - li) % 2 == 0, stream=st)
             n += 1
             inp = self.acts[li][sl]
+            if self.x3 and not last:
+                n += self._split(inp, self.xk[li + 1], ops.SPLIT_LEFT, self.xr[li + 1], ops.SPLIT_RIGHT, rows, o)
+                inp = self.xk[li + 1][:rows]
         return n
 
     def evaluate(self, return_predictions: bool = False):
@@ -387,7 +432,11 @@ class TrainStep:
             if self.fused_ce:
                 # output layer and loss in one kernel: logits live in tensor memory only, dlogits is what is stored
                 k_last = dims[L - 1][0] if L > 1 else self.k0
-                ops.linear_ce(self.x0[sl] if L == 1 else self.acts[L - 2][sl], self._w(L - 1), self._b(L - 1),
+                if self.x3:
+                    x_last, w_last, k_last = self.xk[L - 1][:rows], self.wk[L - 1], 3 * k_last
+                else:
+                    x_last, w_last = (self.x0[sl] if L == 1 else self.acts[L - 2][sl]), self._w(L - 1)
+                ops.linear_ce(x_last, w_last, self._b(L - 1),
                               self.y[sl], self.dlogits[sl], self.loss, self._b(L - 1, grad=True), self.ce_scratch,
                               M=rows, N=spec.num_classes, K=k_last, grad_scale=1.0 / (batch * cfg.world),
                               loss_scale=1.0 / batch, accumulate=ci > 0, n_valid=n_valid, stream=st)
@@ -403,16 +452,23 @@ class TrainStep:
             # therefore finished first and their all-reduce hides under the wgrad GEMMs of the last chunk.
             dys = [None] * L
             dys[L - 1] = self.dlogits[sl]
+            x3 = self.x3
+            if x3:   # hi/lo copies of the output-layer gradient for its dgrad and wgrad
+                n += self._split(dys[L - 1], self.dyk[L - 1], ops.SPLIT_LEFT, self.dyr[L - 1], ops.SPLIT_LEFT, rows,
+                                 spec.num_classes)
             for li in range(L - 1, 0, -1):
                 k, o = dims[li]
                 dx = self.dh[li - 1][sl, :k]
                 # dY_{l-1} = (dY_l W_l) * mask_{l-1} / keep, and its column sums += bias gradient of layer l-1
-                ops.linear_dgrad(dys[li], self._w(li), None, dx, M=rows, N=o, K=k, relu=True, dscale=inv_keep,
+                ops.linear_dgrad(self.dyk[li][:rows] if x3 else dys[li], self.wr[li] if x3 else self._w(li), None, dx,
+                                 M=rows, N=3 * o if x3 else o, K=k, relu=True, dscale=inv_keep,
                                  relu_mask=self.masks[li - 1][sl], dbias=self._b(li - 1, grad=True),
                                  scratch=self.dg_scratch if cfg.deterministic_bias_grad else None,
                                  reverse_m=cfg.l2_tile_order and (L - 1 - li) % 2 == 0, stream=st)
                 n += 2 if cfg.deterministic_bias_grad else 1
                 dys[li - 1] = dx
+                if x3:
+                    n += self._split(dx, self.dyk[li - 1], ops.SPLIT_LEFT, self.dyr[li - 1], ops.SPLIT_LEFT, rows, k)
             if spec.num_cat:
                 # (the table gradients were zeroed by the previous optimizer pass / at allocation)
                 if self.fused_emb:
@@ -421,7 +477,8 @@ class TrainStep:
                                          embed_dim=spec.embed_dim, stream=st)
                     n += 1
                 else:
-                    ops.linear_dgrad(dys[0], self._w(0), None, self.dx0[sl], M=rows, N=dims[0][1], K=self.k0,
+                    ops.linear_dgrad(self.dyk[0][:rows] if x3 else dys[0], self.wr[0] if x3 else self._w(0), None,
+                                     self.dx0[sl], M=rows, N=3 * dims[0][1] if x3 else dims[0][1], K=self.k0,
                                      relu=False, reverse_m=cfg.l2_tile_order and (L - 1) % 2 == 0, stream=st)
                     ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
                                 num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim,
@@ -449,12 +506,17 @@ class TrainStep:
                 self._ev_join.record(ps)
             grouped = cfg.grouped_wgrad if cfg.grouped_wgrad is not None else cfg.world == 1
             xs = [self.x0[sl] if li == 0 else self.acts[li - 1][sl] for li in range(L)]
+            m_w = rows
+            if x3:   # contraction over 3 x rows: [dY_hi ; dY_hi ; dY_lo]^T . [X_hi ; X_lo ; X_hi]
+                xs = [self._rstack(self.xr[li], rows, self.kin[li]) for li in range(L)]
+                dys = [self._rstack(self.dyr[li], rows, dims[li][1]) for li in range(L)]
+                m_w = 3 * rows
             # split-K partials are red.add-ed onto the gradient buffer the optimizer left zeroed: no memset node
             if grouped:
                 # one launch for every layer's weight gradient (largest layer first)
                 order = list(range(L - 1, -1, -1))
                 ops.linear_wgrad_grouped([dys[li] for li in order], [xs[li] for li in order],
-                                         [self._gw(li) for li in order], M=rows,
+                                         [self._gw(li) for li in order], M=m_w,
                                          Ns=[dims[li][1] for li in order],
                                          Ks=[self.k0 if li == 0 else dims[li][0] for li in order], stream=st)
                 n += 1
@@ -469,7 +531,7 @@ class TrainStep:
                     # while an all-reduce is in flight the persistent GEMM grid leaves `reserve` SMs to NCCL's CTAs
                     if reserve and comm_live:
                         ops.set_sm_budget(self.sms - reserve)
-                    ops.linear_wgrad(dys[li], xs[li], self._gw(li), M=rows, N=o, K=kk, accumulate=True, stream=st)
+                    ops.linear_wgrad(dys[li], xs[li], self._gw(li), M=m_w, N=o, K=kk, accumulate=True, stream=st)
                     if reserve and comm_live:
                         ops.set_sm_budget(0)
                     n += 1
@@ -485,7 +547,7 @@ class TrainStep:
         if prefetch and self.overlap_pre:
             self._opt_range(0, lay.tables_offset, (None, self.step_ctr, spe, self.ticket), self.step_ctr, st)
             st.wait_event(self._ev_join)   # join: tables updated, cursor moved, next batch gathered
-            return n + 1
+            return n + 1 + (self._split_weights() if self.x3 else 0)
         if cfg.world > 1 and cfg.overlap_comm:
             ranges = [(self._ev_done[bi], s_, e_) for bi, (s_, e_, _) in enumerate(self.buckets)]
             order = sorted(range(len(ranges)),
@@ -520,6 +582,8 @@ class TrainStep:
             # step counter has to keep pace
             ops.advance_step(None, self.step_ctr2, spe, stream=st)
             n += 1
+        if self.x3:
+            n += self._split_weights()     # hi/lo copies of the updated weights for the next step's GEMMs
         return n
 
     def _opt_range(self, s_: int, e_: int, adv, step_ptr: torch.Tensor, stream) -> None:

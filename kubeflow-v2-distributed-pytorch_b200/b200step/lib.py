@@ -52,6 +52,7 @@ SIGNATURES = {
     "b200_emb_bwd": (_i, [_p, _i64, _p, _p, _i64, _i, _i, _i64, _i, _i, _p]),
     "b200_sgd_step": (_i, [_p, _p, _p, _p, _i64, _i64, _d, _d, _d, _i, _p, _p, C.c_int32, _p, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _d, _d, _d, _d, _d, _p, _i, _p, _p, C.c_int32, _p, _p]),
+    "b200_split_tf32": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, _i, _p]),
     "b200_cast_bf16": (_i, [_p, _p, _i64, _p]),
     "b200_zero": (_i, [_p, _i64, _p]),
     "b200_advance_step": (_i, [_p, _p, C.c_int32, _p]),

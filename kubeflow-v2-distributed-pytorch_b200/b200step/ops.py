@@ -167,6 +167,17 @@ def adam_step(p, g, m, v, shadow, step, *, n_shadow: int, lr: float, beta1: floa
                         _stream(stream))
 
 
+SPLIT_LEFT = 0b100    # (hi, hi, lo): the left operand of a 3xTF32 product
+SPLIT_RIGHT = 0b010   # (hi, lo, hi): the right operand
+
+
+def split_tf32(src, kcat, kmask: int, rstack, rmask: int, *, rows: int, cols: int, stream=None):
+    """hi/lo copies of an fp32 matrix laid out along the contraction dimension (include/b200step.h)."""
+    _cuda(src, kcat, rstack)
+    get_lib().split_tf32(ptr(src), src.stride(0), rows, cols, ptr(kcat), int(kmask), ptr(rstack), int(rmask),
+                         _stream(stream))
+
+
 def cast_bf16(src, dst, stream=None):
     _cuda(src, dst)
     get_lib().cast_bf16(ptr(src), ptr(dst), src.numel(), _stream(stream))

@@ -112,6 +112,41 @@ cast_bf16_kernel(const float* __restrict__ src, void* __restrict__ dst, long lon
     reinterpret_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16_rn(src[i]);
 }
 
+// ---- fp32 operands for error-compensated TF32 products ("3xTF32") ---------------------------------------------------
+// The tensor cores have no fp32 multiply.  With x = hi + lo, hi = tf32(x) and lo = x - hi (exact in fp32, then itself
+// within 2^-11 of a tf32 number),  a.b = a_hi.b_hi + a_hi.b_lo + a_lo.b_hi  up to 2^-22 relative: three TF32
+// products accumulated in fp32.  Laid side by side along the contraction dimension they are ONE ordinary GEMM:
+//     [A_hi | A_hi | A_lo] . [B_hi | B_lo | B_hi]^T      (contraction 3x as long)
+// so the TF32 kernels stay as they are and this kernel prepares the operands: block j of the output holds hi or lo
+// according to bit j of the mask, as three column blocks (`kcat`, for an operand whose contraction dimension is
+// its row) and / or three row blocks (`rstack`, contraction over rows).
+__device__ __forceinline__ float tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__global__ void __launch_bounds__(OPT_THREADS)
+split_tf32_kernel(const float* __restrict__ src, long long ld, long long R, int C, float* __restrict__ kcat,
+                  int kmask, float* __restrict__ rstack, int rmask) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int cv = C >> 2;
+  const long long total = R * cv;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += stride) {
+    const long long r = q / cv;
+    const int c = (int)(q - r * cv) << 2;
+    const float4 x = *reinterpret_cast<const float4*>(src + r * ld + c);
+    const float4 hi = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
+    const float4 lo = make_float4(x.x - hi.x, x.y - hi.y, x.z - hi.z, x.w - hi.w);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      if (kcat) *reinterpret_cast<float4*>(kcat + r * (3ll * C) + (long long)j * C + c) = ((kmask >> j) & 1) ? lo : hi;
+      if (rstack) *reinterpret_cast<float4*>(rstack + ((long long)j * R + r) * C + c) = ((rmask >> j) & 1) ? lo : hi;
+    }
+  }
+}
+
 __global__ void advance_step_kernel(int* cursor, int* step, int steps_per_epoch) {
   pdl_launch_dependents();
   pdl_wait();
@@ -214,6 +249,21 @@ extern "C" int b200_adam_step(float* p, float* g, float* exp_avg, float* exp_avg
 extern "C" int b200_cast_bf16(const float* src, void* dst_bf16, int64_t n, b200_stream_t stream) {
   B200_REQUIRE(n > 0, "n must be positive");
   B200_CHECK_CUDA(launch_pdl(cast_bf16_kernel, dim3(stream_grid(n / 4 + 1)), dim3(OPT_THREADS), 0, static_cast<cudaStream_t>(stream), src, dst_bf16, n));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_split_tf32(const float* src, int64_t ld, int64_t rows, int64_t cols, float* kcat, int kmask,
+                               float* rstack, int rmask, b200_stream_t stream) {
+  B200_REQUIRE(src != nullptr && rows > 0 && cols > 0 && cols % 4 == 0 && ld % 4 == 0 && ld >= cols,
+               "b200_split_tf32: cols and ld must be positive multiples of 4");
+  B200_REQUIRE(kcat != nullptr || rstack != nullptr, "b200_split_tf32: no output given");
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(kcat) |
+                 reinterpret_cast<uintptr_t>(rstack)) & 15) == 0, "b200_split_tf32: 16-byte aligned buffers needed");
+  B200_REQUIRE(kmask >= 0 && kmask < 8 && rmask >= 0 && rmask < 8, "masks are 3 bits");
+  B200_CHECK_CUDA(launch_pdl(split_tf32_kernel, dim3(stream_grid(rows * cols / 4)), dim3(OPT_THREADS), 0,
+                             static_cast<cudaStream_t>(stream), src, (long long)ld, (long long)rows, (int)cols, kcat,
+                             kmask, rstack, rmask));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

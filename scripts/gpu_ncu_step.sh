@@ -1,8 +1,4 @@
-# One full training step under `ncu --set full` (T0, bf16, B=65536) + the launch list of the same command.
-set -x
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
-$CMD > gpurun_out/ncu_plain3.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_final.csv $CMD > gpurun_out/ncu_list3.log 2>&1
-echo "list rc=$?"
-ncu --set full --clock-control none --import-source on -s 60 -c 40 -o gpurun_out/prof_step $CMD > gpurun_out/ncu_full3.log 2>&1
-echo "full rc=$?"
+#!/bin/bash
+# One graph-replayed T0 step under ncu --set full (11 launches): skips the bf16 cast and the eager warm-up step.
+cd "$(dirname "$0")/.."
+timeout 500 ncu --set full --clock-control none -k regex:"^(preprocess|gemm_kernel|linear_ce|reduce_partials|emb_bwd|wgrad_grouped|sgd_kernel|cast_bf16)" --launch-skip 12 -c 11 -o gpurun_out/r02_step -f python bench.py --steps 2 --warmup 3 --no-parity --no-cpu-baseline --sustain-seconds 0 > gpurun_out/r02_ncu_full.log 2>&1; echo rc=$? >> gpurun_out/r02_ncu_full.log

@@ -51,6 +51,7 @@ def test_additive_flags_default_to_reference_behaviour():
     assert a.precision == "fp32"            # the reference's nn.Linear arithmetic (task.py:309); bf16 / tf32 are opt-in
     a = parser.parse_args(["--dist-url=env://", "--multiprocessing-distributed", "--num_epochs=2"])  # notebook ARGS
     assert a.dist_url == "env://" and a.multiprocessing_distributed and a.num_epochs == 2
+    assert parser.parse_args(["--precision", "tf32"]).precision == "tf32"
     a = parser.parse_args(["--arch", "tabular_mlp_wide", "--weight-decay", "0.01", "-a", "tabular_mlp"])
     assert a.arch == "tabular_mlp" and a.weight_decay == 0.01
 

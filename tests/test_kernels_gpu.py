@@ -639,3 +639,42 @@ def test_linear_dgrad_emb_rejects_odd_embedding_width(ops):
                              torch.zeros(128, 4, dtype=torch.int32, device="cuda"),
                              torch.zeros(4 * 10 * 12, device="cuda"),
                              M=128, N=64, num_cat=4, table_rows=10, embed_dim=12)
+
+
+# ----------------------------------------------------------------------------- 3xTF32: fp32-grade linear layers
+def test_split_tf32_layouts_and_exactness(ops):
+    R, C = 300, 96
+    x = _rand((R, C + 8), torch.float32, 61)[:, :C]          # a strided view: ld > cols
+    kcat = torch.full((R, 3 * C), float("nan"), device="cuda")
+    rst = torch.full((3 * R, C), float("nan"), device="cuda")
+    ops.split_tf32(x, kcat, ops.SPLIT_LEFT, rst, ops.SPLIT_RIGHT, rows=R, cols=C)
+    torch.cuda.synchronize()
+    hi, lo = kcat[:, :C], kcat[:, 2 * C:]
+    assert torch.equal(kcat[:, C:2 * C], hi)                                  # (hi, hi, lo)
+    assert torch.equal(hi + lo, x)                                            # the split is exact
+    assert torch.count_nonzero(hi.view(torch.int32) & 0x1FFF).item() == 0     # hi is a tf32 number
+    assert (lo.abs() <= hi.abs() * 2.0 ** -11 + 1e-45).all()
+    assert torch.equal(rst[:R], hi) and torch.equal(rst[R:2 * R], lo) and torch.equal(rst[2 * R:], hi)   # (hi, lo, hi)
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 512, 448), (333, 1000, 512)])
+def test_three_pass_tf32_gemm_is_fp32_grade(ops, M, N, K):
+    """[X_hi | X_hi | X_lo] . [W_hi | W_lo | W_hi]^T through the ordinary TF32 forward kernel: error ~1e-6 of the
+    output scale, against ~1e-3 for the single pass."""
+    x = _rand((M, K), torch.float32, 62)
+    w = _rand((N, K), torch.float32, 63, 0.05)
+    xk = torch.empty(M, 3 * K, device="cuda")
+    wk = torch.empty(N, 3 * K, device="cuda")
+    ops.split_tf32(x, xk, ops.SPLIT_LEFT, None, 0, rows=M, cols=K)
+    ops.split_tf32(w, wk, ops.SPLIT_RIGHT, None, 0, rows=N, cols=K)
+    y3 = torch.empty(M, N, device="cuda")
+    y1 = torch.empty(M, N, device="cuda")
+    ops.linear_fwd(xk, wk, None, y3, M=M, N=N, K=3 * K, relu=False)
+    ops.linear_fwd(x, w, None, y1, M=M, N=N, K=K, relu=False)
+    torch.cuda.synchronize()
+    ref = x.double() @ w.double().t()
+    scale = ref.abs().max().item()
+    e3 = (y3.double() - ref).abs().max().item() / scale
+    e1 = (y1.double() - ref).abs().max().item() / scale
+    print(f"3xTF32 err {e3:.2e}, single TF32 err {e1:.2e}")
+    assert e3 <= 2e-6 and e1 > 20 * e3
