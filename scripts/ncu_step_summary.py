@@ -59,7 +59,7 @@ for i, r in enumerate(step):
     tot += us
     traffic[f"{i}:{seq[i]}"] = rd + wr
     out.append("| %d | %s | %.1f | %.1f | %.1f | %.1f | %.1f | %.1f | %d | %d | %d |" % (
-        i, seq[i], us, rd / 1e6, wr / 1e6, val(r, "dram__throughput.avg.pct_of_peak_sustained_elapsed"),
+        i, seq[i], us, rd / 1e6, wr / 1e6, val(r, "FBSP.TriageCompute.dram__throughput.avg.pct_of_peak_sustained_elapsed"),
         val(r, "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
         val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"), val(r, "launch__registers_per_thread"),
         val(r, "launch__grid_size"), val(r, "launch__cluster_size") if "launch__cluster_size" in ix else 0))
