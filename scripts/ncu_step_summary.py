@@ -50,7 +50,7 @@ for i, s in enumerate(seq):
 out, traffic = [], {}
 out.append(f"# One training step under `ncu --set full --clock-control none` ({workload}, 1 GPU, round {tag})\n")
 out.append("Per-launch figures, cold-ish caches and serialised by the profiler: compare shares, not absolutes.\n")
-out.append("| # | kernel | us | dram read MB | dram write MB | dram % | tensor pipe % | issue active % | regs | grid | cluster |")
+out.append("| # | kernel | us | dram read MB | dram write MB | dram % of 6.55 TB/s | tensor pipe % | issue active % | regs | grid | cluster |")
 out.append("|---|---|---|---|---|---|---|---|---|---|---|")
 tot = 0.0
 for i, r in enumerate(step):
@@ -59,7 +59,7 @@ for i, r in enumerate(step):
     tot += us
     traffic[f"{i}:{seq[i]}"] = rd + wr
     out.append("| %d | %s | %.1f | %.1f | %.1f | %.1f | %.1f | %.1f | %d | %d | %d |" % (
-        i, seq[i], us, rd / 1e6, wr / 1e6, val(r, "FBSP.TriageCompute.dram__throughput.avg.pct_of_peak_sustained_elapsed"),
+        i, seq[i], us, rd / 1e6, wr / 1e6, 100.0 * (rd + wr) / (us * 1e-6) / 6550.7e9,   # of the measured copy bandwidth (MEASURED_PEAKS.json)
         val(r, "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
         val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"), val(r, "launch__registers_per_thread"),
         val(r, "launch__grid_size"), val(r, "launch__cluster_size") if "launch__cluster_size" in ix else 0))
