@@ -462,7 +462,10 @@ def run_b200(args, rank, local_rank, world):
     traffic_tab = {}
     if os.path.exists(tpath):
         with open(tpath) as fh:
-            traffic_tab = json.load(fh).get(args.workload, {})
+            blob = json.load(fh)
+            # newest capture of this workload: keys "<workload>@<round>" -> {"<launch index>:<kernel>": DRAM bytes}
+            tags = sorted(k for k in blob if k.startswith(args.workload + "@"))
+            traffic_tab = blob[tags[-1]] if tags else {}
     gem = [r for r in prof if r["bound"] == "tensor"]
     mem = [r for r in prof if r["bound"] == "hbm"]
     gem_ms = sum(r["ms"] * r["per_step"] for r in gem)
@@ -477,17 +480,21 @@ def run_b200(args, rank, local_rank, world):
         tensor_peak = tf32_peak / passes
         peak_note = (f"TF32 peak measured in this run (torch.matmul 8192^3, best of 10): {tf32_peak:.1f} TFLOP/s"
                      + (" / 3 passes of the error-compensated product" if passes > 1 else ""))
-    gem_traffic = [traffic_tab.get(r["name"]) for r in gem]
+    # DRAM bytes (read + write, ncu --set full, scripts/ncu_step_summary.py) of the step's GEMM-type launches, per launch
+    gem_traffic = [v for k, v in traffic_tab.items()
+                   if k.split(":")[1] in ("gemm_kernel", "linear_ce_kernel", "wgrad_grouped_kernel")]
     roof_tensor = {"bound": "tensor", "kernel": "gemm_kernel (fwd + dgrad + wgrad launches of the step)",
                    "achieved": gem_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": gem_tflops / tensor_peak,
-                   "traffic": (sum(gem_traffic) / len(gem_traffic)) if gem_traffic and all(v is not None for v in gem_traffic) else None,
+                   "traffic": (sum(gem_traffic) / len(gem_traffic)) if gem_traffic else None,
+                   "traffic_note": "mean DRAM bytes per GEMM-type launch of one step (profiles/ncu_traffic.json)",
                    "share_of_step": gem_ms / total_ms, "share_of_step_ms": gem_ms / step_ms,
                    "kernel_ms": gem_ms, "flops_basis": "2*M*N*K on unpadded dims (SURVEY.md 8d)",
                    "launches_per_step": sum(r["per_step"] for r in gem),
                    "peak_source": peak_note}
     topm = max(mem, key=lambda r: r["ms"])
     roof_hbm = {"bound": "hbm", "kernel": topm["name"], "achieved": topm["gbs"], "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": topm["gbs"] / peaks["hbm_gbs"], "traffic": traffic_tab.get(topm["name"]),
+                "unit": "GB/s", "frac": topm["gbs"] / peaks["hbm_gbs"],
+                "traffic": next((v for k, v in traffic_tab.items() if topm["name"].split("[")[0] in k), None),
                 "share_of_step": topm["share"], "peak_source": peaks["source"] + " copy bandwidth"}
     roof = roof_tensor if gem_ms >= topm["ms"] * topm["per_step"] else roof_hbm
     flops = spec.flops_per_sample()["total"]
