@@ -9,6 +9,7 @@
 // (same version torch.distributed uses), so libb200step.so has no link-time NCCL dependency.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -28,6 +29,9 @@ struct NcclApi {
   ncclResult_t (*MemFree)(void*) = nullptr;
   ncclResult_t (*CommRegister)(const ncclComm_t, void*, size_t, void**) = nullptr;
   ncclResult_t (*CommDeregister)(const ncclComm_t, void*) = nullptr;
+  // symmetric-memory windows (NCCL >= 2.27): collectives on a window use NCCL's low-latency symmetric kernels
+  ncclResult_t (*CommWindowRegister)(ncclComm_t, void*, size_t, ncclWindow_t*, int) = nullptr;
+  ncclResult_t (*CommWindowDeregister)(ncclComm_t, ncclWindow_t) = nullptr;
 };
 
 static NcclApi g_nccl;
@@ -36,6 +40,8 @@ static int g_world = 0;
 constexpr int MAX_REG = 16;
 static void* g_reg_handles[MAX_REG];
 static int g_num_reg = 0;
+static ncclWindow_t g_windows[MAX_REG];
+static int g_num_win = 0;
 
 static int load_nccl() {
   if (g_nccl.handle) return 0;
@@ -59,6 +65,8 @@ static int load_nccl() {
   *reinterpret_cast<void**>(&g_nccl.MemFree) = dlsym(h, "ncclMemFree");
   *reinterpret_cast<void**>(&g_nccl.CommRegister) = dlsym(h, "ncclCommRegister");
   *reinterpret_cast<void**>(&g_nccl.CommDeregister) = dlsym(h, "ncclCommDeregister");
+  *reinterpret_cast<void**>(&g_nccl.CommWindowRegister) = dlsym(h, "ncclCommWindowRegister");
+  *reinterpret_cast<void**>(&g_nccl.CommWindowDeregister) = dlsym(h, "ncclCommWindowDeregister");
   g_nccl.handle = h;
   return 0;
 }
@@ -139,11 +147,23 @@ extern "C" int b200_comm_register(void* buf, int64_t bytes) {
   B200_REQUIRE(g_num_reg < MAX_REG, "too many registered buffers");
   B200_CHECK_NCCL(g_nccl.CommRegister(g_comm, buf, (size_t)bytes, &g_reg_handles[g_num_reg]));
   ++g_num_reg;
+  // Also as a symmetric window (a collective call: every rank registers its buffer of the same size, in the same
+  // order): small all-reduces — T0's gradient buckets are 1-2 MB — then take NCCL's symmetric low-latency path.
+  // B200STEP_NCCL_WINDOW=0 skips it; a library without the call, or a refusal, leaves the plain registration.
+  const char* e = getenv("B200STEP_NCCL_WINDOW");
+  if (g_nccl.CommWindowRegister != nullptr && !(e && e[0] == '0') && g_num_win < MAX_REG) {
+    ncclWindow_t win = nullptr;
+    if (g_nccl.CommWindowRegister(g_comm, buf, (size_t)bytes, &win, NCCL_WIN_COLL_SYMMETRIC) == ncclSuccess && win)
+      g_windows[g_num_win++] = win;
+  }
   return 0;
 }
 
 extern "C" int b200_comm_destroy(void) {
   if (g_comm) {
+    for (int i = 0; i < g_num_win; ++i)
+      if (g_nccl.CommWindowDeregister) g_nccl.CommWindowDeregister(g_comm, g_windows[i]);
+    g_num_win = 0;
     for (int i = 0; i < g_num_reg; ++i)
       if (g_nccl.CommDeregister) g_nccl.CommDeregister(g_comm, g_reg_handles[i]);
     g_num_reg = 0;
