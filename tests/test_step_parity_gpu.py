@@ -394,5 +394,12 @@ def test_fp32_precision_is_fp32_grade(optimizer):
             err = (so[k] - sg[k]).abs().max().item() / so[k].abs().max().clamp_min(1e-12).item()
             assert err <= 5e-4, (k, err)
     # and the single-pass path really is coarser on the same run (otherwise this test would prove nothing)
-    _, _, _, lo2, lg2 = _run_pair(spec, rows=8192, batch=4096, steps=2, precision="tf32", optimizer=optimizer, lr=lr)
-    assert max(abs(a - b) / max(1.0, abs(a)) for a, b in zip(lo2, lg2)) > worst
+    _, oracle2, eng2, lo2, lg2 = _run_pair(spec, rows=8192, batch=4096, steps=2, precision="tf32", optimizer=optimizer,
+                                           lr=lr)
+    rel2 = [abs(a - b) / max(1.0, abs(a)) for a, b in zip(lo2, lg2)]
+    print(f"tf32 (one pass) loss rel err over the same first 2 steps: {max(rel2):.2e} vs {max(rel[:2]):.2e}")
+    assert max(rel2) > max(rel[:2])          # same steps of the same run, before the trajectories drift
+    if optimizer == "sgd":                   # 2 one-pass steps leave the weights further off than 8 three-pass steps
+        p3, p1 = _param_err(oracle, eng), _param_err(oracle2, eng2)
+        print(f"parameter rel-L2: three-pass after 8 steps {p3:.2e}, one-pass after 2 steps {p1:.2e}")
+        assert p1 > p3
