@@ -53,6 +53,9 @@ int b200_set_sm_budget(int sms);
  *                                   ignored one. */
 #define B200_STATUS_BAD_CATEGORICAL_ID 1u
 #define B200_STATUS_BAD_LABEL 2u
+/*   B200_STATUS_BAD_ROW_INDEX       b200_image_augment met a sampler index outside [0, n_rows) (Dataset.__getitem__
+ *                                   raises IndexError): row 0 is read instead. */
+#define B200_STATUS_BAD_ROW_INDEX 4u
 int b200_set_status_word(uint32_t* device_word);
 
 /* ---- K-pre: fused batch load + standardise + categorical gather ---------------------------
@@ -268,6 +271,68 @@ int b200_graph_begin(b200_stream_t s);
 int b200_graph_end(b200_stream_t s, void** out_exec_host);
 int b200_graph_launch(void* exec, b200_stream_t s);
 int b200_graph_destroy(void* exec);
+
+/* ---- convolutional path: ResNet-18 on 3x32x32 images (task.py:171 `models.__dict__[args.arch]()`, task.py:247-257) ----
+ * Activations are NHWC = row-major [B*H*W, C] matrices, so every convolution is an im2col gather followed by the
+ * tcgen05 GEMMs above: conv fwd = b200_im2col + b200_linear_fwd (bias NULL); conv backward wrt input =
+ * b200_linear_dgrad + b200_col2im; wrt filter = b200_linear_wgrad(dy, col).  The filter is stored as
+ * Wg[Cout][ky][kx][c] with row stride ldcol (torch's OIHW permuted to O,H,W,I; columns past kh*kw*C are zero).
+ * All tensors: 16-byte aligned device pointers; `dtype` as above (storage type of activations). */
+
+/* K-aug: the reference's input pipeline for one batch (task.py:247-263): DistributedSampler order (row_idx, cursor as
+ * in b200_preprocess: sample b of the step is row_idx[cursor[0]*cursor_stride + b]; both nullable), then torchvision's
+ * RandomCrop(W, padding=pad) + RandomHorizontalFlip + ToTensor + Normalize(mean3, std3) (transforms.py:653,720):
+ * draws[p*4 + {0,1,2}] = {crop top, crop left, flip} for sample position p, drawn on the host (NULL: centre crop, no
+ * flip = the evaluation transform); images uint8 [n_rows, H, W, 3]; x_out [batch, H, W, 3] in `dtype`, bit-identical
+ * to torchvision in fp32; y_out[b] = labels[row] (nullable).  mean3 / std3 are HOST pointers, read during the call.
+ * A row index outside [0, n_rows) sets B200_STATUS_BAD_ROW_INDEX. */
+int b200_image_augment(const uint8_t* images, const int64_t* labels, const int64_t* row_idx, const int32_t* cursor,
+                       int64_t cursor_stride, const int8_t* draws, int64_t n_rows, const float* mean3,
+                       const float* std3, int pad, void* x_out, int64_t* y_out, int64_t batch, int H, int W,
+                       int dtype, b200_stream_t stream);
+/* col[m, (ky*kw+kx)*C + c] = x[b, ho*stride-pad+ky, wo*stride-pad+kx, c] (0 outside), m = (b*Ho+ho)*Wo+wo,
+ * Ho = (H+2*pad-kh)/stride+1; columns [kh*kw*C, ldcol) are zero-filled.  (F.conv2d's unfold, torch/nn/modules/conv.py) */
+int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, int H, int W, int C, int kh, int kw, int stride,
+                int pad, int dtype, b200_stream_t stream);
+/* The adjoint, as a gather: dx[b,h,w,c] = sum of the dcol entries that im2col filled from x[b,h,w,c], plus
+ * add[b,h,w,c] when add != NULL (the gradient arriving over a residual connection).  C % 4 == 0. */
+int b200_col2im(const void* dcol, int64_t ldcol, const void* add, void* dx, int64_t B, int H, int W, int C, int kh,
+                int kw, int stride, int pad, int dtype, b200_stream_t stream);
+
+/* nn.BatchNorm2d in training mode (torch/nn/modules/batchnorm.py; F.batch_norm with training=True) over y[M, C],
+ * M = B*H*W.  scratch: b200_bn_scratch_floats(C) floats that must be ZERO before the first use (each call leaves
+ * them ready for the next).  C = 4 * (a divisor of 256): 64, 128, 256, 512 ...
+ * _stats: mean[c], invstd[c] = 1/sqrt(biased var + eps); when running_mean != NULL also
+ *         running = (1-momentum)*running + momentum*{mean, unbiased var} and num_batches[0] += 1 (nullable).
+ *         Sums are folded in a fixed order (run-to-run deterministic).
+ * _apply: out = act((y - mean)*invstd*gamma + beta (+ res)), act = ReLU when relu != 0.  With the running statistics
+ *         passed as mean / invstd this is the eval-mode forward. */
+int64_t b200_bn_scratch_floats(int64_t C);
+int b200_bn_fwd_stats(const void* y, int64_t M, int64_t C, float eps, float momentum, float* mean, float* invstd,
+                      float* running_mean, float* running_var, int64_t* num_batches, float* scratch,
+                      int64_t scratch_floats, int dtype, b200_stream_t stream);
+int b200_bn_fwd_apply(const void* y, const void* res, void* out, int64_t M, int64_t C, const float* mean,
+                      const float* invstd, const float* gamma, const float* beta, int relu, int dtype,
+                      b200_stream_t stream);
+/* Backward of the same (task.py:311).  dz = dout * (out > 0) when out != NULL (the ReLU that followed), else dout.
+ * _reduce: dbeta[c] = sum_m dz, dgamma[c] = sum_m dz * xhat (fixed order);
+ * _apply:  dy = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M); dz_out (nullable) receives dz for the residual branch. */
+int b200_bn_bwd_reduce(const void* dout, const void* out, const void* y, int64_t M, int64_t C, const float* mean,
+                       const float* invstd, float* dgamma, float* dbeta, float* scratch, int64_t scratch_floats,
+                       int dtype, b200_stream_t stream);
+int b200_bn_bwd_apply(const void* dout, const void* out, const void* y, void* dy, void* dz_out, int64_t M, int64_t C,
+                      const float* mean, const float* invstd, const float* gamma, const float* dgamma,
+                      const float* dbeta, int dtype, b200_stream_t stream);
+
+/* nn.MaxPool2d(k, stride, pad) on NHWC; taps[m, c] (one byte per output element) records the winning window position
+ * (first maximum in row-major window order, NaN wins — aten's rule) for the backward gather. */
+int b200_maxpool_fwd(const void* x, void* out, uint8_t* taps, int64_t B, int H, int W, int C, int k, int stride,
+                     int pad, int dtype, b200_stream_t stream);
+int b200_maxpool_bwd(const void* dout, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
+                     int stride, int pad, int dtype, b200_stream_t stream);
+/* nn.AdaptiveAvgPool2d((1,1)) on NHWC: out[b, c] = mean over the HW pixels; bwd: dx[b, p, c] = dout[b, c] / HW */
+int b200_avgpool_fwd(const void* x, void* out, int64_t B, int HW, int C, int dtype, b200_stream_t stream);
+int b200_avgpool_bwd(const void* dout, void* dx, int64_t B, int HW, int C, int dtype, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

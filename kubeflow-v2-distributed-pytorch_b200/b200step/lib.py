@@ -54,6 +54,18 @@ SIGNATURES = {
     "b200_adam_step": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _d, _d, _d, _d, _d, _p, _i, _p, _p, C.c_int32, _p, _p]),
     "b200_split_tf32": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, _i, _p]),
     "b200_cast_bf16": (_i, [_p, _p, _i64, _p]),
+    "b200_image_augment": (_i, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p, _i, _p, _p, _i64, _i, _i, _i, _p]),
+    "b200_im2col": (_i, [_p, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_col2im": (_i, [_p, _i64, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_bn_scratch_floats": (_i64, [_i64]),
+    "b200_bn_fwd_stats": (_i, [_p, _i64, _i64, _f, _f, _p, _p, _p, _p, _p, _p, _i64, _i, _p]),
+    "b200_bn_fwd_apply": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _i, _i, _p]),
+    "b200_bn_bwd_reduce": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i64, _i, _p]),
+    "b200_bn_bwd_apply": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "b200_maxpool_fwd": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_maxpool_bwd": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_avgpool_fwd": (_i, [_p, _p, _i64, _i, _i, _i, _p]),
+    "b200_avgpool_bwd": (_i, [_p, _p, _i64, _i, _i, _i, _p]),
     "b200_zero": (_i, [_p, _i64, _p]),
     "b200_advance_step": (_i, [_p, _p, C.c_int32, _p]),
     "b200_comm_unique_id": (_i, [_p]),
@@ -81,7 +93,7 @@ SIGNATURES = {
 # functions whose int return value is NOT an error code
 _NO_CHECK = {"b200_last_error", "b200_abi_version", "b200_ce_scratch_floats", "b200_colsum_scratch_floats",
              "b200_linear_ce_scratch_floats",
-             "b200_dgrad_scratch_floats"}
+             "b200_dgrad_scratch_floats", "b200_bn_scratch_floats"}
 
 
 class B200Error(RuntimeError):

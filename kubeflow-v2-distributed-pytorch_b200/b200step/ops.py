@@ -224,3 +224,86 @@ def set_sm_budget(sms: int) -> None:
 def zero(t, stream=None):
     _cuda(t)
     get_lib().zero(ptr(t), t.numel() * t.element_size(), _stream(stream))
+
+
+# ---- convolutional path (include/b200step.h: "convolutional path") ---------------------------------------------
+STATUS_BAD_ROW_INDEX = 4
+
+
+def conv_out_size(n: int, k: int, stride: int, pad: int) -> int:
+    return (n + 2 * pad - k) // stride + 1
+
+
+def image_augment(images, labels, row_idx, cursor, draws, mean3, std3, x_out, y_out, *, batch: int, H: int, W: int,
+                  pad: int = 4, cursor_stride: int = 0, stream=None):
+    """mean3 / std3: CPU float32 tensors of 3 elements (read during the call)."""
+    _cuda(images, labels, row_idx, draws, x_out, y_out)
+    get_lib().image_augment(ptr(images), ptr(labels), ptr(row_idx), ptr(cursor), int(cursor_stride), ptr(draws),
+                            images.shape[0], ptr(mean3), ptr(std3), int(pad), ptr(x_out), ptr(y_out), batch, H, W,
+                            dtype_code(x_out.dtype), _stream(stream))
+
+
+def im2col(x, col, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, stream=None):
+    _cuda(x, col)
+    get_lib().im2col(ptr(x), ptr(col), col.stride(0), B, H, W, C, kh, kw, stride, pad, dtype_code(x.dtype),
+                     _stream(stream))
+
+
+def col2im(dcol, add, dx, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, stream=None):
+    _cuda(dcol, add, dx)
+    get_lib().col2im(ptr(dcol), dcol.stride(0), ptr(add), ptr(dx), B, H, W, C, kh, kw, stride, pad,
+                     dtype_code(dx.dtype), _stream(stream))
+
+
+def bn_scratch_floats(C: int) -> int:
+    return int(get_lib().bn_scratch_floats(C))
+
+
+def bn_fwd_stats(y, mean, invstd, running_mean, running_var, num_batches, scratch, *, M: int, C: int,
+                 eps: float = 1e-5, momentum: float = 0.1, stream=None):
+    _cuda(y, mean, invstd, running_mean, running_var, num_batches, scratch)
+    get_lib().bn_fwd_stats(ptr(y), M, C, float(eps), float(momentum), ptr(mean), ptr(invstd), ptr(running_mean),
+                           ptr(running_var), ptr(num_batches), ptr(scratch), scratch.numel(), dtype_code(y.dtype),
+                           _stream(stream))
+
+
+def bn_fwd_apply(y, res, out, mean, invstd, gamma, beta, *, M: int, C: int, relu: bool, stream=None):
+    _cuda(y, res, out, mean, invstd, gamma, beta)
+    get_lib().bn_fwd_apply(ptr(y), ptr(res), ptr(out), M, C, ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+                           int(relu), dtype_code(y.dtype), _stream(stream))
+
+
+def bn_bwd_reduce(dout, out, y, mean, invstd, dgamma, dbeta, scratch, *, M: int, C: int, stream=None):
+    _cuda(dout, out, y, mean, invstd, dgamma, dbeta, scratch)
+    get_lib().bn_bwd_reduce(ptr(dout), ptr(out), ptr(y), M, C, ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta),
+                            ptr(scratch), scratch.numel(), dtype_code(y.dtype), _stream(stream))
+
+
+def bn_bwd_apply(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, *, M: int, C: int, stream=None):
+    _cuda(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta)
+    get_lib().bn_bwd_apply(ptr(dout), ptr(out), ptr(y), ptr(dy), ptr(dz_out), M, C, ptr(mean), ptr(invstd),
+                           ptr(gamma), ptr(dgamma), ptr(dbeta), dtype_code(y.dtype), _stream(stream))
+
+
+def maxpool_fwd(x, out, taps, *, B: int, H: int, W: int, C: int, k: int = 3, stride: int = 2, pad: int = 1,
+                stream=None):
+    _cuda(x, out, taps)
+    get_lib().maxpool_fwd(ptr(x), ptr(out), ptr(taps), B, H, W, C, k, stride, pad, dtype_code(x.dtype),
+                          _stream(stream))
+
+
+def maxpool_bwd(dout, taps, dx, *, B: int, H: int, W: int, C: int, k: int = 3, stride: int = 2, pad: int = 1,
+                stream=None):
+    _cuda(dout, taps, dx)
+    get_lib().maxpool_bwd(ptr(dout), ptr(taps), ptr(dx), B, H, W, C, k, stride, pad, dtype_code(dx.dtype),
+                          _stream(stream))
+
+
+def avgpool_fwd(x, out, *, B: int, HW: int, C: int, stream=None):
+    _cuda(x, out)
+    get_lib().avgpool_fwd(ptr(x), ptr(out), B, HW, C, dtype_code(x.dtype), _stream(stream))
+
+
+def avgpool_bwd(dout, dx, *, B: int, HW: int, C: int, stream=None):
+    _cuda(dout, dx)
+    get_lib().avgpool_bwd(ptr(dout), ptr(dx), B, HW, C, dtype_code(dx.dtype), _stream(stream))

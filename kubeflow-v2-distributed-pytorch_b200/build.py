@@ -21,7 +21,7 @@ CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libb200step.so")
-SOURCES = ["abi.cu", "preprocess.cu", "gemm_tcgen05.cu", "gemm_ce.cu", "loss.cu", "optim.cu", "comm.cu"]
+SOURCES = ["abi.cu", "preprocess.cu", "gemm_tcgen05.cu", "gemm_ce.cu", "loss.cu", "optim.cu", "comm.cu", "conv.cu"]
 
 
 def _nccl_include() -> str:

@@ -1,0 +1,689 @@
+// conv.cu — the memory-bound kernels of the convolutional path (ResNet-18 on 3x32x32, task.py:171,247-257).
+//
+// Layout: activations are NHWC, i.e. a row-major matrix [B*H*W, C] — exactly what the tcgen05 GEMMs of
+// gemm_tcgen05.cu read and write, so a convolution is
+//     im2col (this file)  ->  b200_linear_fwd   (col[M, kh*kw*C] . Wg[Cout, kh*kw*C]^T, no bias)
+//     b200_linear_dgrad   ->  col2im (this file, gather form: deterministic, no atomics)
+//     b200_linear_wgrad   (dY^T . col, fp32 into the flat gradient buffer)
+// with the filter stored as Wg[Cout][ky][kx][c] (the permutation of torch's OIHW that makes a patch contiguous).
+// BatchNorm2d in training mode (batch statistics, running-stat update, torch/nn/modules/batchnorm.py) is two passes
+// over the GEMM output: statistics (fixed-order partials, last block finalises) and apply (+residual, +ReLU).
+// Every kernel here is HBM-bound: 8- or 16-byte vectors of 4 channels per thread, coalesced along C.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+
+// ---- 4-channel vector access for both storage types ------------------------------------------------------------
+template <typename T> struct Vec4;
+template <> struct Vec4<float> {
+  static __device__ __forceinline__ float4 load(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  static __device__ __forceinline__ void store(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+};
+template <> struct Vec4<__nv_bfloat16> {
+  static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
+    const uint2 r = *reinterpret_cast<const uint2*>(p);
+    return make_float4(bf16_lo(r.x), bf16_hi(r.x), bf16_lo(r.y), bf16_hi(r.y));
+  }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, float4 v) {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+};
+template <typename T> __device__ __forceinline__ T from_float(float v);
+template <> __device__ __forceinline__ float from_float<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <typename T> __device__ __forceinline__ float to_float(T v);
+template <> __device__ __forceinline__ float to_float<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_float<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+static inline int grid_for(int64_t work_items, int threads, int per_sm = 8) {
+  const int64_t blocks = (work_items + threads - 1) / threads;
+  const int64_t cap = (int64_t)sm_count() * per_sm;
+  return (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+// ---- K-aug: RandomCrop(32, padding=4) + RandomHorizontalFlip + ToTensor + Normalize (task.py:250-255) -----------
+// One thread per output pixel.  draws[p] = {top, left, flip, -}: the three numbers torchvision draws per sample
+// (transforms.py RandomCrop.get_params: randint(0, 9) twice; RandomHorizontalFlip: rand(1) < 0.5), drawn on the host
+// with torch's generator in the same order.  Arithmetic is ToTensor's u8 -> fp32 `/255` and Normalize's
+// `(x - mean) / std`, each correctly rounded (no FMA contraction), so the fp32 result is bit-identical to torchvision.
+template <typename T>
+__global__ void __launch_bounds__(256)
+augment_kernel(const uint8_t* __restrict__ images, const int64_t* __restrict__ labels, const int64_t* __restrict__ row_idx,
+               const int32_t* __restrict__ cursor, int64_t cursor_stride, const int8_t* __restrict__ draws,
+               int64_t n_rows, float m0, float m1, float m2, float s0, float s1, float s2, int pad,
+               T* __restrict__ x, int64_t* __restrict__ y, int B, int H, int W, uint32_t* status) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int64_t base = cursor != nullptr ? (int64_t)cursor[0] * cursor_stride : 0;
+  const int64_t total = (int64_t)B * H * W;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int w = (int)(t % W), h = (int)((t / W) % H);
+    const int64_t b = t / ((int64_t)W * H);
+    const int64_t pos = base + b;
+    int64_t r = row_idx != nullptr ? row_idx[pos] : pos;
+    if (r < 0 || r >= n_rows) { flag_status(status, B200_STATUS_BAD_ROW_INDEX); r = 0; }
+    const int top = draws != nullptr ? draws[pos * 4 + 0] : pad;
+    const int left = draws != nullptr ? draws[pos * 4 + 1] : pad;
+    const int flip = draws != nullptr ? draws[pos * 4 + 2] : 0;
+    // output pixel (h, w) of the flipped crop = pixel (top + h, left + (flip ? W-1-w : w)) of the padded image
+    const int sh = top + h - pad, sw = left + (flip ? W - 1 - w : w) - pad;
+    float p0 = 0.f, p1 = 0.f, p2 = 0.f;     // RandomCrop pads with fill = 0 BEFORE ToTensor / Normalize
+    if (sh >= 0 && sh < H && sw >= 0 && sw < W) {
+      const uint8_t* px = images + ((r * H + sh) * (int64_t)W + sw) * 3;
+      p0 = __fdiv_rn((float)px[0], 255.f); p1 = __fdiv_rn((float)px[1], 255.f); p2 = __fdiv_rn((float)px[2], 255.f);
+    }
+    T* o = x + t * 3;
+    o[0] = from_float<T>(__fdiv_rn(__fsub_rn(p0, m0), s0));
+    o[1] = from_float<T>(__fdiv_rn(__fsub_rn(p1, m1), s1));
+    o[2] = from_float<T>(__fdiv_rn(__fsub_rn(p2, m2), s2));
+    if (h == 0 && w == 0 && y != nullptr) y[b] = labels[r];
+  }
+}
+
+// ---- im2col ------------------------------------------------------------------------------------------------------
+// col[m, (ky*kw + kx)*C + c] = x[b, ho*stride - pad + ky, wo*stride - pad + kx, c]   (0 outside the image),
+// m = (b*Ho + ho)*Wo + wo; columns [kh*kw*C, ldcol) are zero-filled (the GEMM's K padding).
+// VEC = 4: one thread moves 4 channels (C % 4 == 0); VEC = 1: scalar (the 3-channel input of conv1).
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256)
+im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W, int C, int Ho, int Wo, int kh, int kw,
+              int stride, int pad, int64_t ldcol, int kcols) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int K = kh * kw * C;
+  const int vrow = kcols / VEC;                       // vectors per col row (padding included)
+  const int64_t total = (int64_t)B * Ho * Wo * vrow;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(t % vrow) * VEC;
+    const int64_t m = t / vrow;
+    const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho);
+    const int64_t b = m / ((int64_t)Wo * Ho);
+    T* dst = col + m * ldcol + k;
+    bool inside = false;
+    const T* src = nullptr;
+    if (k < K) {
+      const int tap = k / C, c = k - tap * C;
+      const int ky = tap / kw, kx = tap - ky * kw;
+      const int h = ho * stride - pad + ky, w = wo * stride - pad + kx;
+      inside = h >= 0 && h < H && w >= 0 && w < W;
+      src = x + ((b * H + h) * (int64_t)W + w) * C + c;
+    }
+    if (VEC == 4) {
+      if (sizeof(T) == 4) {
+        *reinterpret_cast<float4*>(dst) = inside ? *reinterpret_cast<const float4*>(src) : make_float4(0, 0, 0, 0);
+      } else {
+        *reinterpret_cast<uint2*>(dst) = inside ? *reinterpret_cast<const uint2*>(src) : make_uint2(0, 0);
+      }
+    } else {
+      *dst = inside ? *src : from_float<T>(0.f);
+    }
+  }
+}
+
+// ---- col2im (gather form) -------------------------------------------------------------------------------------------
+// dx[b,h,w,c] = sum over taps (ky,kx) with (h + pad - ky) = ho*stride, (w + pad - kx) = wo*stride in range of
+//               dcol[(b,ho,wo), (ky*kw+kx)*C + c]   (+ add[b,h,w,c] when `add` is given: the residual branch's gradient)
+// Every dcol element is read exactly once; sums are taken in tap order in fp32.
+template <typename T>
+__global__ void __launch_bounds__(256)
+col2im_kernel(const T* __restrict__ dcol, int64_t ldcol, const T* __restrict__ add, T* __restrict__ dx, int B, int H,
+              int W, int C, int Ho, int Wo, int kh, int kw, int stride, int pad) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = (int64_t)B * H * W * vc;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t pix = t / vc;
+    const int w = (int)(pix % W), h = (int)((pix / W) % H);
+    const int64_t b = pix / ((int64_t)W * H);
+    float4 acc = add != nullptr ? Vec4<T>::load(add + pix * C + c) : make_float4(0, 0, 0, 0);
+    for (int ky = 0; ky < kh; ++ky) {
+      const int hn = h + pad - ky;
+      if (hn < 0 || hn % stride != 0) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int kx = 0; kx < kw; ++kx) {
+        const int wn = w + pad - kx;
+        if (wn < 0 || wn % stride != 0) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const int64_t m = (b * Ho + ho) * (int64_t)Wo + wo;
+        const float4 v = Vec4<T>::load(dcol + m * ldcol + (int64_t)(ky * kw + kx) * C + c);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+    Vec4<T>::store(dx + pix * C + c, acc);
+  }
+}
+
+// ---- BatchNorm2d, training mode ------------------------------------------------------------------------------------
+// Column statistics of y[M, C] (M = B*H*W).  256 threads = (C/4 channel vectors) x (rows in flight); block j owns a
+// contiguous row range, reduces it in registers, then across its row lanes in shared memory in a fixed order, and
+// writes one partial row.  The last block to finish (ticket) folds the partial rows IN ORDER in fp64, so the result does
+// not depend on scheduling.  `Fin` turns the two column sums into the kernel's outputs.
+constexpr int BN_THREADS = 256;
+constexpr int BN_MAX_C = 512;
+
+template <typename Acc>
+__device__ __forceinline__ void bn_block_reduce(Acc a, Acc b, int vc, float* partial_row, int C) {
+  // a, b: this thread's two float4 column sums for channel vector (tid % vc)
+  __shared__ float4 sh[2][BN_THREADS];
+  const int tid = threadIdx.x;
+  sh[0][tid] = a;
+  sh[1][tid] = b;
+  __syncthreads();
+  if (tid < vc) {
+    float4 s0 = sh[0][tid], s1 = sh[1][tid];
+    for (int r = tid + vc; r < BN_THREADS; r += vc) {
+      const float4 u = sh[0][r], v = sh[1][r];
+      s0.x += u.x; s0.y += u.y; s0.z += u.z; s0.w += u.w;
+      s1.x += v.x; s1.y += v.y; s1.z += v.z; s1.w += v.w;
+    }
+    *reinterpret_cast<float4*>(partial_row + tid * 4) = s0;
+    *reinterpret_cast<float4*>(partial_row + C + tid * 4) = s1;
+  }
+}
+
+// true in exactly one block: the one that arrives last (all partial rows are then visible to it)
+__device__ __forceinline__ bool bn_last_block(uint32_t* ticket) {
+  __shared__ uint32_t s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *ticket = 0;                 // ready for the next launch (graph replay)
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_stats_kernel(const T* __restrict__ y, int64_t M, int C, float* __restrict__ partials, uint32_t* ticket, float eps,
+                float momentum, float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ running_mean,
+                float* __restrict__ running_var, int64_t* __restrict__ num_batches) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4, lanes = BN_THREADS / vc;
+  const int cv = threadIdx.x % vc, ry = threadIdx.x / vc;
+  const int64_t chunk = (M + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = blockIdx.x * chunk, r1 = min(M, r0 + chunk);
+  float4 s = make_float4(0, 0, 0, 0), q = make_float4(0, 0, 0, 0);
+  if (ry < lanes)
+    for (int64_t r = r0 + ry; r < r1; r += lanes) {
+      const float4 v = Vec4<T>::load(y + r * C + cv * 4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      q.x = fmaf(v.x, v.x, q.x); q.y = fmaf(v.y, v.y, q.y); q.z = fmaf(v.z, v.z, q.z); q.w = fmaf(v.w, v.w, q.w);
+    }
+  bn_block_reduce(s, q, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
+  if (!bn_last_block(ticket)) return;
+  for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+    double ds = 0.0, dq = 0.0;
+    for (int j = 0; j < (int)gridDim.x; ++j) {
+      ds += (double)partials[(int64_t)j * 2 * C + c];
+      dq += (double)partials[(int64_t)j * 2 * C + C + c];
+    }
+    const double mu = ds / (double)M;
+    double var = dq / (double)M - mu * mu;             // biased: what normalises the batch
+    if (var < 0.0) var = 0.0;
+    mean[c] = (float)mu;
+    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean != nullptr) {                       // batchnorm.py: running = (1 - momentum)*running + momentum*new,
+      const double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;   // with the UNBIASED variance
+      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mu);
+      running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+    }
+  }
+  if (threadIdx.x == 0 && num_batches != nullptr) num_batches[0] += 1;
+}
+
+// out = act(y*scale + shift (+ res)),  scale = gamma*invstd, shift = beta - mean*scale
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const T* __restrict__ y, const T* __restrict__ res, T* __restrict__ out, int64_t M, int C,
+                const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                const float* __restrict__ beta, int relu) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = M * vc;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t off = (t / vc) * C + c;
+    const float4 mu = *reinterpret_cast<const float4*>(mean + c), is = *reinterpret_cast<const float4*>(invstd + c);
+    const float4 g = *reinterpret_cast<const float4*>(gamma + c), be = *reinterpret_cast<const float4*>(beta + c);
+    const float4 v = Vec4<T>::load(y + off);
+    float4 o;
+    o.x = fmaf((v.x - mu.x) * is.x, g.x, be.x); o.y = fmaf((v.y - mu.y) * is.y, g.y, be.y);
+    o.z = fmaf((v.z - mu.z) * is.z, g.z, be.z); o.w = fmaf((v.w - mu.w) * is.w, g.w, be.w);
+    if (res != nullptr) {
+      const float4 r = Vec4<T>::load(res + off);
+      o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+    }
+    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+    Vec4<T>::store(out + off, o);
+  }
+}
+
+// backward, pass 1: dbeta[c] = sum_m dz, dgamma[c] = sum_m dz * xhat,  dz = dout * (out > 0) when `out` is given
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, const T* __restrict__ y, int64_t M, int C,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ partials,
+                     uint32_t* ticket, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4, lanes = BN_THREADS / vc;
+  const int cv = threadIdx.x % vc, ry = threadIdx.x / vc;
+  const int64_t chunk = (M + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = blockIdx.x * chunk, r1 = min(M, r0 + chunk);
+  const float4 mu = *reinterpret_cast<const float4*>(mean + cv * 4), is = *reinterpret_cast<const float4*>(invstd + cv * 4);
+  float4 sb = make_float4(0, 0, 0, 0), sg = make_float4(0, 0, 0, 0);
+  if (ry < lanes)
+    for (int64_t r = r0 + ry; r < r1; r += lanes) {
+      const int64_t off = r * C + cv * 4;
+      float4 d = Vec4<T>::load(dout + off);
+      if (out != nullptr) {
+        const float4 o = Vec4<T>::load(out + off);
+        d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
+      }
+      const float4 v = Vec4<T>::load(y + off);
+      sb.x += d.x; sb.y += d.y; sb.z += d.z; sb.w += d.w;
+      sg.x = fmaf(d.x, (v.x - mu.x) * is.x, sg.x); sg.y = fmaf(d.y, (v.y - mu.y) * is.y, sg.y);
+      sg.z = fmaf(d.z, (v.z - mu.z) * is.z, sg.z); sg.w = fmaf(d.w, (v.w - mu.w) * is.w, sg.w);
+    }
+  bn_block_reduce(sb, sg, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
+  if (!bn_last_block(ticket)) return;
+  for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+    double db = 0.0, dg = 0.0;
+    for (int j = 0; j < (int)gridDim.x; ++j) {
+      db += (double)partials[(int64_t)j * 2 * C + c];
+      dg += (double)partials[(int64_t)j * 2 * C + C + c];
+    }
+    dbeta[c] = (float)db;
+    dgamma[c] = (float)dg;
+  }
+}
+
+// backward, pass 2: dy = gamma*invstd * (dz - dbeta/M - xhat*dgamma/M);  dz_out (nullable) = dz for the residual branch
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ out, const T* __restrict__ y, T* __restrict__ dy,
+                    T* __restrict__ dz_out, int64_t M, int C, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ dgamma,
+                    const float* __restrict__ dbeta) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = M * vc;
+  const float inv_m = 1.f / (float)M;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t off = (t / vc) * C + c;
+    const float4 mu = *reinterpret_cast<const float4*>(mean + c), is = *reinterpret_cast<const float4*>(invstd + c);
+    const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+    const float4 dg = *reinterpret_cast<const float4*>(dgamma + c), db = *reinterpret_cast<const float4*>(dbeta + c);
+    float4 d = Vec4<T>::load(dout + off);
+    if (out != nullptr) {
+      const float4 o = Vec4<T>::load(out + off);
+      d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
+    }
+    if (dz_out != nullptr) Vec4<T>::store(dz_out + off, d);
+    const float4 v = Vec4<T>::load(y + off);
+    float4 r;
+    r.x = g.x * is.x * (d.x - db.x * inv_m - (v.x - mu.x) * is.x * dg.x * inv_m);
+    r.y = g.y * is.y * (d.y - db.y * inv_m - (v.y - mu.y) * is.y * dg.y * inv_m);
+    r.z = g.z * is.z * (d.z - db.z * inv_m - (v.z - mu.z) * is.z * dg.z * inv_m);
+    r.w = g.w * is.w * (d.w - db.w * inv_m - (v.w - mu.w) * is.w * dg.w * inv_m);
+    Vec4<T>::store(dy + off, r);
+  }
+}
+
+// ---- MaxPool2d(kernel 3, stride 2, padding 1) (torchvision resnet.py: self.maxpool) ------------------------------------
+// fwd keeps the winning tap (first maximum in (ky, kx) order, NaN wins: aten's `val > max || isnan(val)`) as one byte
+// per output element; bwd is the gather over the <= 4 windows that contain an input pixel.
+template <typename T>
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ out, uint8_t* __restrict__ tap_out, int B, int H, int W,
+                   int C, int Ho, int Wo, int k, int stride, int pad) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = (int64_t)B * Ho * Wo * vc;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t m = t / vc;
+    const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho);
+    const int64_t b = m / ((int64_t)Wo * Ho);
+    float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    int tap[4] = {255, 255, 255, 255};
+    for (int ky = 0; ky < k; ++ky) {
+      const int h = ho * stride - pad + ky;
+      if (h < 0 || h >= H) continue;
+      for (int kx = 0; kx < k; ++kx) {
+        const int w = wo * stride - pad + kx;
+        if (w < 0 || w >= W) continue;
+        const float4 v4 = Vec4<T>::load(x + ((b * H + h) * (int64_t)W + w) * C + c);
+        const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (tap[j] == 255 || v[j] > best[j] || v[j] != v[j]) { best[j] = v[j]; tap[j] = ky * k + kx; }
+      }
+    }
+    Vec4<T>::store(out + m * C + c, make_float4(best[0], best[1], best[2], best[3]));
+    *reinterpret_cast<uchar4*>(tap_out + m * C + c) = make_uchar4(tap[0], tap[1], tap[2], tap[3]);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const T* __restrict__ dout, const uint8_t* __restrict__ tap_in, T* __restrict__ dx, int B, int H, int W,
+                   int C, int Ho, int Wo, int k, int stride, int pad) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = (int64_t)B * H * W * vc;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t pix = t / vc;
+    const int w = (int)(pix % W), h = (int)((pix / W) % H);
+    const int64_t b = pix / ((int64_t)W * H);
+    float4 acc = make_float4(0, 0, 0, 0);
+    for (int ky = 0; ky < k; ++ky) {
+      const int hn = h + pad - ky;
+      if (hn < 0 || hn % stride != 0 || hn / stride >= Ho) continue;
+      for (int kx = 0; kx < k; ++kx) {
+        const int wn = w + pad - kx;
+        if (wn < 0 || wn % stride != 0 || wn / stride >= Wo) continue;
+        const int64_t m = (b * Ho + hn / stride) * (int64_t)Wo + wn / stride;
+        const uchar4 tp = *reinterpret_cast<const uchar4*>(tap_in + m * C + c);
+        const float4 d = Vec4<T>::load(dout + m * C + c);
+        const int me = ky * k + kx;
+        if (tp.x == me) acc.x += d.x;
+        if (tp.y == me) acc.y += d.y;
+        if (tp.z == me) acc.z += d.z;
+        if (tp.w == me) acc.w += d.w;
+      }
+    }
+    Vec4<T>::store(dx + pix * C + c, acc);
+  }
+}
+
+// ---- AdaptiveAvgPool2d((1,1)): out[b, c] = mean over the HW pixels; bwd spreads dout / HW --------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ out, int B, int HW, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = (int64_t)B * vc;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t b = t / vc;
+    float4 s = make_float4(0, 0, 0, 0);
+    for (int p = 0; p < HW; ++p) {
+      const float4 v = Vec4<T>::load(x + (b * HW + p) * C + c);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    const float inv = 1.f / (float)HW;
+    Vec4<T>::store(out + b * C + c, make_float4(s.x * inv, s.y * inv, s.z * inv, s.w * inv));
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+avgpool_bwd_kernel(const T* __restrict__ dout, T* __restrict__ dx, int B, int HW, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4;
+  const int64_t total = (int64_t)B * HW * vc;
+  const float inv = 1.f / (float)HW;
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t % vc) * 4;
+    const int64_t pix = t / vc;
+    const float4 d = Vec4<T>::load(dout + (pix / HW) * C + c);
+    Vec4<T>::store(dx + pix * C + c, make_float4(d.x * inv, d.y * inv, d.z * inv, d.w * inv));
+  }
+}
+
+}  // namespace b200
+
+// ---- C ABI ----------------------------------------------------------------------------------------------------------
+using namespace b200;
+typedef __nv_bfloat16 bf16_t;
+
+#define CONV_COMMON(name, ptr_ok)                                                                              \
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, name ": unknown dtype code %d", dtype);                \
+  B200_REQUIRE(ptr_ok, name ": NULL or misaligned (16 bytes) tensor pointer");                                 \
+  cudaStream_t st = static_cast<cudaStream_t>(stream)
+#define ALIGNED16(p) ((p) != nullptr && (reinterpret_cast<uintptr_t>(p) & 15) == 0)
+#define ALIGNED16_OR_NULL(p) ((reinterpret_cast<uintptr_t>(p) & 15) == 0)
+static inline int conv_out(int in, int k, int stride, int pad) { return (in + 2 * pad - k) / stride + 1; }
+
+extern "C" int b200_image_augment(const uint8_t* images, const int64_t* labels, const int64_t* row_idx,
+                                  const int32_t* cursor, int64_t cursor_stride, const int8_t* draws, int64_t n_rows,
+                                  const float* mean3, const float* std3, int pad, void* x_out, int64_t* y_out,
+                                  int64_t batch, int H, int W, int dtype, b200_stream_t stream) {
+  CONV_COMMON("image_augment", images != nullptr && x_out != nullptr && mean3 != nullptr && std3 != nullptr);
+  B200_REQUIRE(batch > 0 && H > 0 && W > 0 && n_rows > 0 && batch * H * W < (1ll << 31) && pad >= 0 && pad < 64,
+               "image_augment: bad sizes (batch=%lld H=%d W=%d rows=%lld pad=%d)", (long long)batch, H, W,
+               (long long)n_rows, pad);
+  B200_REQUIRE(y_out == nullptr || labels != nullptr, "image_augment: y_out without labels");
+  const int grid = grid_for(batch * H * W, 256);
+  const void* xo = x_out;
+  if (dtype == B200_BF16)
+    B200_CHECK_CUDA(launch_pdl(augment_kernel<bf16_t>, dim3(grid), dim3(256), 0, st, images, labels, row_idx, cursor,
+                               cursor_stride, draws, n_rows, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2],
+                               pad, (bf16_t*)xo, y_out, (int)batch, H, W, status_word()));
+  else
+    B200_CHECK_CUDA(launch_pdl(augment_kernel<float>, dim3(grid), dim3(256), 0, st, images, labels, row_idx, cursor,
+                               cursor_stride, draws, n_rows, mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2],
+                               pad, (float*)xo, y_out, (int)batch, H, W, status_word()));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, int H, int W, int C, int kh, int kw,
+                           int stride, int pad, int dtype, b200_stream_t stream) {
+  CONV_COMMON("im2col", ALIGNED16(col) && x != nullptr);
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && C > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0 && kh <= H + 2 * pad &&
+                   kw <= W + 2 * pad, "im2col: bad geometry");
+  const int Ho = conv_out(H, kh, stride, pad), Wo = conv_out(W, kw, stride, pad);
+  const int K = kh * kw * C;
+  const int es = dtype == B200_F32 ? 4 : 2;
+  B200_REQUIRE(ldcol >= K && (ldcol * es) % 16 == 0, "im2col: ldcol=%lld must be >= %d and a multiple of 16 bytes",
+               (long long)ldcol, K);
+  B200_REQUIRE(B * Ho * Wo * ldcol < (1ll << 40), "im2col: col matrix too large");
+  const bool vec = C % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  const int64_t items = B * Ho * Wo * (vec ? ldcol / 4 : ldcol);
+  const int grid = grid_for(items, 256, 16);
+  const int kcols = (int)ldcol;
+  if (dtype == B200_BF16) {
+    if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 4>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+    else B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 1>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+  } else {
+    if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 4>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+    else B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 1>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_col2im(const void* dcol, int64_t ldcol, const void* add, void* dx, int64_t B, int H, int W, int C,
+                           int kh, int kw, int stride, int pad, int dtype, b200_stream_t stream) {
+  CONV_COMMON("col2im", ALIGNED16(dcol) && ALIGNED16(dx) && ALIGNED16_OR_NULL(add));
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && C > 0 && C % 4 == 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0,
+               "col2im: bad geometry (C must be a multiple of 4)");
+  const int es = dtype == B200_F32 ? 4 : 2;
+  B200_REQUIRE(ldcol >= (int64_t)kh * kw * C && (ldcol * es) % 16 == 0, "col2im: bad ldcol=%lld", (long long)ldcol);
+  const int Ho = conv_out(H, kh, stride, pad), Wo = conv_out(W, kw, stride, pad);
+  const int grid = grid_for(B * H * W * (C / 4), 256, 16);
+  if (dtype == B200_BF16)
+    B200_CHECK_CUDA(launch_pdl(col2im_kernel<bf16_t>, dim3(grid), dim3(256), 0, st, (const bf16_t*)dcol, ldcol, (const bf16_t*)add, (bf16_t*)dx, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad));
+  else
+    B200_CHECK_CUDA(launch_pdl(col2im_kernel<float>, dim3(grid), dim3(256), 0, st, (const float*)dcol, ldcol, (const float*)add, (float*)dx, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- BatchNorm entry points ---------------------------------------------------------------------------------------
+constexpr int BN_MAX_BLOCKS = 296;                   // two row blocks per SM
+constexpr int BN_SCRATCH_HEAD = 4;                   // floats in front of the partial rows: the ticket word + padding
+
+extern "C" int64_t b200_bn_scratch_floats(int64_t C) { return BN_SCRATCH_HEAD + (int64_t)BN_MAX_BLOCKS * 2 * C; }
+
+static int bn_check(const char* who, int64_t M, int64_t C, const float* scratch, int64_t scratch_floats) {
+  B200_REQUIRE(M > 0 && M < (1ll << 40) && C >= 4 && C <= 1024 && C % 4 == 0 && BN_THREADS % (C / 4) == 0,
+               "%s: C=%lld must be 4 * (a divisor of 256), M=%lld positive", who, (long long)C, (long long)M);
+  B200_REQUIRE(scratch == nullptr || (ALIGNED16(scratch) && scratch_floats >= b200_bn_scratch_floats(C)),
+               "%s: scratch must be 16-byte aligned and hold b200_bn_scratch_floats(C) = %lld floats", who,
+               (long long)b200_bn_scratch_floats(C));
+  return 0;
+}
+static inline int bn_blocks(int64_t M, int64_t C) {
+  const int64_t lanes = BN_THREADS / (C / 4);
+  const int64_t want = (M + lanes * 8 - 1) / (lanes * 8);            // >= 8 rows per thread before splitting further
+  const int64_t cap = std::min<int64_t>(BN_MAX_BLOCKS, (int64_t)sm_count() * 2);
+  return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+template <typename T>
+static int bn_stats_t(const void* y, int64_t M, int C, float* scratch, float eps, float momentum, float* mean,
+                      float* invstd, float* rm, float* rv, int64_t* nb, cudaStream_t st) {
+  B200_CHECK_CUDA(launch_pdl(bn_stats_kernel<T>, dim3(bn_blocks(M, C)), dim3(BN_THREADS), 0, st, (const T*)y, M, C,
+                             scratch + BN_SCRATCH_HEAD, reinterpret_cast<uint32_t*>(scratch), eps, momentum, mean,
+                             invstd, rm, rv, nb));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_fwd_stats(const void* y, int64_t M, int64_t C, float eps, float momentum, float* mean,
+                                 float* invstd, float* running_mean, float* running_var, int64_t* num_batches,
+                                 float* scratch, int64_t scratch_floats, int dtype, b200_stream_t stream) {
+  CONV_COMMON("bn_fwd_stats", ALIGNED16(y) && mean != nullptr && invstd != nullptr && scratch != nullptr);
+  if (int r = bn_check("bn_fwd_stats", M, C, scratch, scratch_floats)) return r;
+  B200_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_fwd_stats: running_mean / running_var go together");
+  return dtype == B200_BF16 ? bn_stats_t<bf16_t>(y, M, (int)C, scratch, eps, momentum, mean, invstd, running_mean, running_var, num_batches, st)
+                            : bn_stats_t<float>(y, M, (int)C, scratch, eps, momentum, mean, invstd, running_mean, running_var, num_batches, st);
+}
+
+template <typename T>
+static int bn_apply_t(const void* y, const void* res, void* out, int64_t M, int C, const float* mean, const float* invstd,
+                      const float* gamma, const float* beta, int relu, cudaStream_t st) {
+  B200_CHECK_CUDA(launch_pdl(bn_apply_kernel<T>, dim3(grid_for(M * (C / 4), 256, 16)), dim3(256), 0, st, (const T*)y,
+                             (const T*)res, (T*)out, M, C, mean, invstd, gamma, beta, relu));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_fwd_apply(const void* y, const void* res, void* out, int64_t M, int64_t C, const float* mean,
+                                 const float* invstd, const float* gamma, const float* beta, int relu, int dtype,
+                                 b200_stream_t stream) {
+  CONV_COMMON("bn_fwd_apply", ALIGNED16(y) && ALIGNED16(out) && ALIGNED16_OR_NULL(res) && ALIGNED16(mean) &&
+                                  ALIGNED16(invstd) && ALIGNED16(gamma) && ALIGNED16(beta));
+  if (int r = bn_check("bn_fwd_apply", M, C, nullptr, 0)) return r;
+  return dtype == B200_BF16 ? bn_apply_t<bf16_t>(y, res, out, M, (int)C, mean, invstd, gamma, beta, relu, st)
+                            : bn_apply_t<float>(y, res, out, M, (int)C, mean, invstd, gamma, beta, relu, st);
+}
+
+template <typename T>
+static int bn_bwd_reduce_t(const void* dout, const void* out, const void* y, int64_t M, int C, const float* mean,
+                           const float* invstd, float* scratch, float* dgamma, float* dbeta, cudaStream_t st) {
+  B200_CHECK_CUDA(launch_pdl(bn_bwd_reduce_kernel<T>, dim3(bn_blocks(M, C)), dim3(BN_THREADS), 0, st, (const T*)dout,
+                             (const T*)out, (const T*)y, M, C, mean, invstd, scratch + BN_SCRATCH_HEAD,
+                             reinterpret_cast<uint32_t*>(scratch), dgamma, dbeta));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_bwd_reduce(const void* dout, const void* out, const void* y, int64_t M, int64_t C,
+                                  const float* mean, const float* invstd, float* dgamma, float* dbeta, float* scratch,
+                                  int64_t scratch_floats, int dtype, b200_stream_t stream) {
+  CONV_COMMON("bn_bwd_reduce", ALIGNED16(dout) && ALIGNED16(y) && ALIGNED16_OR_NULL(out) && ALIGNED16(mean) &&
+                                   ALIGNED16(invstd) && dgamma != nullptr && dbeta != nullptr && scratch != nullptr);
+  if (int r = bn_check("bn_bwd_reduce", M, C, scratch, scratch_floats)) return r;
+  return dtype == B200_BF16 ? bn_bwd_reduce_t<bf16_t>(dout, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st)
+                            : bn_bwd_reduce_t<float>(dout, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st);
+}
+
+template <typename T>
+static int bn_bwd_apply_t(const void* dout, const void* out, const void* y, void* dy, void* dz, int64_t M, int C,
+                          const float* mean, const float* invstd, const float* gamma, const float* dgamma,
+                          const float* dbeta, cudaStream_t st) {
+  B200_CHECK_CUDA(launch_pdl(bn_bwd_apply_kernel<T>, dim3(grid_for(M * (C / 4), 256, 16)), dim3(256), 0, st,
+                             (const T*)dout, (const T*)out, (const T*)y, (T*)dy, (T*)dz, M, C, mean, invstd, gamma,
+                             dgamma, dbeta));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_bwd_apply(const void* dout, const void* out, const void* y, void* dy, void* dz_out, int64_t M,
+                                 int64_t C, const float* mean, const float* invstd, const float* gamma,
+                                 const float* dgamma, const float* dbeta, int dtype, b200_stream_t stream) {
+  CONV_COMMON("bn_bwd_apply", ALIGNED16(dout) && ALIGNED16(y) && ALIGNED16(dy) && ALIGNED16_OR_NULL(out) &&
+                                  ALIGNED16_OR_NULL(dz_out) && ALIGNED16(mean) && ALIGNED16(invstd) && ALIGNED16(gamma) &&
+                                  ALIGNED16(dgamma) && ALIGNED16(dbeta));
+  if (int r = bn_check("bn_bwd_apply", M, C, nullptr, 0)) return r;
+  return dtype == B200_BF16
+             ? bn_bwd_apply_t<bf16_t>(dout, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st)
+             : bn_bwd_apply_t<float>(dout, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st);
+}
+
+// ---- pooling entry points -------------------------------------------------------------------------------------------
+template <typename T>
+static int maxpool_t(bool fwd, const void* in, void* out, uint8_t* taps, int B, int H, int W, int C, int Ho, int Wo, int k,
+                     int stride, int pad, cudaStream_t st) {
+  if (fwd)
+    B200_CHECK_CUDA(launch_pdl(maxpool_fwd_kernel<T>, dim3(grid_for((int64_t)B * Ho * Wo * (C / 4), 256, 16)), dim3(256),
+                               0, st, (const T*)in, (T*)out, taps, B, H, W, C, Ho, Wo, k, stride, pad));
+  else
+    B200_CHECK_CUDA(launch_pdl(maxpool_bwd_kernel<T>, dim3(grid_for((int64_t)B * H * W * (C / 4), 256, 16)), dim3(256), 0,
+                               st, (const T*)in, (const uint8_t*)taps, (T*)out, B, H, W, C, Ho, Wo, k, stride, pad));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+static int maxpool_check(int64_t B, int H, int W, int C, int k, int stride, int pad) {
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && C > 0 && C % 4 == 0 && k > 0 && k <= 15 && stride > 0 && pad >= 0 &&
+                   2 * pad <= k && B * H * W < (1ll << 31),
+               "maxpool: bad geometry (C %% 4 == 0, kernel <= 15, padding <= kernel / 2)");
+  return 0;
+}
+extern "C" int b200_maxpool_fwd(const void* x, void* out, uint8_t* taps, int64_t B, int H, int W, int C, int k,
+                                int stride, int pad, int dtype, b200_stream_t stream) {
+  CONV_COMMON("maxpool_fwd", ALIGNED16(x) && ALIGNED16(out) && ALIGNED16(taps));
+  if (int r = maxpool_check(B, H, W, C, k, stride, pad)) return r;
+  const int Ho = conv_out(H, k, stride, pad), Wo = conv_out(W, k, stride, pad);
+  return dtype == B200_BF16 ? maxpool_t<bf16_t>(true, x, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
+                            : maxpool_t<float>(true, x, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
+}
+extern "C" int b200_maxpool_bwd(const void* dout, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
+                                int stride, int pad, int dtype, b200_stream_t stream) {
+  CONV_COMMON("maxpool_bwd", ALIGNED16(dout) && ALIGNED16(dx) && ALIGNED16(taps));
+  if (int r = maxpool_check(B, H, W, C, k, stride, pad)) return r;
+  const int Ho = conv_out(H, k, stride, pad), Wo = conv_out(W, k, stride, pad);
+  return dtype == B200_BF16
+             ? maxpool_t<bf16_t>(false, dout, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
+             : maxpool_t<float>(false, dout, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
+}
+
+template <typename T>
+static int avgpool_t(bool fwd, const void* in, void* out, int B, int HW, int C, cudaStream_t st) {
+  if (fwd)
+    B200_CHECK_CUDA(launch_pdl(avgpool_fwd_kernel<T>, dim3(grid_for((int64_t)B * (C / 4), 256)), dim3(256), 0, st,
+                               (const T*)in, (T*)out, B, HW, C));
+  else
+    B200_CHECK_CUDA(launch_pdl(avgpool_bwd_kernel<T>, dim3(grid_for((int64_t)B * HW * (C / 4), 256)), dim3(256), 0, st,
+                               (const T*)in, (T*)out, B, HW, C));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_avgpool_fwd(const void* x, void* out, int64_t B, int HW, int C, int dtype, b200_stream_t stream) {
+  CONV_COMMON("avgpool_fwd", ALIGNED16(x) && ALIGNED16(out));
+  B200_REQUIRE(B > 0 && HW > 0 && C > 0 && C % 4 == 0 && B * HW < (1ll << 31), "avgpool: bad sizes (C %% 4 == 0)");
+  return dtype == B200_BF16 ? avgpool_t<bf16_t>(true, x, out, (int)B, HW, C, st) : avgpool_t<float>(true, x, out, (int)B, HW, C, st);
+}
+extern "C" int b200_avgpool_bwd(const void* dout, void* dx, int64_t B, int HW, int C, int dtype, b200_stream_t stream) {
+  CONV_COMMON("avgpool_bwd", ALIGNED16(dout) && ALIGNED16(dx));
+  B200_REQUIRE(B > 0 && HW > 0 && C > 0 && C % 4 == 0 && B * HW < (1ll << 31), "avgpool: bad sizes (C %% 4 == 0)");
+  return dtype == B200_BF16 ? avgpool_t<bf16_t>(false, dout, dx, (int)B, HW, C, st) : avgpool_t<float>(false, dout, dx, (int)B, HW, C, st);
+}
