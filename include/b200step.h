@@ -32,6 +32,9 @@ typedef void* b200_stream_t; /* a cudaStream_t */
 #define B200_FLAG_ACCUMULATE 2 /* wgrad: dw += ... instead of dw = ... */
 #define B200_FLAG_REVERSE_M 4  /* fwd / dgrad: process the row tiles last-to-first.  Same result; a consumer that starts
                                   with the rows its producer wrote LAST finds them still in the 126 MB L2 */
+#define B200_FLAG_DETERMINISTIC 8 /* wgrad: do not split the batch dimension across CTAs: every output tile is summed
+                                  by one CTA pair in a fixed order, so the result is bit-reproducible run to run (the
+                                  default splits the batch for occupancy and combines the slices with fp32 atomics) */
 
 /* ---- errors / build info ------------------------------------------------------------------ */
 const char* b200_last_error(void);           /* host string, thread-local */

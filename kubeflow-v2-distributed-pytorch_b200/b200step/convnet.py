@@ -230,6 +230,7 @@ class ConvTrainStep:
         self.dt = torch.bfloat16 if cfg.precision == "bf16" else torch.float32
         self.x3 = cfg.precision == "fp32"
         self.augment = augment
+        self.det = bool(getattr(cfg, "deterministic_wgrad", False))
         B = self.B = cfg.batch_size
         f32 = dict(dtype=torch.float32, device=dev)
         act = dict(dtype=self.dt, device=dev)
@@ -428,12 +429,14 @@ class ConvTrainStep:
                 ops.linear_dgrad(dyk, self.wr[c.name], None, dcol, M=M, N=3 * c.cout, K=c.Kp, relu=False,
                                  stream=self.main)
                 n += 1
-            ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, stream=self.main)
+            ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
+                             stream=self.main)
         else:
             if dcol is not None:
                 ops.linear_dgrad(dy, self._w(c.name), None, dcol, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
                 n += 1
-            ops.linear_wgrad(dy, self.col[c.name][:M], gw, M=M, N=c.cout, K=c.Kp, stream=self.main)
+            ops.linear_wgrad(dy, self.col[c.name][:M], gw, M=M, N=c.cout, K=c.Kp, deterministic=self.det,
+                             stream=self.main)
         n += 1 + self._grad_done(c.name + ".weight")
         return n
 
@@ -527,11 +530,11 @@ class ConvTrainStep:
             dyr = self.dyr[: 3 * b * C].view(3 * b, C)
             ops.split_tf32(dl, dyk, ops.SPLIT_LEFT, dyr, ops.SPLIT_LEFT, rows=b, cols=C, stream=self.main)
             ops.linear_dgrad(dyk, self.wr["fc"], None, dfeat, M=b, N=3 * C, K=512, relu=False, stream=self.main)
-            ops.linear_wgrad(dyr, self.featr[: 3 * b], gw, M=3 * b, N=C, K=512, stream=self.main)
+            ops.linear_wgrad(dyr, self.featr[: 3 * b], gw, M=3 * b, N=C, K=512, deterministic=self.det, stream=self.main)
             n += 1
         else:
             ops.linear_dgrad(dl, self._w("fc"), None, dfeat, M=b, N=C, K=512, relu=False, stream=self.main)
-            ops.linear_wgrad(dl, feat, gw, M=b, N=C, K=512, stream=self.main)
+            ops.linear_wgrad(dl, feat, gw, M=b, N=C, K=512, deterministic=self.det, stream=self.main)
         n += 2 + self._grad_done("fc.weight")
         # ---- backward through the blocks
         last = lay.blocks[-1].conv2

@@ -76,6 +76,9 @@ class StepConfig:
                                          # 6.8 M L2 atomics per step take as long from the GEMM epilogue as from the
                                          # scatter kernel (67 us fused vs 35 + 31 us) and 3x longer on Zipf ids;
                                          # K-embbwd's shared-memory privatisation is what cuts them
+    deterministic_wgrad: bool = False    # convolutional path: filter gradients summed in a fixed order (no split of the
+                                         # batch dimension, B200_FLAG_DETERMINISTIC): the whole step is then
+                                         # bit-reproducible run to run, at the cost of wgrad occupancy
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1

@@ -13,6 +13,7 @@ BF16 = 1
 FLAG_RELU = 1
 FLAG_ACCUMULATE = 2
 FLAG_REVERSE_M = 4
+FLAG_DETERMINISTIC = 8
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DEFAULT_LIB = os.path.join(_PKG_DIR, "lib", "libb200step.so")

@@ -10,7 +10,7 @@ from typing import Optional
 import torch
 
 from . import lib as _l
-from .lib import BF16, F32, FLAG_ACCUMULATE, FLAG_RELU, FLAG_REVERSE_M, get_lib, ptr
+from .lib import BF16, F32, FLAG_ACCUMULATE, FLAG_DETERMINISTIC, FLAG_RELU, FLAG_REVERSE_M, get_lib, ptr
 
 __all__ = [
     "dtype_code", "preprocess", "linear_fwd", "linear_dgrad", "linear_wgrad", "ce_loss_grad", "colsum",
@@ -85,10 +85,13 @@ def linear_dgrad_emb(dy, w, idx, dtables, *, M: int, N: int, num_cat: int, table
                                N, num_cat, table_rows, embed_dim, dtype_code(dy.dtype), _stream(stream))
 
 
-def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False, stream=None):
+def linear_wgrad(dy, x, dw, *, M: int, N: int, K: int, accumulate: bool = False, deterministic: bool = False,
+                 stream=None):
     _cuda(dy, x, dw)
     get_lib().linear_wgrad(ptr(dy), dy.stride(0), ptr(x), x.stride(0), ptr(dw), dw.stride(0), M, N, K,
-                           dtype_code(dy.dtype), FLAG_ACCUMULATE if accumulate else 0, _stream(stream))
+                           dtype_code(dy.dtype),
+                           (FLAG_ACCUMULATE if accumulate else 0) | (FLAG_DETERMINISTIC if deterministic else 0),
+                           _stream(stream))
 
 
 def linear_wgrad_grouped(dys, xs, dws, *, M: int, Ns, Ks, stream=None):

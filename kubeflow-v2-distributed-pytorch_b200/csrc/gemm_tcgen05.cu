@@ -910,7 +910,7 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
   // two batch slices per CTA (pair): the epilogue of the first overlaps the MMAs of the second
   static const int wgrad_waves = getenv("B200STEP_WGRAD_WAVES") ? atoi(getenv("B200STEP_WGRAD_WAVES")) : 1;
   int splits = wgrad_waves * (sm_count() / gemm_ctas()) / tiles;
-  if (splits < 1) splits = 1;
+  if (splits < 1 || (flags & B200_FLAG_DETERMINISTIC)) splits = 1;   // one CTA pair sums a tile's whole batch in order
   if (splits > p.k_blocks) splits = p.k_blocks;
   p.kb_per_split = (p.k_blocks + splits - 1) / splits;
   p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
