@@ -40,6 +40,10 @@ WORKLOADS = {
     "t0_tf32_b4096": dict(arch="tabular_mlp", precision="tf32", batch=4096, optimizer="sgd"),   # single TF32 pass
     "t1_bf16_b65536": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="sgd"),
     "t1_bf16_b65536_adam": dict(arch="tabular_mlp_wide", precision="bf16", batch=65536, optimizer="adam"),
+    # the reference-literal model (task.py:63,171: --arch resnet18, batch 1024 per process) — bench_conv.py
+    "resnet18_fp32_b1024": dict(arch="resnet18", precision="fp32", batch=1024, optimizer="sgd", conv=True),
+    "resnet18_tf32_b1024": dict(arch="resnet18", precision="tf32", batch=1024, optimizer="sgd", conv=True),
+    "resnet18_bf16_b1024": dict(arch="resnet18", precision="bf16", batch=1024, optimizer="sgd", conv=True),
     # BASELINE config 1 (CPU only, `--impl reference`): the oracle as real DistributedDataParallel over gloo,
     # 2 processes x (host cores / 2) threads, 4096 rows per rank
     "t0_fp32_b4096_cpu_gloo2": dict(arch="tabular_mlp", precision="fp32", batch=4096, optimizer="sgd", cpu_gloo=2),
@@ -178,6 +182,11 @@ def run_reference(args, rank):
     from b200step.model import ARCHS
 
     wl = WORKLOADS[args.workload]
+    if wl.get("conv"):
+        import bench_conv
+
+        bench_conv.run_reference(args, wl)
+        return
     spec = ARCHS[wl["arch"]]
     # --steps / --warmup are honoured up to a time budget (a 65536-row CPU step takes ~0.3 s on 32 threads)
     steps = max(1, args.steps)
@@ -309,9 +318,14 @@ def run_b200(args, rank, local_rank, world):
 
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py --impl b200 needs a CUDA device: the training step has no CPU path")
+    wl = WORKLOADS[args.workload]
+    if wl.get("conv"):
+        import bench_conv
+
+        bench_conv.run_b200(args, rank, local_rank, world, wl, _peaks(), ClockSampler, _measure_tf32_peak)
+        return
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    wl = WORKLOADS[args.workload]
     if wl.get("cpu_gloo"):
         raise SystemExit(f"--workload {args.workload} is the CPU/gloo baseline (config 1): run it with --impl reference")
     spec = ARCHS[wl["arch"]]

@@ -63,7 +63,8 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--model_filename", type=str, help="Model filename.", default="resnet_distributed.pth")
     parser.add_argument("-a", "--arch", metavar="ARCH", default="resnet18", choices=model_names + TABULAR_ARCHS,
                         help="model architecture: " + " | ".join(TABULAR_ARCHS) +
-                             " (B200 path) | torchvision names (accepted, not built) (default: resnet18)")
+                             " | resnet18 | resnet34 (B200 paths) | other torchvision names (accepted, not built) "
+                             "(default: resnet18)")
     parser.add_argument("--momentum", default=0.9, type=float, metavar="M", help="momentum")
     parser.add_argument("--wd", "--weight-decay", default=1e-4, type=float, metavar="W",
                         help="weight decay (default: 1e-4)", dest="weight_decay")
@@ -116,8 +117,8 @@ def build_parser() -> argparse.ArgumentParser:
 def spec_from_args(args) -> ModelSpec:
     if args.arch not in ARCHS:
         raise NotImplementedError(
-            f"--arch {args.arch}: the torchvision/conv path is not built in the B200 step (DESIGN.md §7); "
-            f"use one of {TABULAR_ARCHS}")
+            f"--arch {args.arch}: of the torchvision models only the BasicBlock ResNets (resnet18, resnet34) have a "
+            f"B200 path (DESIGN.md §7); the tabular models are {TABULAR_ARCHS}")
     spec = ARCHS[args.arch]
     over = {}
     for name in ("num_dense", "num_cat", "cardinality", "embed_dim", "num_classes"):
@@ -202,19 +203,29 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
     if args.pretrained:
         raise NotImplementedError("--pretrained needs the network and a torchvision model; not available here")
     print(f"=> creating model '{args.arch}'")
-    spec = spec_from_args(args)
-
+    from . import convnet
     from .data import make_synthetic
     from .model import init_parameters
     from .sampler import batch_bounds, rank_indices
 
-    params = init_parameters(spec, args.random_seed)
-    dataset = make_synthetic(args.synthetic_rows, spec)
+    conv = args.arch in convnet.ARCH_BLOCKS                    # the reference's own model family (task.py:171)
+    if conv:
+        lay = convnet.resnet_layout(args.arch, num_classes=args.num_classes or 1000)
+        params = convnet.init_state(args.arch, args.random_seed, lay.num_classes)
+        dataset = convnet.load_cifar10_test_split("data") or convnet.make_synthetic_images(
+            args.synthetic_rows, seed=args.random_seed)        # task.py:256-257 (train=False for both loaders)
+        arch_name, n_params = args.arch, sum(v.numel() for k, v in params.items() if "running" not in k and
+                                             "num_batches" not in k)
+    else:
+        spec = spec_from_args(args)
+        params = init_parameters(spec, args.random_seed)
+        dataset = make_synthetic(args.synthetic_rows, spec)
+        arch_name, n_params = spec.name, spec.num_params
     my_rows = rank_indices(len(dataset), world, rank)           # DistributedSampler(train_set), task.py:260
     bounds = batch_bounds(my_rows.numel(), batch_size)          # DataLoader batching, task.py:263
 
     if args.plan_only:
-        plan = {"rank": rank, "world": world, "gpu": gpu, "arch": spec.name, "params": spec.num_params,
+        plan = {"rank": rank, "world": world, "gpu": gpu, "arch": arch_name, "params": n_params,
                 "samples_this_rank": int(my_rows.numel()), "batches_per_epoch": len(bounds),
                 "first_indices": my_rows[:4].tolist(), "last_batch_rows": len(bounds[-1]),
                 "precision": args.precision, "optimizer": args.optimizer}
@@ -246,7 +257,10 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
     cfg = StepConfig(batch_size=batch_size, world=world, rank=rank, precision=args.precision,
                      optimizer=args.optimizer, lr=args.learning_rate, momentum=args.momentum,
                      weight_decay=args.weight_decay, dropout_seed=args.random_seed, use_graph=not args.no_graph)
-    step = TrainStep(spec, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
+    if conv:
+        step = convnet.ConvTrainStep(lay, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
+    else:
+        step = TrainStep(spec, params, dataset, my_rows, cfg, comm, device=torch.device("cuda", args.gpu))
 
     for epoch in range(num_epochs):
         epoch_start = datetime.now().strftime("%Y_%m_%d_%H_%M_%S")
@@ -254,7 +268,9 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
 
         if epoch % 10 == 0:                                         # task.py:279
             if rank == 0:
-                accuracy = step.evaluate()                          # task.py:281 (test set == train set, task.py:256-257)
+                # task.py:281 (test set == train set, task.py:256-257); the image path's test loader applies the random
+                # training transform too (task.py:257 passes `transform`)
+                accuracy = step.evaluate(draws=convnet.draw_augmentation(len(dataset))) if conv else step.evaluate()
                 state = step.state_dict()
                 if args.local_training:
                     torch.save(state, model_filepath)               # task.py:283
@@ -276,6 +292,8 @@ def main_worker(gpu, ngpus_per_node, args) -> None:
 
         if args.set_epoch and epoch > 0:
             step.set_row_order(rank_indices(len(dataset), world, rank, epoch=epoch))
+        if conv:     # this epoch's RandomCrop / RandomHorizontalFlip draws, from torch's generator like the transforms
+            step.set_draws(convnet.draw_augmentation(int(my_rows.numel())))
         for b in bounds:                                            # task.py:303
             if not args.quiet_steps:
                 print(f"training with gpu {args.gpu}")              # task.py:306 (host-side only, no device sync)

@@ -196,6 +196,19 @@ def make_synthetic_images(n: int, seed: int = 0, image: int = 32, num_classes: i
     return ImageDataset(images, labels)
 
 
+def load_cifar10_test_split(root: str = "data") -> Optional[ImageDataset]:
+    """The dataset the reference trains AND tests on: CIFAR10(root="data", train=False) (task.py:256-257), when its
+    files are already on disk (the download the reference asks for needs the network).  None when absent."""
+    import os
+
+    if not os.path.isdir(os.path.join(root, "cifar-10-batches-py")):
+        return None
+    import torchvision
+
+    ds = torchvision.datasets.CIFAR10(root=root, train=False, download=False)
+    return ImageDataset(torch.from_numpy(ds.data).contiguous(), torch.tensor(ds.targets, dtype=torch.int64))
+
+
 def draw_augmentation(n: int, image: int = 32, pad: int = 4) -> torch.Tensor:
     """The random numbers torchvision's transform pipeline (task.py:250-253) consumes for n consecutive samples, from
     torch's global generator in the same order: RandomCrop.get_params -> randint(0, 2*pad+1) for the top, then for the
@@ -501,12 +514,12 @@ class ConvTrainStep:
         self._features = x
         return n
 
-    def _enqueue(self, b: int, row_idx, cursor, draws, advance: bool) -> int:
+    def _enqueue(self, b: int, row_idx, cursor, draws, advance: bool, ds: Optional[ImageDataset] = None) -> int:
         """One whole step for b images: load + augment, forward, loss, backward (+ bucket all-reduces), optimizer."""
         lay, cfg = self.lay, self.cfg
         C = lay.num_classes
         self._pending = [bk[2] for bk in self.buckets]
-        n = self._load(b, row_idx, cursor, draws)
+        n = self._load(b, row_idx, cursor, draws, ds)
         n += self._forward(b, True)
         feat = self._features
         # ---- output layer + CrossEntropyLoss (task.py:309-310) and the start of backward (task.py:311)
@@ -657,6 +670,61 @@ class ConvTrainStep:
         self._enqueue(self.tail, self.row_idx[off:], None, d[off:] if d is not None else None, False)
         self.host_steps += 1
 
+    # ---- host-fed path: what the reference's DataLoader + .cuda() copies do (task.py:303-307) ---------------------
+    HOST_SLOTS = 4
+
+    def host_batch_bytes(self) -> int:
+        img = self.lay.image
+        return self.B * (img * img * 3 + 8 + 4)
+
+    def step_from_host(self, images_u8: torch.Tensor, labels: torch.Tensor, draws: torch.Tensor) -> int:
+        """One step on a batch that lives in (pinned) host memory: raw uint8 images, int64 labels and the int8
+        augmentation draws cross PCIe (3 084 bytes per sample), everything else happens on the device.  Returns a
+        ticket for `host_loss`."""
+        B = self.B
+        if images_u8.shape[0] != B:
+            raise ValueError(f"host batches must have batch_size={B} rows")
+        if not hasattr(self, "_stage"):
+            dev = self.dev
+            self._stage = ImageDataset(torch.empty(B, self.lay.image, self.lay.image, 3, dtype=torch.uint8, device=dev),
+                                       torch.empty(B, dtype=torch.int64, device=dev))
+            self._stage_draws = torch.empty(B, 4, dtype=torch.int8, device=dev)
+            self._loss_host = torch.zeros(self.HOST_SLOTS, dtype=torch.float32).pin_memory()
+            self._loss_ev = [torch.cuda.Event() for _ in range(self.HOST_SLOTS)]
+            self._host_graph, self._host_ticket = None, 0
+        with torch.cuda.stream(self.main):
+            self._stage.images.copy_(images_u8, non_blocking=True)
+            self._stage.labels.copy_(labels, non_blocking=True)
+            self._stage_draws.copy_(draws, non_blocking=True)
+        if self.cfg.use_graph and self.host_steps > 0:
+            if self._host_graph is None:
+                import ctypes as C
+
+                self.main.synchronize()
+                self.comm_stream.synchronize()
+                self.lib.graph_begin(self.main.cuda_stream)
+                try:
+                    self._enqueue(B, None, None, self._stage_draws, False, self._stage)
+                finally:
+                    out = C.c_void_p()
+                    self.lib.graph_end(self.main.cuda_stream, C.byref(out))
+                self._host_graph = out
+            self.lib.graph_launch(self._host_graph, self.main.cuda_stream)
+        else:
+            self.kernels_per_step = self._enqueue(B, None, None, self._stage_draws, False, self._stage)
+        k = self._host_ticket % self.HOST_SLOTS
+        with torch.cuda.stream(self.main):
+            self._loss_host[k: k + 1].copy_(self.loss, non_blocking=True)
+        self._loss_ev[k].record(self.main)
+        self.host_steps += 1
+        self._host_ticket += 1
+        return self._host_ticket - 1
+
+    def host_loss(self, ticket: int) -> float:
+        k = ticket % self.HOST_SLOTS
+        self._loss_ev[k].synchronize()
+        return float(self._loss_host[k])
+
     def loss_value(self) -> float:
         self.main.synchronize()
         return float(self.loss.item())
@@ -738,3 +806,6 @@ class ConvTrainStep:
         if self.graph is not None:
             self.lib.graph_destroy(self.graph)
             self.graph = None
+        if getattr(self, "_host_graph", None) is not None:
+            self.lib.graph_destroy(self._host_graph)
+            self._host_graph = None

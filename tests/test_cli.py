@@ -59,8 +59,8 @@ def test_additive_flags_default_to_reference_behaviour():
 def test_unbuilt_arch_fails_loudly():
     from b200step.cli import build_parser, spec_from_args
 
-    a = build_parser().parse_args([])
-    with pytest.raises(NotImplementedError, match="not built"):
+    a = build_parser().parse_args(["--arch", "vgg16"])         # a torchvision name without a B200 path
+    with pytest.raises(NotImplementedError, match="only the BasicBlock ResNets"):
         spec_from_args(a)
     a = build_parser().parse_args(["--arch", "tabular_mlp", "--hidden", "64,32", "--cardinality", "50"])
     s = spec_from_args(a)
@@ -117,3 +117,13 @@ def test_training_without_gpu_exits_nonzero():
                    "--batch_size", "32", "--gpu", "0"], {"MASTER_PORT": "29553"})
     assert r.returncode != 0
     assert "CUDA device" in r.stderr or "CUDA" in r.stderr
+
+
+def test_default_arch_resnet18_plans_the_reference_model():
+    """`python task.py` with no --arch is the reference's literal configuration: resnet18, 11 689 512 parameters, the
+    10 000-image test split over the ranks, batches of 1024 (task.py:58,63,256,263)."""
+    r = _run_task(["--plan_only", "--local_training"], {"WORLD_SIZE": "-1"})
+    assert r.returncode == 0, r.stdout + r.stderr
+    plan = json.loads([l for l in r.stdout.splitlines() if l.startswith("PLAN ")][0][5:])
+    assert plan["arch"] == "resnet18" and plan["params"] == 11689512
+    assert plan["samples_this_rank"] == 10000 and plan["batches_per_epoch"] == 10 and plan["last_batch_rows"] == 784
