@@ -79,11 +79,14 @@ class ResNetOracle:
     def __init__(self, arch: str, images_u8: torch.Tensor, labels: torch.Tensor, rank_rows: Sequence[torch.Tensor], *,
                  batch_size: int, lr: float = 0.1, momentum: float = 0.9, weight_decay: float = 1e-4, seed: int = 0,
                  num_classes: int = 1000, rank_draws: Optional[Sequence[Optional[torch.Tensor]]] = None,
-                 optimizer: str = "sgd"):
+                 optimizer: str = "sgd", dtype: torch.dtype = torch.float32):
+        """dtype=torch.float64 runs the same objects in double precision: the yardstick for how far the fp32 CPU
+        path itself is from the exact result (tests/test_conv_step_gpu.py, profiles/r02_resnet_parity_conditioning.md)."""
         import torchvision
 
         torch.manual_seed(seed)                                                # set_random_seeds, task.py:162
-        self.model = torchvision.models.__dict__[arch](num_classes=num_classes)   # task.py:171
+        self.model = torchvision.models.__dict__[arch](num_classes=num_classes).to(dtype)   # task.py:171
+        self.dtype = dtype
         self.model.train()
         self.criterion = nn.CrossEntropyLoss()                                 # task.py:211
         if optimizer == "sgd":
@@ -99,7 +102,7 @@ class ResNetOracle:
         rows = self.rank_rows[rank][k * self.B: (k + 1) * self.B]
         d = self.rank_draws[rank]
         x = augment_with_draws(self.images[rows], d[k * self.B: (k + 1) * self.B] if d is not None else None)
-        return x, self.labels[rows]
+        return x.to(self.dtype), self.labels[rows]
 
     def step(self) -> List[float]:
         """One optimizer step; returns every rank's local loss (what each process prints at task.py:310)."""
@@ -132,7 +135,7 @@ class ResNetOracle:
         with torch.no_grad():
             for s in range(0, images_u8.shape[0], batch):
                 x = augment_with_draws(images_u8[s: s + batch], draws[s: s + batch] if draws is not None else None)
-                preds.append(self.model(x).argmax(dim=1))
+                preds.append(self.model(x.to(self.dtype)).argmax(dim=1))
         self.model.train()
         p = torch.cat(preds)
         return float((p == labels).sum().item()) / labels.numel(), p
