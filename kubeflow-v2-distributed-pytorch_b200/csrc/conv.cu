@@ -122,6 +122,86 @@ im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W,
   }
 }
 
+// Fast path, C / VEC a power of two (every ResNet layer but conv1): one warp per output row, lanes stride over the
+// row's 16-byte vectors; tap and channel of a vector come from a shift / mask and one multiply-shift division.
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_vec_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W, int C, int Ho, int Wo, int kh, int kw,
+                  int stride, int pad, int64_t ldcol, int cshift /*log2(C / VEC)*/) {
+  pdl_launch_dependents();
+  pdl_wait();
+  constexpr int VEC = 16 / (int)sizeof(T);
+  const int taps = kh * kw;
+  const int vrow = (int)(ldcol / VEC);
+  const int vk = taps << cshift;                       // vectors that carry data; the rest of the row is padding
+  const uint32_t inv_kw = 65536u / (uint32_t)kw + 1u;  // tap / kw for tap < 64: exact
+  const int64_t rows = (int64_t)B * Ho * Wo;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t m = warp0; m < rows; m += nwarps) {
+    const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho);
+    const int64_t b = m / ((int64_t)Wo * Ho);
+    const int h0 = ho * stride - pad, w0 = wo * stride - pad;
+    const T* img = x + b * H * (int64_t)W * C;
+    uint4* dst = reinterpret_cast<uint4*>(col + m * ldcol);
+#pragma unroll 4
+    for (int v = lane; v < vrow; v += 32) {
+      uint4 val = make_uint4(0, 0, 0, 0);
+      if (v < vk) {
+        const int tap = v >> cshift, cv = v & ((1 << cshift) - 1);
+        const int ky = (int)(((uint32_t)tap * inv_kw) >> 16), kx = tap - ky * kw;
+        const int h = h0 + ky, w = w0 + kx;
+        if (h >= 0 && h < H && w >= 0 && w < W)
+          val = *reinterpret_cast<const uint4*>(img + ((int64_t)h * W + w) * C + cv * VEC);
+      }
+      dst[v] = val;
+    }
+  }
+}
+
+// Small channel counts (conv1: C = 3, K = 147): a block builds IM_ROWS col rows in shared memory — one (row, tap)
+// pair per thread step, C scalar copies each — and writes them out as coalesced 16-byte vectors.
+constexpr int IM_ROWS = 32;
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_smallc_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W, int C, int Ho, int Wo, int kh,
+                     int kw, int stride, int pad, int64_t ldcol) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ __align__(16) unsigned char im_smem[];
+  T* tile = reinterpret_cast<T*>(im_smem);              // [IM_ROWS][ldcol]
+  constexpr int VEC = 16 / (int)sizeof(T);
+  const int taps = kh * kw, K = taps * C;
+  const int64_t rows = (int64_t)B * Ho * Wo;
+  const int kcols = (int)ldcol;
+  for (int64_t m0 = (int64_t)blockIdx.x * IM_ROWS; m0 < rows; m0 += (int64_t)gridDim.x * IM_ROWS) {
+    const int nr = (int)min((int64_t)IM_ROWS, rows - m0);
+    for (int i = threadIdx.x; i < nr * taps; i += blockDim.x) {
+      const int r = i / taps, tap = i - r * taps;
+      const int ky = tap / kw, kx = tap - ky * kw;
+      const int64_t m = m0 + r;
+      const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho);
+      const int64_t b = m / ((int64_t)Wo * Ho);
+      const int h = ho * stride - pad + ky, w = wo * stride - pad + kx;
+      const bool inside = h >= 0 && h < H && w >= 0 && w < W;
+      const T* src = x + ((b * H + h) * (int64_t)W + w) * C;
+      T* d = tile + r * kcols + tap * C;
+      for (int c = 0; c < C; ++c) d[c] = inside ? src[c] : from_float<T>(0.f);
+    }
+    for (int i = threadIdx.x; i < nr * (kcols - K); i += blockDim.x) {     // the GEMM's K padding
+      const int r = i / (kcols - K);
+      tile[r * kcols + K + (i - r * (kcols - K))] = from_float<T>(0.f);
+    }
+    __syncthreads();
+    const int nvec = nr * kcols / VEC;                   // rows are contiguous in col when ldcol == kcols
+    uint4* dst = reinterpret_cast<uint4*>(col + m0 * ldcol);
+    const uint4* srcv = reinterpret_cast<const uint4*>(tile);
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = srcv[i];
+    __syncthreads();
+  }
+}
+
 // ---- col2im (gather form) -------------------------------------------------------------------------------------------
 // dx[b,h,w,c] = sum over taps (ky,kx) with (h + pad - ky) = ho*stride, (w + pad - kx) = wo*stride in range of
 //               dcol[(b,ho,wo), (ky*kw+kx)*C + c]   (+ add[b,h,w,c] when `add` is given: the residual branch's gradient)
@@ -165,7 +245,7 @@ col2im_kernel(const T* __restrict__ dcol, int64_t ldcol, const T* __restrict__ a
 // writes one partial row.  The last block to finish (ticket) folds the partial rows IN ORDER in fp64, so the result does
 // not depend on scheduling.  `Fin` turns the two column sums into the kernel's outputs.
 constexpr int BN_THREADS = 256;
-constexpr int BN_MAX_C = 512;
+constexpr int BN_MAX_C = 1024;
 
 template <typename Acc>
 __device__ __forceinline__ void bn_block_reduce(Acc a, Acc b, int vc, float* partial_row, int C) {
@@ -187,19 +267,80 @@ __device__ __forceinline__ void bn_block_reduce(Acc a, Acc b, int vc, float* par
   }
 }
 
-// true in exactly one block: the one that arrives last (all partial rows are then visible to it)
+// true in exactly one block: the one that arrives last (all partial rows are then visible to it).  ONE thread per block
+// takes the ticket with an acq_rel atomic at gpu scope: bar.sync orders the block's partial-row stores before it
+// (release is cumulative) and its acquire before the other threads' reads, which go to L2 (ld.cg).  A __threadfence()
+// in every thread instead compiles to MEMBAR.SC.GPU + CCTL.IVALL x 256 and cost ~20 us per launch.
 __device__ __forceinline__ bool bn_last_block(uint32_t* ticket) {
   __shared__ uint32_t s_last;
-  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    const uint32_t t = atomicAdd(ticket, 1u);
+    uint32_t t;
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(t) : "l"(ticket) : "memory");
     s_last = (t == gridDim.x - 1);
     if (s_last) *ticket = 0;                 // ready for the next launch (graph replay)
   }
   __syncthreads();
-  if (s_last) __threadfence();
   return s_last != 0;
+}
+
+// The last block folds the `nb` partial rows [nb][2*C] into totals[2*C] (shared memory, fp64).  All 256 threads take
+// part: thread (v, jg) sums rows jg, jg + lanes, ... of the 4 columns 4v..4v+3 with independent 16-byte loads in flight,
+// then the `lanes` sub-sums of a column are added in a fixed order — the result is the same on every run.
+// The running sums are fp32 with a Neumaier compensation term (sum + comp carries ~48 bits) instead of fp64 adds.
+// Plain (weak) 16-byte global load of a partial row written by another block of this grid.  It is ordered after the
+// ticket's acquire (bar.sync) and the L1 was invalidated by that acquire, so it cannot see stale data; `__ldcg` here
+// compiled to LDG.STRONG.GPU, which ptxas would not batch: 64 serialised L2 round trips = 20 us on one SM.
+__device__ __forceinline__ float4 ld_partial_v4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void neumaier_add(float& sum, float& comp, float x) {
+  const float t = sum + x;
+  comp += (fabsf(sum) >= fabsf(x)) ? ((sum - t) + x) : ((x - t) + sum);
+  sum = t;
+}
+__device__ __forceinline__ void bn_fold_partials(const float* __restrict__ partials, int nb, int C, double* totals) {
+  __shared__ float2 stage[BN_THREADS][4];
+  const int vcols = 2 * C / 4;
+  for (int v0 = 0; v0 < vcols; v0 += BN_THREADS) {
+    const int width = min(vcols - v0, BN_THREADS);       // vector columns handled in this pass
+    const int lanes = BN_THREADS / width;                // row lanes per column (>= 1)
+    const int v = threadIdx.x % width, jg = threadIdx.x / width;
+    float s0 = 0, s1 = 0, s2 = 0, s3 = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (jg < lanes) {
+      const float* col = partials + (v0 + v) * 4;
+      for (int j = jg; j < nb; j += 8 * lanes) {          // 8 loads in flight, then the (ordered) additions
+        float4 t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int jj = j + u * lanes;
+          t[u] = jj < nb ? ld_partial_v4(col + (int64_t)jj * 2 * C) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          neumaier_add(s0, c0, t[u].x); neumaier_add(s1, c1, t[u].y);
+          neumaier_add(s2, c2, t[u].z); neumaier_add(s3, c3, t[u].w);
+        }
+      }
+    }
+    stage[threadIdx.x][0] = make_float2(s0, c0); stage[threadIdx.x][1] = make_float2(s1, c1);
+    stage[threadIdx.x][2] = make_float2(s2, c2); stage[threadIdx.x][3] = make_float2(s3, c3);
+    __syncthreads();
+    if (threadIdx.x < width) {
+      double t[4] = {0, 0, 0, 0};
+      for (int g = 0; g < lanes; ++g)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 p = stage[g * width + threadIdx.x][q];
+          t[q] += (double)p.x + (double)p.y;
+        }
+      double* o = totals + (v0 + threadIdx.x) * 4;
+      o[0] = t[0]; o[1] = t[1]; o[2] = t[2]; o[3] = t[3];
+    }
+    __syncthreads();
+  }
 }
 
 template <typename T>
@@ -215,6 +356,7 @@ bn_stats_kernel(const T* __restrict__ y, int64_t M, int C, float* __restrict__ p
   const int64_t r0 = blockIdx.x * chunk, r1 = min(M, r0 + chunk);
   float4 s = make_float4(0, 0, 0, 0), q = make_float4(0, 0, 0, 0);
   if (ry < lanes)
+#pragma unroll 8
     for (int64_t r = r0 + ry; r < r1; r += lanes) {
       const float4 v = Vec4<T>::load(y + r * C + cv * 4);
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
@@ -222,12 +364,10 @@ bn_stats_kernel(const T* __restrict__ y, int64_t M, int C, float* __restrict__ p
     }
   bn_block_reduce(s, q, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
   if (!bn_last_block(ticket)) return;
+  __shared__ double totals[2 * BN_MAX_C];
+  bn_fold_partials(partials, (int)gridDim.x, C, totals);
   for (int c = threadIdx.x; c < C; c += BN_THREADS) {
-    double ds = 0.0, dq = 0.0;
-    for (int j = 0; j < (int)gridDim.x; ++j) {
-      ds += (double)partials[(int64_t)j * 2 * C + c];
-      dq += (double)partials[(int64_t)j * 2 * C + C + c];
-    }
+    const double ds = totals[c], dq = totals[C + c];
     const double mu = ds / (double)M;
     double var = dq / (double)M - mu * mu;             // biased: what normalises the batch
     if (var < 0.0) var = 0.0;
@@ -285,6 +425,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, cons
   const float4 mu = *reinterpret_cast<const float4*>(mean + cv * 4), is = *reinterpret_cast<const float4*>(invstd + cv * 4);
   float4 sb = make_float4(0, 0, 0, 0), sg = make_float4(0, 0, 0, 0);
   if (ry < lanes)
+#pragma unroll 4
     for (int64_t r = r0 + ry; r < r1; r += lanes) {
       const int64_t off = r * C + cv * 4;
       float4 d = Vec4<T>::load(dout + off);
@@ -299,14 +440,11 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, cons
     }
   bn_block_reduce(sb, sg, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
   if (!bn_last_block(ticket)) return;
+  __shared__ double totals[2 * BN_MAX_C];
+  bn_fold_partials(partials, (int)gridDim.x, C, totals);
   for (int c = threadIdx.x; c < C; c += BN_THREADS) {
-    double db = 0.0, dg = 0.0;
-    for (int j = 0; j < (int)gridDim.x; ++j) {
-      db += (double)partials[(int64_t)j * 2 * C + c];
-      dg += (double)partials[(int64_t)j * 2 * C + C + c];
-    }
-    dbeta[c] = (float)db;
-    dgamma[c] = (float)dg;
+    dbeta[c] = (float)totals[c];
+    dgamma[c] = (float)totals[C + c];
   }
 }
 
@@ -394,13 +532,18 @@ maxpool_bwd_kernel(const T* __restrict__ dout, const uint8_t* __restrict__ tap_i
     const int w = (int)(pix % W), h = (int)((pix / W) % H);
     const int64_t b = pix / ((int64_t)W * H);
     float4 acc = make_float4(0, 0, 0, 0);
+    const bool s2 = stride == 2;                          // the ResNet stem: shifts instead of divisions
     for (int ky = 0; ky < k; ++ky) {
       const int hn = h + pad - ky;
-      if (hn < 0 || hn % stride != 0 || hn / stride >= Ho) continue;
+      if (hn < 0) continue;
+      const int hq = s2 ? hn >> 1 : hn / stride;
+      if (hq * stride != hn || hq >= Ho) continue;
       for (int kx = 0; kx < k; ++kx) {
         const int wn = w + pad - kx;
-        if (wn < 0 || wn % stride != 0 || wn / stride >= Wo) continue;
-        const int64_t m = (b * Ho + hn / stride) * (int64_t)Wo + wn / stride;
+        if (wn < 0) continue;
+        const int wq = s2 ? wn >> 1 : wn / stride;
+        if (wq * stride != wn || wq >= Wo) continue;
+        const int64_t m = (b * Ho + hq) * (int64_t)Wo + wq;
         const uchar4 tp = *reinterpret_cast<const uchar4*>(tap_in + m * C + c);
         const float4 d = Vec4<T>::load(dout + m * C + c);
         const int me = ky * k + kx;
@@ -498,16 +641,34 @@ extern "C" int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, i
   B200_REQUIRE(ldcol >= K && (ldcol * es) % 16 == 0, "im2col: ldcol=%lld must be >= %d and a multiple of 16 bytes",
                (long long)ldcol, K);
   B200_REQUIRE(B * Ho * Wo * ldcol < (1ll << 40), "im2col: col matrix too large");
-  const bool vec = C % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
-  const int64_t items = B * Ho * Wo * (vec ? ldcol / 4 : ldcol);
-  const int grid = grid_for(items, 256, 16);
-  const int kcols = (int)ldcol;
-  if (dtype == B200_BF16) {
-    if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 4>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
-    else B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 1>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
-  } else {
-    if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 4>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
-    else B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 1>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+  const int vecn = 16 / es;                               // elements per 16-byte vector
+  const bool aligned = (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  int cshift = -1;
+  if (aligned && C % vecn == 0 && ldcol % vecn == 0 && kh * kw < 64)
+    for (int sft = 0; sft < 16; ++sft)
+      if ((C / vecn) == (1 << sft)) cshift = sft;
+  const int64_t rows = B * Ho * Wo;
+  if (cshift >= 0) {                                       // warp per row, 16-byte vectors
+    const int grid = grid_for(rows * 32, 256, 16);
+    if (dtype == B200_BF16) B200_CHECK_CUDA(launch_pdl(im2col_vec_kernel<bf16_t>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, cshift));
+    else B200_CHECK_CUDA(launch_pdl(im2col_vec_kernel<float>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, cshift));
+  } else if (C <= 8 && ldcol % vecn == 0 && ldcol * es * IM_ROWS <= 48 * 1024) {   // conv1: rows staged in shared memory
+    const int grid = grid_for((rows + IM_ROWS - 1) / IM_ROWS * 256, 256, 8);
+    const size_t smem = (size_t)ldcol * es * IM_ROWS;
+    if (dtype == B200_BF16) B200_CHECK_CUDA(launch_pdl(im2col_smallc_kernel<bf16_t>, dim3(grid), dim3(256), smem, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol));
+    else B200_CHECK_CUDA(launch_pdl(im2col_smallc_kernel<float>, dim3(grid), dim3(256), smem, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol));
+  } else {                                                 // any other geometry: one thread per 4 channels / per element
+    const bool vec = C % 4 == 0 && aligned;
+    const int64_t items = rows * (vec ? ldcol / 4 : ldcol);
+    const int grid = grid_for(items, 256, 16);
+    const int kcols = (int)ldcol;
+    if (dtype == B200_BF16) {
+      if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 4>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+      else B200_CHECK_CUDA(launch_pdl(im2col_kernel<bf16_t, 1>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+    } else {
+      if (vec) B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 4>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+      else B200_CHECK_CUDA(launch_pdl(im2col_kernel<float, 1>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, kcols));
+    }
   }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -546,7 +707,7 @@ static int bn_check(const char* who, int64_t M, int64_t C, const float* scratch,
 }
 static inline int bn_blocks(int64_t M, int64_t C) {
   const int64_t lanes = BN_THREADS / (C / 4);
-  const int64_t want = (M + lanes * 8 - 1) / (lanes * 8);            // >= 8 rows per thread before splitting further
+  const int64_t want = (M + lanes * 16 - 1) / (lanes * 16);          // >= 16 rows per thread before splitting further
   const int64_t cap = std::min<int64_t>(BN_MAX_BLOCKS, (int64_t)sm_count() * 2);
   return (int)std::max<int64_t>(1, std::min(want, cap));
 }

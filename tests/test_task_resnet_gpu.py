@@ -73,8 +73,9 @@ def _check_checkpoints(tmp, oracle, steps, out):
     for k in so:
         if k.endswith("num_batches_tracked"):
             assert int(final[k]) == int(so[k]) == steps
-        elif "running" in k:                                  # forward-side buffers: plain rounding error
-            assert torch.allclose(final[k], so[k], rtol=1e-3, atol=1e-4), k
+        elif "running" in k:                                  # forward-side buffers: rounding error x the weight drift
+            rel = ((final[k] - so[k]).norm() / so[k].norm()).item()
+            assert rel <= 2e-3, (k, rel)
 
 
 def test_task_py_default_arch_single_gpu(tmp_path):
