@@ -12,6 +12,7 @@ back, so checkpoints are interchangeable with the reference's (`module.`-prefixe
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Tuple
 
@@ -314,7 +315,9 @@ class ConvTrainStep:
         self.dcol_ds = torch.zeros(max([B * c.Ho * c.Wo * c.Kp for c in downs] + [4]), **act)
         amax = max(B * c.Ho * c.Wo * c.cout for c in convs)
         xin = max([B * c.H * c.W * c.cin for c in convs if c is not layout.stem])
-        self.dy = torch.zeros(amax, **act)           # gradient wrt a conv output
+        # gradient wrt each conv output: one buffer per conv, because its wgrad GEMM runs on a side stream while the
+        # main stream already produces the next layer's gradient
+        self.dyc = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs}
         self.dz = torch.zeros(amax, **act)           # gradient wrt a block output after its ReLU mask
         self.dact = [torch.zeros(max(amax, xin), **act) for _ in range(3)]   # rotating: block-output / mid grads
         self.dlogits = torch.zeros(B, _round_up(layout.num_classes, 8), **act)
@@ -338,6 +341,10 @@ class ConvTrainStep:
         # ---- streams, step bookkeeping, DDP buckets
         self.main = torch.cuda.Stream(device=dev)
         self.comm_stream = torch.cuda.Stream(device=dev)
+        self.side = torch.cuda.Stream(device=dev)          # filter-gradient GEMMs, off the backward chain's critical path
+        self.side_wgrad = (not self.x3) and os.environ.get("B200STEP_SIDE_WGRAD", "1") != "0"
+        self._ev_dy = {c.name: torch.cuda.Event() for c in convs}
+        self._ev_wg = {c.name: torch.cuda.Event() for c in convs}
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -407,6 +414,9 @@ class ConvTrainStep:
         s, e, _ = self.buckets[bi]
         self._ev_ready[bi].record(self.main)
         self.comm_stream.wait_event(self._ev_ready[bi])
+        for k, ev in self._side_pending:                # filter gradients of this bucket still running on the side stream
+            if self.bucket_of[k] == bi:
+                self.comm_stream.wait_event(ev)
         self.comm.allreduce_sum(self.g[s:e], self.comm_stream)
         self._ev_done[bi].record(self.comm_stream)
         return 1
@@ -445,11 +455,22 @@ class ConvTrainStep:
             ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
                              stream=self.main)
         else:
+            wstream = self.main
+            if self.side_wgrad:
+                # dy is complete here: fork.  The wgrad GEMM only feeds the optimizer (and its DDP bucket), so it runs
+                # on the side stream under the dgrad / col2im / BatchNorm-backward chain, whose small kernels leave
+                # most SMs idle; `_join_side` / the bucket's all-reduce wait for its event.
+                self._ev_dy[c.name].record(self.main)
+                self.side.wait_event(self._ev_dy[c.name])
+                wstream = self.side
             if dcol is not None:
                 ops.linear_dgrad(dy, self._w(c.name), None, dcol, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
                 n += 1
             ops.linear_wgrad(dy, self.col[c.name][:M], gw, M=M, N=c.cout, K=c.Kp, deterministic=self.det,
-                             stream=self.main)
+                             stream=wstream)
+            if self.side_wgrad:
+                self._ev_wg[c.name].record(self.side)
+                self._side_pending.append((c.name + ".weight", self._ev_wg[c.name]))
         n += 1 + self._grad_done(c.name + ".weight")
         return n
 
@@ -519,6 +540,7 @@ class ConvTrainStep:
         lay, cfg = self.lay, self.cfg
         C = lay.num_classes
         self._pending = [bk[2] for bk in self.buckets]
+        self._side_pending = []
         n = self._load(b, row_idx, cursor, draws, ds)
         n += self._forward(b, True)
         feat = self._features
@@ -563,18 +585,20 @@ class ConvTrainStep:
             M, Cc = b * c2.Ho * c2.Wo, c2.cout
             free = [t for t in self.dact if t.data_ptr() != dout.data_ptr()]     # dout sits in one of the three
             mid, nxt = free[0], free[1]
-            dy = self.dy[: M * Cc].view(M, Cc)
+            dy = self.dyc[c2.name][:M]
             dz = self.dz[: M * Cc].view(M, Cc)
             n += self._bn_bwd(c2.bn, dout, self.a[c2.name][:M], self.yc[c2.name][:M], dy, dz)
             dcol = self.dcol[: M * c2.Kp].view(M, c2.Kp)
             n += self._conv_bwd(c2, dy, b, dcol)
             d_a1 = mid[: M * Cc].view(M, Cc)
             ops.col2im(dcol, None, d_a1, B=b, H=c2.H, W=c2.W, C=c2.cin, kh=3, kw=3, stride=1, pad=1, stream=self.main)
+            dy = self.dyc[c1.name][:M]
             n += 1 + self._bn_bwd(c1.bn, d_a1, self.a[c1.name][:M], self.yc[c1.name][:M], dy, None)
             dcol = self.dcol[: M * c1.Kp].view(M, c1.Kp)
             n += self._conv_bwd(c1, dy, b, dcol)
             Min = b * c1.H * c1.W
             if dn is not None:
+                dy = self.dyc[dn.name][:M]
                 n += self._bn_bwd(dn.bn, dz, None, self.yc[dn.name][:M], dy, None)
                 dcd = self.dcol_ds[: M * dn.Kp].view(M, dn.Kp)
                 n += self._conv_bwd(dn, dy, b, dcd)
@@ -595,10 +619,12 @@ class ConvTrainStep:
         free = [t for t in self.dact if t.data_ptr() != dout.data_ptr()]
         d_a0 = free[0][: M0 * 64].view(M0, 64)
         ops.maxpool_bwd(dout, self.taps, d_a0, B=b, H=st.Ho, W=st.Wo, C=64, stream=self.main)
-        dy0 = self.dy[: M0 * 64].view(M0, 64)
+        dy0 = self.dyc[st.name][:M0]
         n += 1 + self._bn_bwd("bn1", d_a0, self.a[st.name][:M0], self.yc[st.name][:M0], dy0, None)
         n += self._conv_bwd(st, dy0, b, None)
         # ---- optimizer.step() (task.py:312) once every bucket is reduced; the gradients are left zeroed (task.py:308)
+        for _, ev in self._side_pending:                 # join: every filter gradient is complete
+            self.main.wait_event(ev)
         if cfg.world > 1:
             for ev in self._ev_done:
                 self.main.wait_event(ev)
@@ -641,6 +667,7 @@ class ConvTrainStep:
 
         self.main.synchronize()
         self.comm_stream.synchronize()
+        self.side.synchronize()
         self.lib.graph_begin(self.main.cuda_stream)
         try:
             self.kernels_per_step = self._enqueue(self.B, self.row_idx, self.cursor, self._draws(), True)
@@ -702,6 +729,7 @@ class ConvTrainStep:
 
                 self.main.synchronize()
                 self.comm_stream.synchronize()
+                self.side.synchronize()
                 self.lib.graph_begin(self.main.cuda_stream)
                 try:
                     self._enqueue(B, None, None, self._stage_draws, False, self._stage)
@@ -732,6 +760,7 @@ class ConvTrainStep:
     def synchronize(self) -> None:
         self.main.synchronize()
         self.comm_stream.synchronize()
+        self.side.synchronize()
         bits = int(self.status.item())
         if bits:
             self.status.zero_()
@@ -803,6 +832,7 @@ class ConvTrainStep:
     def close(self) -> None:
         self.main.synchronize()
         self.comm_stream.synchronize()
+        self.side.synchronize()
         if self.graph is not None:
             self.lib.graph_destroy(self.graph)
             self.graph = None
