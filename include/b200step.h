@@ -163,8 +163,8 @@ int b200_ce_loss_grad(const void* logits, int64_t ldl, const int64_t* labels,
 
 /* ---- K-gemm-ce: the output layer and the loss as ONE kernel ------------------------------------
  * Replaces b200_linear_fwd (last nn.Linear, task.py:309) followed by b200_ce_loss_grad (task.py:310-311) without
- * ever storing the logits: z = x[M,K]·w[N,K]^T + bias (rounded to `dtype` exactly as the stored logits would have
- * been), loss_out[0] = mean_b(logsumexp(z_b) - z_b[y_b]), dlogits[M,N] = (softmax(z) - onehot(y)) * grad_scale,
+ * ever storing the logits: z = x[M,K]·w[N,K]^T + bias kept in fp32 (never rounded to `dtype`, because never stored),
+ * loss_out[0] = mean_b(logsumexp(z_b) - z_b[y_b]), dlogits[M,N] = (softmax(z) - onehot(y)) * grad_scale,
  * dbias[N] (nullable) = column sums of dlogits as stored.  Same semantics for grad_scale / loss_scale / accumulate /
  * ignore_index / n_valid / out-of-range labels as b200_ce_loss_grad.  N <= 1024 classes (a cluster of up to four
  * CTA pairs holds one softmax row in tensor memory); scratch: b200_linear_ce_scratch_floats(N) floats, contents
