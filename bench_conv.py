@@ -333,9 +333,23 @@ def run_b200(args, rank, local_rank, world, wl, peaks, ClockSampler, measure_tf3
         tensor_peak = tf32 / passes
         peak_note = f"TF32 peak measured in this run: {tf32:.1f} TFLOP/s" + (" / 3 passes" if passes > 1 else "")
     gem_tflops = flops["total"] * B / (gem_ms / 1e3) / 1e12
+    # DRAM bytes per launch from the ncu pass of scripts/gpu_ncu_resnet_traffic.sh (profiles/ncu_traffic.json)
+    gem_traffic = mem_traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            blob = json.load(fh)
+        tags = sorted(k for k in blob if k.startswith(args.workload + "@"))
+        if tags:
+            tab = {k: v for k, v in blob[tags[-1]].items() if not k.startswith("_")}
+            g = [v for k, v in tab.items() if k in ("gemm_kernel", "linear_ce_kernel")]
+            m = [v for k, v in tab.items() if k not in ("gemm_kernel", "linear_ce_kernel", "reduce_partials_kernel")]
+            gem_traffic = sum(v["dram_bytes"] for v in g) / max(1, sum(v["launches"] for v in g))
+            mem_traffic = sum(v["dram_bytes"] for v in m) / max(1, sum(v["launches"] for v in m))
     roof_tensor = {"bound": "tensor", "kernel": "gemm_kernel / linear_ce_kernel (all conv + fc GEMM launches of the step)",
                    "achieved": gem_tflops, "peak": tensor_peak, "unit": "TFLOP/s", "frac": gem_tflops / tensor_peak,
-                   "traffic": None, "share_of_step": gem_ms / total_ms, "share_of_step_ms": gem_ms / step_ms,
+                   "traffic": gem_traffic, "traffic_note": "mean DRAM bytes per GEMM launch of one step (ncu)",
+                   "share_of_step": gem_ms / total_ms, "share_of_step_ms": gem_ms / step_ms,
                    "kernel_ms": gem_ms, "launches_per_step": sum(r["per_step"] for r in gem),
                    "flops_basis": "2*Ho*Wo*Cout*kh*kw*Cin per conv, fwd + dgrad + wgrad (conv1: no dgrad)",
                    "peak_source": peak_note}
@@ -343,7 +357,10 @@ def run_b200(args, rank, local_rank, world, wl, peaks, ClockSampler, measure_tf3
     mem_gbs = mem_bytes / (mem_ms / 1e3) / 1e9
     roof_hbm = {"bound": "hbm", "kernel": "conv.cu kernels (im2col, col2im, BatchNorm, pooling) + K-opt, all launches of "
                 "the step", "achieved": mem_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": mem_gbs / peaks["hbm_gbs"], "traffic": None, "share_of_step": mem_ms / total_ms,
+                "frac": mem_gbs / peaks["hbm_gbs"], "traffic": mem_traffic,
+                "traffic_note": "mean DRAM bytes per launch of these kernels (ncu); below the algorithmic bytes because "
+                                "im2col matrices and activations are re-read from the 126 MB L2",
+                "share_of_step": mem_ms / total_ms,
                 "share_of_step_ms": mem_ms / step_ms, "kernel_ms": mem_ms,
                 "launches_per_step": sum(r["per_step"] for r in mem),
                 "bytes_basis": "every operand of every launch read or written once", "peak_source": peaks["source"] +
