@@ -297,6 +297,16 @@ int b200_image_augment(const uint8_t* images, const int64_t* labels, const int64
  * Ho = (H+2*pad-kh)/stride+1; columns [kh*kw*C, ldcol) are zero-filled.  (F.conv2d's unfold, torch/nn/modules/conv.py) */
 int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, int H, int W, int C, int kh, int kw, int stride,
                 int pad, int dtype, b200_stream_t stream);
+/* Convolution forward as an IMPLICIT GEMM (no col matrix): y[B*Ho*Wo, Cout] = conv2d(x NHWC, w) with w stored as
+ * Wg[Cout][ky][kx][c] (row stride ldw).  The tcgen05 GEMM's A tiles are fetched by im2col-mode TMA straight from x
+ * (padding halo zero-filled by the hardware).  C must be a multiple of 64 (bf16) / 32 (fp32); flags: B200_FLAG_RELU. */
+int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y, int64_t ldy, int64_t B, int H, int W, int C,
+                  int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags, b200_stream_t stream);
+/* Filter gradient of the same convolution, also without a col matrix: dw[Cout, kh*kw*C] (+)= dy^T . unfold(x), fp32
+ * (row stride lddw); flags: B200_FLAG_ACCUMULATE, B200_FLAG_DETERMINISTIC as for b200_linear_wgrad. */
+int b200_conv_wgrad(const void* dy, int64_t lddy, const void* x, float* dw, int64_t lddw, int64_t B, int H, int W,
+                    int C, int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags,
+                    b200_stream_t stream);
 /* The adjoint, as a gather: dx[b,h,w,c] = sum of the dcol entries that im2col filled from x[b,h,w,c], plus
  * add[b,h,w,c] when add != NULL (the gradient arriving over a residual connection).  C % 4 == 0. */
 int b200_col2im(const void* dcol, int64_t ldcol, const void* add, void* dx, int64_t B, int H, int W, int C, int kh,

@@ -252,6 +252,24 @@ def im2col(x, col, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: 
                      _stream(stream))
 
 
+def conv_fwd(x, w, y, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, Cout: int,
+             relu: bool = False, stream=None):
+    """y = conv2d(x NHWC, w[Cout, kh*kw*C]) as an implicit GEMM (im2col-mode TMA, no col matrix)."""
+    _cuda(x, w, y)
+    get_lib().conv_fwd(ptr(x), ptr(w), w.stride(0), ptr(y), y.stride(0), B, H, W, C, kh, kw, stride, pad, Cout,
+                       dtype_code(x.dtype), FLAG_RELU if relu else 0, _stream(stream))
+
+
+def conv_wgrad(dy, x, dw, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, Cout: int,
+               accumulate: bool = False, deterministic: bool = False, stream=None):
+    """dw[Cout, kh*kw*C] = dy^T . unfold(x NHWC) as an implicit GEMM (no col matrix)."""
+    _cuda(dy, x, dw)
+    get_lib().conv_wgrad(ptr(dy), dy.stride(0), ptr(x), ptr(dw), dw.stride(0), B, H, W, C, kh, kw, stride, pad, Cout,
+                         dtype_code(x.dtype),
+                         (FLAG_ACCUMULATE if accumulate else 0) | (FLAG_DETERMINISTIC if deterministic else 0),
+                         _stream(stream))
+
+
 def col2im(dcol, add, dx, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, stream=None):
     _cuda(dcol, add, dx)
     get_lib().col2im(ptr(dcol), dcol.stride(0), ptr(add), ptr(dx), B, H, W, C, kh, kw, stride, pad,

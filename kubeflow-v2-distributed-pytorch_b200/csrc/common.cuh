@@ -306,6 +306,27 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar_addr), "r"(c0), "r"(c1)
       : "memory");
 }
+// im2col-mode TMA loads (tensor map from make_tmap_im2col): (c, w, h, n) = channel offset and the first output pixel's
+// window origin, (ow, oh) = the filter tap
+__device__ __forceinline__ void tma_load_im2col_pair(void* smem_dst, const CUtensorMap* m, uint32_t leader_bar_addr,
+                                                     int32_t c, int32_t w, int32_t h, int32_t n, uint16_t ow,
+                                                     uint16_t oh) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar_addr), "r"(c), "r"(w), "r"(h),
+      "r"(n), "h"(ow), "h"(oh)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c,
+                                                int32_t w, int32_t h, int32_t n, uint16_t ow, uint16_t oh) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h),
+      "r"(n), "h"(ow), "h"(oh)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_slot, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
                "r"(ncols)

@@ -92,6 +92,56 @@ static int make_tmap(CUtensorMap* m, int tf32, const void* ptr, uint64_t inner, 
   return 0;
 }
 
+// ---- im2col-mode tensor map: the A operand of a convolution read straight from the NHWC activation ---------------
+// One TMA instruction then delivers `pixels` consecutive OUTPUT pixels (row-major over Wo, Ho, N — the GEMM's row
+// order) x `channels` input channels of ONE filter tap into a 128B-swizzled tile, zero-filling the padding halo: the
+// `col` matrix never exists.  Bounding box as in cuTensorMapEncodeIm2col: lower corner = -pad, upper corner =
+// pad - (k - 1); traversal stride = the convolution's stride.  Instruction coordinates: (c, w, h, n) = (channel offset,
+// q*stride - pad, p*stride - pad, image) and offsets (kx, ky).
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+static EncodeIm2colFn get_encode_im2col_fn() {
+  static EncodeIm2colFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &sym, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !sym) {
+    set_error("cudaGetDriverEntryPoint(cuTensorMapEncodeIm2col) failed: %s", cudaGetErrorString(e));
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeIm2colFn>(sym);
+  return fn;
+}
+static int make_tmap_im2col(CUtensorMap* m, int tf32, const void* x, int64_t B, int H, int W, int C, int kh, int kw,
+                            int stride, int pad, uint32_t channels, uint32_t pixels, bool mn_major = false) {
+  EncodeIm2colFn fn = get_encode_im2col_fn();
+  if (!fn) return 1;
+  const uint64_t es = tf32 ? 4 : 2;
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (C * es) % 16 == 0,
+               "conv operand %p must be 16-byte aligned with C*elemsize a multiple of 16", x);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t strides[3] = {C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+  int lower[2] = {-pad, -pad};
+  int upper[2] = {pad - (kw - 1), pad - (kh - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = fn(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                  const_cast<void*>(x), dims, strides, lower, upper, channels, pixels, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed with CUresult %d (B=%lld H=%d W=%d C=%d k=%dx%d s=%d p=%d)",
+               (int)r, (long long)B, H, W, C, kh, kw, stride, pad);
+  // drivers up to 13.1 set a descriptor bit that is wrong for tensors under 128 KiB (same correction as CUTLASS's
+  // make_im2col_tma_copy_desc)
+  int drv = 0;
+  if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 && (uint64_t)B * H * W * C * es < 131072)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return 0;
+}
+
 static int check_dims(int64_t M, int64_t N, int64_t K, int dtype) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "GEMM dims must be positive (M=%lld N=%lld K=%lld)", (long long)M,

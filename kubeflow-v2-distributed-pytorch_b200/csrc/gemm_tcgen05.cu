@@ -44,6 +44,10 @@ struct GemmParams {
   long long ld_idx;
   long long emb_rows;
   int emb_shift;             // log2(embedding width)
+  // convolution as implicit GEMM: the K-major A operand comes from an im2col-mode tensor map over the NHWC input
+  // (k-block kb = filter tap kb / cv_cpb, channels (kb % cv_cpb) * BLOCK_K ...); 0 = plain matrix A
+  int cv_on, cv_Ho, cv_Wo, cv_stride, cv_pad, cv_kw, cv_cpb;
+  int cv_C, cv_K;            // wgrad (MN-major B from the input): channels and kh*kw*C
 };
 
 // kCtas = 2: the two CTAs of a cluster form a pair (tcgen05 cta_group::2).  The pair owns a 256 x 256 tile: each CTA
@@ -125,6 +129,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int n0 = (tile % p.n_tiles) * BLOCK_N + rank * B_ROWS;     // this CTA's share of the B tile
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+        int cv_w = 0, cv_h = 0, cv_n = 0;       // implicit GEMM: window origin of this CTA's first output pixel
+        if (p.cv_on) {
+          const int q = m0 % p.cv_Wo, t = m0 / p.cv_Wo;
+          cv_w = q * p.cv_stride - p.cv_pad;
+          cv_h = (t % p.cv_Ho) * p.cv_stride - p.cv_pad;
+          cv_n = t / p.cv_Ho;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + s * STAGE_BYTES;
@@ -134,7 +145,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
             const uint32_t fb = smem_u32(&full_bar[s]) & 0xFEFFFFFFu;  // same offset in the leader CTA
             if constexpr (!kAMN) {
-              tma_load_2d_pair(sa, &tmA, fb, kb * BLOCK_K, m0);
+              if (p.cv_on) {
+                const int tap = kb / p.cv_cpb, ky = tap / p.cv_kw;
+                tma_load_im2col_pair(sa, &tmA, fb, (kb - tap * p.cv_cpb) * BLOCK_K, cv_w, cv_h, cv_n,
+                                     (uint16_t)(tap - ky * p.cv_kw), (uint16_t)ky);
+              } else {
+                tma_load_2d_pair(sa, &tmA, fb, kb * BLOCK_K, m0);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < BLOCK_M / EPR; ++j)
@@ -142,6 +159,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if constexpr (!kBMN) {
               tma_load_2d_pair(sb, &tmB, fb, kb * BLOCK_K, n0);
+            } else if (p.cv_on) {
+              // wgrad of a convolution: B(n' = filter column, k' = pixel) straight from the NHWC input; this k-block
+              // is BLOCK_K consecutive output pixels, each 128-byte column group one (tap, channel slice)
+              const int pix = kb * BLOCK_K, q = pix % p.cv_Wo, t = pix / p.cv_Wo;
+              const int bw = q * p.cv_stride - p.cv_pad, bh = (t % p.cv_Ho) * p.cv_stride - p.cv_pad, bn = t / p.cv_Ho;
+#pragma unroll
+              for (int j = 0; j < B_ROWS / EPR; ++j) {
+                const int col0 = n0 + j * EPR;
+                const bool in = col0 < p.cv_K;
+                const int tap = in ? col0 / p.cv_C : 0, ky = tap / p.cv_kw;
+                tma_load_im2col_pair(sb + j * MN_BOX_BYTES, &tmB, fb, in ? col0 - tap * p.cv_C : p.cv_C, bw, bh, bn,
+                                     (uint16_t)(tap - ky * p.cv_kw), (uint16_t)ky);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < B_ROWS / EPR; ++j)
@@ -150,7 +180,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } else {
             mbar_expect_tx(&full_bar[s], STAGE_BYTES);
             if constexpr (!kAMN) {
-              tma_load_2d(sa, &tmA, &full_bar[s], kb * BLOCK_K, m0);
+              if (p.cv_on) {
+                const int tap = kb / p.cv_cpb, ky = tap / p.cv_kw;
+                tma_load_im2col(sa, &tmA, &full_bar[s], (kb - tap * p.cv_cpb) * BLOCK_K, cv_w, cv_h, cv_n,
+                                (uint16_t)(tap - ky * p.cv_kw), (uint16_t)ky);
+              } else {
+                tma_load_2d(sa, &tmA, &full_bar[s], kb * BLOCK_K, m0);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < BLOCK_M / EPR; ++j)
@@ -158,6 +194,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if constexpr (!kBMN) {
               tma_load_2d(sb, &tmB, &full_bar[s], kb * BLOCK_K, n0);
+            } else if (p.cv_on) {
+              const int pix = kb * BLOCK_K, q = pix % p.cv_Wo, t = pix / p.cv_Wo;
+              const int bw = q * p.cv_stride - p.cv_pad, bh = (t % p.cv_Ho) * p.cv_stride - p.cv_pad, bn = t / p.cv_Ho;
+#pragma unroll
+              for (int j = 0; j < B_ROWS / EPR; ++j) {
+                const int col0 = n0 + j * EPR;
+                const bool in = col0 < p.cv_K;
+                const int tap = in ? col0 / p.cv_C : 0, ky = tap / p.cv_kw;
+                tma_load_im2col(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], in ? col0 - tap * p.cv_C : p.cv_C, bw, bh, bn,
+                                (uint16_t)(tap - ky * p.cv_kw), (uint16_t)ky);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < B_ROWS / EPR; ++j)
@@ -802,6 +849,39 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
               : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);
 }
 
+// Convolution forward as an implicit GEMM: y[B*Ho*Wo, Cout] = unfold(x)[.., kh*kw*C] . w[Cout, kh*kw*C]^T without the
+// unfold ever being stored — the A tiles come from an im2col-mode tensor map over the NHWC input.
+extern "C" int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y, int64_t ldy, int64_t B, int H, int W,
+                             int C, int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags,
+                             b200_stream_t stream) {
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && kh > 0 && kw > 0 && kh * kw < 256 && stride > 0 && pad >= 0 && C > 0 &&
+                   C % bk == 0, "conv_fwd: C=%d must be a multiple of %d (one 128-byte k-block per tap slice)", C, bk);
+  const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+  B200_REQUIRE(Ho > 0 && Wo > 0, "conv_fwd: empty output");
+  const int64_t M = B * Ho * Wo, K = (int64_t)kh * kw * C;
+  if (int r = check_dims(M, Cout, K, dtype)) return r;
+  B200_REQUIRE(ldw >= K, "conv_fwd: filter row stride %lld < kh*kw*C = %lld", (long long)ldw, (long long)K);
+  CUtensorMap ta, tb, tc;
+  if (int r = make_tmap_im2col(&ta, tf32, x, B, H, W, C, kh, kw, stride, pad, bk, BLOCK_M)) return r;
+  if (int r = make_tmap(&tb, tf32, w, K, Cout, ldw, bk, BLOCK_N / gemm_ctas())) return r;
+  if (int r = make_tmap(&tc, tf32, y, Cout, M, ldy, bk, 32, false, true)) return r;
+  GemmParams p{};
+  p.M = (int)M; p.N = (int)Cout;
+  const int tile_m = BLOCK_M * gemm_ctas();
+  p.k_blocks = (int)(K / bk);
+  p.m_tiles = (int)((M + tile_m - 1) / tile_m);
+  p.n_tiles = (int)((Cout + BLOCK_N - 1) / BLOCK_N);
+  p.splits = 1; p.kb_per_split = p.k_blocks;
+  p.out = y; p.ldo = ldy; p.flags = flags & (B200_FLAG_RELU | B200_FLAG_REVERSE_M); p.dscale = 1.f;
+  p.cv_on = 1; p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_stride = stride; p.cv_pad = pad; p.cv_kw = kw; p.cv_cpb = C / bk;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, tc, p, st)
+              : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);
+}
+
 extern "C" int b200_linear_dgrad(const void* dy, int64_t lddy, const void* w, int64_t ldw, const void* act,
                                  int64_t ldact, void* dx, int64_t lddx, int64_t M, int64_t N, int64_t K,
                                  int dtype, int flags, float dscale, const uint32_t* relu_mask, int64_t ldmask,
@@ -920,6 +1000,48 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
     // split-K partial tiles are summed with red.add: start from zero
     B200_CHECK_CUDA(cudaMemset2DAsync(dw, lddw * sizeof(float), 0, K * sizeof(float), N, st));
   }
+  return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
+              : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st);
+}
+
+// Filter gradient of a convolution as an implicit GEMM: dw[Cout, kh*kw*C] (+)= dy[B*Ho*Wo, Cout]^T . unfold(x), with the
+// unfold read by im2col-mode TMA from the NHWC input (the col matrix of the forward pass is not needed either).
+extern "C" int b200_conv_wgrad(const void* dy, int64_t lddy, const void* x, float* dw, int64_t lddw, int64_t B, int H,
+                               int W, int C, int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags,
+                               b200_stream_t stream) {
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64;   // output pixels per stage
+  const int epr = tf32 ? 32 : 64;  // filter columns per 128-byte group
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && kh > 0 && kw > 0 && kh * kw < 256 && stride > 0 && pad >= 0 && C > 0 &&
+                   C % epr == 0, "conv_wgrad: C=%d must be a multiple of %d", C, epr);
+  const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+  B200_REQUIRE(Ho > 0 && Wo > 0, "conv_wgrad: empty output");
+  const int64_t M = B * Ho * Wo, K = (int64_t)kh * kw * C, N = Cout;
+  if (int r = check_dims(M, N, K, dtype)) return r;
+  B200_REQUIRE(lddw >= K && lddw % 4 == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
+               "conv_wgrad output must be 16-byte aligned with lddw %% 4 == 0 and lddw >= kh*kw*C");
+  CUtensorMap ta, tb;
+  if (int r = make_tmap(&ta, tf32, dy, N, M, lddy, epr, bk, true)) return r;
+  if (int r = make_tmap_im2col(&tb, tf32, x, B, H, W, C, kh, kw, stride, pad, epr, bk, true)) return r;
+  GemmParams p{};
+  p.M = (int)N; p.N = (int)K;
+  const int tile_m = BLOCK_M * gemm_ctas();
+  p.k_blocks = (int)((M + bk - 1) / bk);
+  p.m_tiles = (int)((N + tile_m - 1) / tile_m);
+  p.n_tiles = (int)((K + BLOCK_N - 1) / BLOCK_N);
+  const int tiles = p.m_tiles * p.n_tiles;
+  int splits = (sm_count() / gemm_ctas()) / tiles;
+  if (splits < 1 || (flags & B200_FLAG_DETERMINISTIC)) splits = 1;
+  if (splits > p.k_blocks) splits = p.k_blocks;
+  p.kb_per_split = (p.k_blocks + splits - 1) / splits;
+  p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+  p.out = dw; p.ldo = lddw; p.flags = flags; p.dscale = 1.f;
+  p.cv_on = 1; p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_stride = stride; p.cv_pad = pad; p.cv_kw = kw; p.cv_cpb = C / bk;
+  p.cv_C = C; p.cv_K = (int)K;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p.splits > 1 && !(flags & B200_FLAG_ACCUMULATE))
+    B200_CHECK_CUDA(cudaMemset2DAsync(dw, lddw * sizeof(float), 0, K * sizeof(float), N, st));
   return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
               : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st);
 }

@@ -286,3 +286,71 @@ def test_augment_reports_a_bad_sample_index(ops):
     torch.cuda.synchronize()
     assert int(word.item()) & ops.STATUS_BAD_ROW_INDEX
     word.zero_()
+
+
+IMPLICIT_GEOMS = [
+    # B, H, C, k, stride, pad, Cout
+    (32, 8, 64, 3, 1, 1, 64), (32, 8, 64, 3, 2, 1, 128), (32, 8, 64, 1, 2, 0, 128), (32, 2, 256, 3, 2, 1, 512),
+    (32, 1, 512, 3, 1, 1, 512), (16, 4, 128, 3, 1, 1, 128), (3, 5, 64, 3, 1, 1, 72), (1024, 8, 64, 3, 1, 1, 64),
+    (2, 3, 128, 3, 2, 1, 64),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["tf32", "bf16"])
+@pytest.mark.parametrize("B,H,C,k,stride,pad,Cout", IMPLICIT_GEOMS)
+def test_implicit_gemm_convolution_forward(ops, dtype, B, H, C, k, stride, pad, Cout):
+    """b200_conv_fwd (A tiles by im2col-mode TMA, no col matrix) against the explicit im2col + GEMM path, which must
+    agree BIT FOR BIT (same operand bytes reach the same MMAs in the same order), and against F.conv2d."""
+    from b200step.convnet import filter_to_gemm
+
+    g = torch.Generator().manual_seed(8)
+    x = torch.randn(B, C, H, H, generator=g).to(dtype)
+    w = (torch.randn(Cout, C, k, k, generator=g) / (C * k * k) ** 0.5).to(dtype)
+    ref = F.conv2d(x.float(), w.float(), stride=stride, padding=pad)
+    Ho = ops.conv_out_size(H, k, stride, pad)
+    M, K = B * Ho * Ho, k * k * C
+    wg = filter_to_gemm(w, K).cuda()
+    xg = _nhwc(x)
+    col = torch.empty(M, K, dtype=dtype, device="cuda")
+    y_explicit = torch.empty(M, Cout, dtype=dtype, device="cuda")
+    ops.im2col(xg, col, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad)
+    ops.linear_fwd(col, wg, None, y_explicit, M=M, N=Cout, K=K, relu=False)
+    y = torch.full((M, Cout), 9.0, dtype=dtype, device="cuda")
+    ops.conv_fwd(xg, wg, y, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout)
+    torch.cuda.synchronize()
+    assert torch.equal(y, y_explicit)
+    rt = 2e-2 if dtype == torch.bfloat16 else 5e-3
+    assert torch.allclose(_nchw(y, B, Ho, Ho, Cout), ref, rtol=rt, atol=rt)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["tf32", "bf16"])
+@pytest.mark.parametrize("B,H,C,k,stride,pad,Cout", IMPLICIT_GEOMS)
+def test_implicit_gemm_filter_gradient(ops, dtype, B, H, C, k, stride, pad, Cout):
+    """b200_conv_wgrad (B tiles by im2col-mode TMA) against the explicit dy^T . col GEMM — bit for bit in deterministic
+    mode — and against autograd."""
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(B, C, H, H, generator=g).to(dtype)
+    wr = (torch.randn(Cout, C, k, k, generator=g) / (C * k * k) ** 0.5).requires_grad_(True)
+    yr = F.conv2d(x.float(), wr, stride=stride, padding=pad)
+    dyr = torch.randn(yr.shape, generator=g).to(dtype)
+    yr.backward(dyr.float())
+    from b200step.convnet import gemm_to_filter
+
+    Ho = ops.conv_out_size(H, k, stride, pad)
+    M, K = B * Ho * Ho, k * k * C
+    xg, dy = _nhwc(x), _nhwc(dyr).view(M, Cout)
+    col = torch.empty(M, K, dtype=dtype, device="cuda")
+    ops.im2col(xg, col, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad)
+    dw_explicit = torch.empty(Cout, K, dtype=torch.float32, device="cuda")
+    ops.linear_wgrad(dy, col, dw_explicit, M=M, N=Cout, K=K, deterministic=True)
+    dw = torch.full((Cout, K), 5.0, dtype=torch.float32, device="cuda")
+    ops.conv_wgrad(dy, xg, dw, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout, deterministic=True)
+    torch.cuda.synchronize()
+    assert torch.equal(dw, dw_explicit)
+    dw2 = torch.full((Cout, K), 5.0, dtype=torch.float32, device="cuda")      # default: batch dimension split, atomics
+    ops.conv_wgrad(dy, xg, dw2, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout)
+    rt = 2e-2 if dtype == torch.bfloat16 else 5e-3
+    scale = wr.grad.abs().max().item()
+    for t in (dw, dw2):
+        got = gemm_to_filter(t.cpu(), (Cout, C, k, k))
+        assert (got - wr.grad).abs().max().item() <= rt * scale
