@@ -138,7 +138,7 @@ def profile_kernels(eng, B):
     x3 = 3 if eng.x3 else 1
     names = ["image_augment", "im2col", "col2im", "bn_fwd_stats", "bn_fwd_apply", "bn_bwd_reduce", "bn_bwd_apply",
              "maxpool_fwd", "maxpool_bwd", "avgpool_fwd", "avgpool_bwd", "linear_fwd", "linear_ce", "linear_dgrad",
-             "linear_wgrad", "sgd_step", "adam_step", "split_tf32"]
+             "linear_wgrad", "conv_fwd", "conv_wgrad", "sgd_step", "adam_step", "split_tf32"]
     orig = {n: getattr(ops, n) for n in names}
     records = []
 
@@ -149,6 +149,11 @@ def profile_kernels(eng, B):
             return "gemm_dgrad", {"flops": 2.0 * k["M"] * (k["N"] // x3) * k["K"]}
         if name == "linear_wgrad":
             return "gemm_wgrad", {"flops": 2.0 * (k["M"] // x3) * k["N"] * k["K"]}
+        if name in ("conv_fwd", "conv_wgrad"):
+            Ho = ops.conv_out_size(k["H"], k["kh"], k["stride"], k["pad"])
+            Wo = ops.conv_out_size(k["W"], k["kw"], k["stride"], k["pad"])
+            return ("gemm_fwd" if name == "conv_fwd" else "gemm_wgrad"), \
+                {"flops": 2.0 * k["B"] * Ho * Wo * k["Cout"] * k["kh"] * k["kw"] * k["C"]}
         if name == "image_augment":
             return name, {"bytes": k["batch"] * k["H"] * k["W"] * 3 * (1 + es)}
         if name == "im2col":

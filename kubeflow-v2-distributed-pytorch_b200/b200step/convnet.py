@@ -299,7 +299,14 @@ class ConvTrainStep:
         self.convs = {c.name: c for c in convs}
         self.x0 = torch.zeros(B * layout.image * layout.image, 3, **act)
         self.y = torch.zeros(B, dtype=torch.int64, device=dev)
-        self.col = {c.name: torch.zeros(B * c.Ho * c.Wo, c.Kp, **act) for c in convs}       # kept for wgrad
+        # Implicit GEMM (b200_conv_fwd / b200_conv_wgrad: A / B tiles by im2col-mode TMA straight from the NHWC
+        # activation) for every conv whose channel count fills whole 128-byte k-blocks; conv1 (C = 3) and the 3xTF32
+        # mode (which needs hi/lo copies of the unfolded operand) keep the explicit col matrix.
+        vec = 64 if self.dt == torch.bfloat16 else 32
+        self.implicit = {c.name: (not self.x3) and c.cin % vec == 0 and c.K == c.Kp and
+                         os.environ.get("B200STEP_IMPLICIT_CONV", "1") != "0" for c in convs}
+        self.col = {c.name: torch.zeros(B * c.Ho * c.Wo, c.Kp, **act) for c in convs if not self.implicit[c.name]}
+        self.xin: Dict[str, torch.Tensor] = {}          # implicit convs: the input activation seen in forward
         self.yc = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs}      # conv output (pre-BN)
         self.a = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs if ".downsample" not in c.name}
         self.sc = {b.name: torch.zeros_like(self.yc[b.down.name]) for b in layout.blocks if b.down is not None}
@@ -425,6 +432,11 @@ class ConvTrainStep:
     def _conv_fwd(self, c: ConvDesc, x: torch.Tensor, rows_b: int) -> int:
         """yc[c] = conv(x) for `rows_b` images: im2col + GEMM (+ operand split in fp32 mode)."""
         M = rows_b * c.Ho * c.Wo
+        if self.implicit[c.name]:
+            self.xin[c.name] = x
+            ops.conv_fwd(x, self._w(c.name), self.yc[c.name][:M], B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k,
+                         stride=c.stride, pad=c.pad, Cout=c.cout, stream=self.main)
+            return 1
         col, y = self.col[c.name][:M], self.yc[c.name][:M]
         ops.im2col(x, col, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, stride=c.stride, pad=c.pad, stream=self.main)
         n = 2
@@ -466,8 +478,12 @@ class ConvTrainStep:
             if dcol is not None:
                 ops.linear_dgrad(dy, self._w(c.name), None, dcol, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
                 n += 1
-            ops.linear_wgrad(dy, self.col[c.name][:M], gw, M=M, N=c.cout, K=c.Kp, deterministic=self.det,
-                             stream=wstream)
+            if self.implicit[c.name]:
+                ops.conv_wgrad(dy, self.xin[c.name], gw, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k,
+                               stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det, stream=wstream)
+            else:
+                ops.linear_wgrad(dy, self.col[c.name][:M], gw, M=M, N=c.cout, K=c.Kp, deterministic=self.det,
+                                 stream=wstream)
             if self.side_wgrad:
                 self._ev_wg[c.name].record(self.side)
                 self._side_pending.append((c.name + ".weight", self._ev_wg[c.name]))
