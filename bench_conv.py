@@ -138,7 +138,7 @@ def profile_kernels(eng, B):
     x3 = 3 if eng.x3 else 1
     names = ["image_augment", "im2col", "col2im", "bn_fwd_stats", "bn_fwd_apply", "bn_bwd_reduce", "bn_bwd_apply",
              "maxpool_fwd", "maxpool_bwd", "avgpool_fwd", "avgpool_bwd", "linear_fwd", "linear_ce", "linear_dgrad",
-             "linear_wgrad", "conv_fwd", "conv_wgrad", "sgd_step", "adam_step", "split_tf32"]
+             "linear_wgrad", "conv_fwd", "conv_wgrad", "conv_dgrad", "sgd_step", "adam_step", "split_tf32"]
     orig = {n: getattr(ops, n) for n in names}
     records = []
 
@@ -154,6 +154,8 @@ def profile_kernels(eng, B):
             Wo = ops.conv_out_size(k["W"], k["kw"], k["stride"], k["pad"])
             return ("gemm_fwd" if name == "conv_fwd" else "gemm_wgrad"), \
                 {"flops": 2.0 * k["B"] * Ho * Wo * k["Cout"] * k["kh"] * k["kw"] * k["C"]}
+        if name == "conv_dgrad":
+            return "gemm_dgrad", {"flops": 2.0 * k["B"] * k["H"] * k["W"] * k["C"] * k["kh"] * k["kw"] * k["Cout"]}
         if name == "image_augment":
             return name, {"bytes": k["batch"] * k["H"] * k["W"] * 3 * (1 + es)}
         if name == "im2col":

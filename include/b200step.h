@@ -302,6 +302,11 @@ int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, int H, int W
  * (padding halo zero-filled by the hardware).  C must be a multiple of 64 (bf16) / 32 (fp32); flags: B200_FLAG_RELU. */
 int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y, int64_t ldy, int64_t B, int H, int W, int C,
                   int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags, b200_stream_t stream);
+/* Input gradient of a STRIDE-1 convolution without the dcol matrix and the col2im pass: dx[B*H*W, C] = conv2d(dy,
+ * flipped filter, padding k-1-pad); dy is [B, Ho, Wo, Cout] NHWC, w the same Wg[Cout][ky][kx][c] the forward uses (read
+ * as an MN-major operand at the flipped tap).  Cout a multiple of 64 (bf16) / 32 (fp32), square filters. */
+int b200_conv_dgrad(const void* dy, const void* w, int64_t ldw, void* dx, int64_t lddx, int64_t B, int H, int W, int C,
+                    int kh, int kw, int pad, int64_t Cout, int dtype, b200_stream_t stream);
 /* Filter gradient of the same convolution, also without a col matrix: dw[Cout, kh*kw*C] (+)= dy^T . unfold(x), fp32
  * (row stride lddw); flags: B200_FLAG_ACCUMULATE, B200_FLAG_DETERMINISTIC as for b200_linear_wgrad. */
 int b200_conv_wgrad(const void* dy, int64_t lddy, const void* x, float* dw, int64_t lddw, int64_t B, int H, int W,
@@ -327,13 +332,15 @@ int b200_bn_fwd_stats(const void* y, int64_t M, int64_t C, float eps, float mome
 int b200_bn_fwd_apply(const void* y, const void* res, void* out, int64_t M, int64_t C, const float* mean,
                       const float* invstd, const float* gamma, const float* beta, int relu, int dtype,
                       b200_stream_t stream);
-/* Backward of the same (task.py:311).  dz = dout * (out > 0) when out != NULL (the ReLU that followed), else dout.
+/* Backward of the same (task.py:311).  The incoming gradient is dout (+ dout2 when dout2 != NULL: the two branches that
+ * meet at a residual connection, summed on the fly instead of by a separate pass).
+ * dz = dout * (out > 0) when out != NULL (the ReLU that followed), else dout.
  * _reduce: dbeta[c] = sum_m dz, dgamma[c] = sum_m dz * xhat (fixed order);
  * _apply:  dy = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M); dz_out (nullable) receives dz for the residual branch. */
-int b200_bn_bwd_reduce(const void* dout, const void* out, const void* y, int64_t M, int64_t C, const float* mean,
+int b200_bn_bwd_reduce(const void* dout, const void* dout2, const void* out, const void* y, int64_t M, int64_t C, const float* mean,
                        const float* invstd, float* dgamma, float* dbeta, float* scratch, int64_t scratch_floats,
                        int dtype, b200_stream_t stream);
-int b200_bn_bwd_apply(const void* dout, const void* out, const void* y, void* dy, void* dz_out, int64_t M, int64_t C,
+int b200_bn_bwd_apply(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz_out, int64_t M, int64_t C,
                       const float* mean, const float* invstd, const float* gamma, const float* dgamma,
                       const float* dbeta, int dtype, b200_stream_t stream);
 
@@ -341,7 +348,7 @@ int b200_bn_bwd_apply(const void* dout, const void* out, const void* y, void* dy
  * (first maximum in row-major window order, NaN wins — aten's rule) for the backward gather. */
 int b200_maxpool_fwd(const void* x, void* out, uint8_t* taps, int64_t B, int H, int W, int C, int k, int stride,
                      int pad, int dtype, b200_stream_t stream);
-int b200_maxpool_bwd(const void* dout, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
+int b200_maxpool_bwd(const void* dout, const void* dout2, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
                      int stride, int pad, int dtype, b200_stream_t stream);
 /* nn.AdaptiveAvgPool2d((1,1)) on NHWC: out[b, c] = mean over the HW pixels; bwd: dx[b, p, c] = dout[b, c] / HW */
 int b200_avgpool_fwd(const void* x, void* out, int64_t B, int HW, int C, int dtype, b200_stream_t stream);

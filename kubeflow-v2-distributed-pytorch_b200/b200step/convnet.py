@@ -318,14 +318,12 @@ class ConvTrainStep:
         # ---- gradients of activations: scratch shared by all layers (sizes: the largest user)
         big = max(B * c.Ho * c.Wo * c.Kp for c in convs if c is not layout.stem)
         self.dcol = torch.zeros(big, **act)
-        downs = [b.down for b in layout.blocks if b.down is not None]
-        self.dcol_ds = torch.zeros(max([B * c.Ho * c.Wo * c.Kp for c in downs] + [4]), **act)
         amax = max(B * c.Ho * c.Wo * c.cout for c in convs)
         xin = max([B * c.H * c.W * c.cin for c in convs if c is not layout.stem])
         # gradient wrt each conv output: one buffer per conv, because its wgrad GEMM runs on a side stream while the
         # main stream already produces the next layer's gradient
         self.dyc = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs}
-        self.dz = torch.zeros(amax, **act)           # gradient wrt a block output after its ReLU mask
+        self.dz2 = [torch.zeros(amax, **act) for _ in range(2)]   # gradient wrt a block output after its ReLU mask
         self.dact = [torch.zeros(max(amax, xin), **act) for _ in range(3)]   # rotating: block-output / mid grads
         self.dlogits = torch.zeros(B, _round_up(layout.num_classes, 8), **act)
         self.dfeat = torch.zeros(B, 512, **act)
@@ -450,8 +448,39 @@ class ConvTrainStep:
             ops.linear_fwd(col, self._w(c.name), None, y, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
         return n
 
-    def _conv_bwd(self, c: ConvDesc, dy: torch.Tensor, rows_b: int, dcol: Optional[torch.Tensor]) -> int:
-        """Filter gradient of conv c into the flat gradient buffer and, when `dcol` is given, dcol = dy . Wg."""
+    def _implicit_dgrad(self, c: ConvDesc) -> bool:
+        """b200_conv_dgrad applies: implicit conv, stride 1, Cout in whole 128-byte k-blocks."""
+        vec = 64 if self.dt == torch.bfloat16 else 32
+        return self.implicit[c.name] and c.stride == 1 and c.cout % vec == 0 and \
+            os.environ.get("B200STEP_IMPLICIT_DGRAD", "1") != "0"
+
+    def _conv_bwd_input(self, c: ConvDesc, dy: torch.Tensor, rows_b: int, dx: torch.Tensor, add, dyk=None) -> int:
+        """dx = gradient of conv c wrt its input (+ add).  Implicit GEMM over dy when it applies, else dgrad GEMM into
+        the dcol scratch + col2im."""
+        M = rows_b * c.Ho * c.Wo
+        if add is None and self._implicit_dgrad(c):
+            ops.conv_dgrad(dy, self._w(c.name), dx, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, pad=c.pad,
+                           Cout=c.cout, stream=self.main)
+            return 1
+        n = 2
+        dcol = self.dcol[: M * c.Kp].view(M, c.Kp)
+        if self.x3:
+            if dyk is None:
+                dyk = self.dyk[: M * 3 * c.cout].view(M, 3 * c.cout)
+                ops.split_tf32(dy, dyk, ops.SPLIT_LEFT, None, 0, rows=M, cols=c.cout, stream=self.main)
+                n += 1
+            ops.linear_dgrad(dyk, self.wr[c.name], None, dcol, M=M, N=3 * c.cout, K=c.Kp, relu=False, stream=self.main)
+        else:
+            ops.linear_dgrad(dy, self._w(c.name), None, dcol, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
+        ops.col2im(dcol, add, dx, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, stride=c.stride, pad=c.pad,
+                   stream=self.main)
+        return n
+
+    def _conv_bwd(self, c: ConvDesc, dy: torch.Tensor, rows_b: int, dx: Optional[torch.Tensor], add,
+                  defer_input: bool = False) -> int:
+        """Backward of conv c given dy: the filter gradient into the flat gradient buffer and, when `dx` is given, the
+        input gradient (+ add) into dx.  `defer_input`: only the filter gradient now (the caller issues
+        `_conv_bwd_input` later, e.g. after the shortcut branch produced `add`)."""
         M = rows_b * c.Ho * c.Wo
         gw = self._pv(c.name + ".weight", self.g)
         n = 0
@@ -460,24 +489,21 @@ class ConvTrainStep:
             dyr = self.dyr[: 3 * M * c.cout].view(3 * M, c.cout)
             ops.split_tf32(dy, dyk, ops.SPLIT_LEFT, dyr, ops.SPLIT_LEFT, rows=M, cols=c.cout, stream=self.main)
             n += 1
-            if dcol is not None:
-                ops.linear_dgrad(dyk, self.wr[c.name], None, dcol, M=M, N=3 * c.cout, K=c.Kp, relu=False,
-                                 stream=self.main)
-                n += 1
             ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
                              stream=self.main)
+            if dx is not None and not defer_input:
+                n += self._conv_bwd_input(c, dy, rows_b, dx, add, dyk)
         else:
             wstream = self.main
             if self.side_wgrad:
                 # dy is complete here: fork.  The wgrad GEMM only feeds the optimizer (and its DDP bucket), so it runs
                 # on the side stream under the dgrad / col2im / BatchNorm-backward chain, whose small kernels leave
-                # most SMs idle; `_join_side` / the bucket's all-reduce wait for its event.
+                # most SMs idle; the join before K-opt / the bucket's all-reduce wait for its event.
                 self._ev_dy[c.name].record(self.main)
                 self.side.wait_event(self._ev_dy[c.name])
                 wstream = self.side
-            if dcol is not None:
-                ops.linear_dgrad(dy, self._w(c.name), None, dcol, M=M, N=c.cout, K=c.Kp, relu=False, stream=self.main)
-                n += 1
+            if dx is not None and not defer_input:
+                n += self._conv_bwd_input(c, dy, rows_b, dx, add)
             if self.implicit[c.name]:
                 ops.conv_wgrad(dy, self.xin[c.name], gw, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k,
                                stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det, stream=wstream)
@@ -503,12 +529,12 @@ class ConvTrainStep:
                          relu=relu, stream=self.main)
         return n
 
-    def _bn_bwd(self, bn: str, dout: torch.Tensor, out, y: torch.Tensor, dy: torch.Tensor, dz) -> int:
+    def _bn_bwd(self, bn: str, dout: torch.Tensor, out, y: torch.Tensor, dy: torch.Tensor, dz, dout2=None) -> int:
         M, C = y.shape
         mean, invstd, _, _, _ = self._bn(bn)
         dg, db = self._pv(bn + ".weight", self.g), self._pv(bn + ".bias", self.g)
-        ops.bn_bwd_reduce(dout, out, y, mean, invstd, dg, db, self.bn_scratch, M=M, C=C, stream=self.main)
-        ops.bn_bwd_apply(dout, out, y, dy, dz, mean, invstd, self._pv(bn + ".weight"), dg, db, M=M, C=C,
+        ops.bn_bwd_reduce(dout, out, y, mean, invstd, dg, db, self.bn_scratch, M=M, C=C, dout2=dout2, stream=self.main)
+        ops.bn_bwd_apply(dout, out, y, dy, dz, mean, invstd, self._pv(bn + ".weight"), dg, db, M=M, C=C, dout2=dout2,
                          stream=self.main)
         return 2 + self._grad_done(bn + ".bias") + self._grad_done(bn + ".weight")
 
@@ -596,48 +622,45 @@ class ConvTrainStep:
             n += 1
         else:
             dout = dfeat
-        for blk in reversed(lay.blocks):
+        dout2 = None                       # second branch of the incoming gradient (summed by its consumer)
+        for bi, blk in enumerate(reversed(lay.blocks)):
             c1, c2, dn = blk.conv1, blk.conv2, blk.down
             M, Cc = b * c2.Ho * c2.Wo, c2.cout
             free = [t for t in self.dact if t.data_ptr() != dout.data_ptr()]     # dout sits in one of the three
             mid, nxt = free[0], free[1]
             dy = self.dyc[c2.name][:M]
-            dz = self.dz[: M * Cc].view(M, Cc)
-            n += self._bn_bwd(c2.bn, dout, self.a[c2.name][:M], self.yc[c2.name][:M], dy, dz)
-            dcol = self.dcol[: M * c2.Kp].view(M, c2.Kp)
-            n += self._conv_bwd(c2, dy, b, dcol)
+            dz = self.dz2[bi & 1][: M * Cc].view(M, Cc)     # alternating: the previous block's dz may be `dout2` here
+            n += self._bn_bwd(c2.bn, dout, self.a[c2.name][:M], self.yc[c2.name][:M], dy, dz, dout2)
             d_a1 = mid[: M * Cc].view(M, Cc)
-            ops.col2im(dcol, None, d_a1, B=b, H=c2.H, W=c2.W, C=c2.cin, kh=3, kw=3, stride=1, pad=1, stream=self.main)
+            n += self._conv_bwd(c2, dy, b, d_a1, None)
             dy = self.dyc[c1.name][:M]
-            n += 1 + self._bn_bwd(c1.bn, d_a1, self.a[c1.name][:M], self.yc[c1.name][:M], dy, None)
-            dcol = self.dcol[: M * c1.Kp].view(M, c1.Kp)
-            n += self._conv_bwd(c1, dy, b, dcol)
+            n += self._bn_bwd(c1.bn, d_a1, self.a[c1.name][:M], self.yc[c1.name][:M], dy, None)
             Min = b * c1.H * c1.W
-            if dn is not None:
-                dy = self.dyc[dn.name][:M]
-                n += self._bn_bwd(dn.bn, dz, None, self.yc[dn.name][:M], dy, None)
-                dcd = self.dcol_ds[: M * dn.Kp].view(M, dn.Kp)
-                n += self._conv_bwd(dn, dy, b, dcd)
-                add = mid[: Min * c1.cin].view(Min, c1.cin)        # d_a1 is consumed: reuse its buffer
-                ops.col2im(dcd, None, add, B=b, H=dn.H, W=dn.W, C=dn.cin, kh=1, kw=1, stride=dn.stride, pad=0,
-                           stream=self.main)
-                n += 1
-            else:
-                add = dz
             dx = nxt[: Min * c1.cin].view(Min, c1.cin)
-            ops.col2im(dcol, add, dx, B=b, H=c1.H, W=c1.W, C=c1.cin, kh=3, kw=3, stride=c1.stride, pad=1,
-                       stream=self.main)
-            n += 1
-            dout = dx
+            if dn is not None:
+                # projection shortcut: its own BatchNorm + 1x1 stride-2 conv backward, then both branches into dx
+                n += self._conv_bwd(c1, dy, b, None, None, defer_input=True)
+                dyd = self.dyc[dn.name][:M]
+                n += self._bn_bwd(dn.bn, dz, None, self.yc[dn.name][:M], dyd, None)
+                add = mid[: Min * c1.cin].view(Min, c1.cin)        # d_a1 is consumed: reuse its buffer
+                n += self._conv_bwd(dn, dyd, b, add, None)
+                n += self._conv_bwd_input(c1, dy, b, dx, add)
+                dout, dout2 = dx, None
+            elif self._implicit_dgrad(c1):
+                n += self._conv_bwd(c1, dy, b, dx, None)             # dx = main branch only ...
+                dout, dout2 = dx, dz                                 # ... the identity branch (dz) is added by the consumer
+            else:
+                n += self._conv_bwd(c1, dy, b, dx, dz)
+                dout, dout2 = dx, None
         # ---- stem: maxpool, bn1 (+ReLU), conv1's filter gradient (the input needs no gradient)
         st = lay.stem
         M0 = b * st.Ho * st.Wo
         free = [t for t in self.dact if t.data_ptr() != dout.data_ptr()]
         d_a0 = free[0][: M0 * 64].view(M0, 64)
-        ops.maxpool_bwd(dout, self.taps, d_a0, B=b, H=st.Ho, W=st.Wo, C=64, stream=self.main)
+        ops.maxpool_bwd(dout, self.taps, d_a0, B=b, H=st.Ho, W=st.Wo, C=64, dout2=dout2, stream=self.main)
         dy0 = self.dyc[st.name][:M0]
         n += 1 + self._bn_bwd("bn1", d_a0, self.a[st.name][:M0], self.yc[st.name][:M0], dy0, None)
-        n += self._conv_bwd(st, dy0, b, None)
+        n += self._conv_bwd(st, dy0, b, None, None)
         # ---- optimizer.step() (task.py:312) once every bucket is reduced; the gradients are left zeroed (task.py:308)
         for _, ev in self._side_pending:                 # join: every filter gradient is complete
             self.main.wait_event(ev)

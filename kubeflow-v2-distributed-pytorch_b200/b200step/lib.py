@@ -57,16 +57,17 @@ SIGNATURES = {
     "b200_cast_bf16": (_i, [_p, _p, _i64, _p]),
     "b200_image_augment": (_i, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p, _i, _p, _p, _i64, _i, _i, _i, _p]),
     "b200_conv_fwd": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p]),
+    "b200_conv_dgrad": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i64, _i, _p]),
     "b200_conv_wgrad": (_i, [_p, _i64, _p, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p]),
     "b200_im2col": (_i, [_p, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_col2im": (_i, [_p, _i64, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_bn_scratch_floats": (_i64, [_i64]),
     "b200_bn_fwd_stats": (_i, [_p, _i64, _i64, _f, _f, _p, _p, _p, _p, _p, _p, _i64, _i, _p]),
     "b200_bn_fwd_apply": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _i, _i, _p]),
-    "b200_bn_bwd_reduce": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i64, _i, _p]),
-    "b200_bn_bwd_apply": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "b200_bn_bwd_reduce": (_i, [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i64, _i, _p]),
+    "b200_bn_bwd_apply": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
     "b200_maxpool_fwd": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
-    "b200_maxpool_bwd": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "b200_maxpool_bwd": (_i, [_p, _p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_avgpool_fwd": (_i, [_p, _p, _i64, _i, _i, _i, _p]),
     "b200_avgpool_bwd": (_i, [_p, _p, _i64, _i, _i, _i, _p]),
     "b200_zero": (_i, [_p, _i64, _p]),

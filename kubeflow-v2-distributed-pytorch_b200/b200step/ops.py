@@ -260,6 +260,13 @@ def conv_fwd(x, w, y, *, B: int, H: int, W: int, C: int, kh: int, kw: int, strid
                        dtype_code(x.dtype), FLAG_RELU if relu else 0, _stream(stream))
 
 
+def conv_dgrad(dy, w, dx, *, B: int, H: int, W: int, C: int, kh: int, kw: int, pad: int, Cout: int, stream=None):
+    """dx[B*H*W, C] of a stride-1 convolution as an implicit GEMM over dy (no dcol matrix, no col2im)."""
+    _cuda(dy, w, dx)
+    get_lib().conv_dgrad(ptr(dy), ptr(w), w.stride(0), ptr(dx), dx.stride(0), B, H, W, C, kh, kw, pad, Cout,
+                         dtype_code(dx.dtype), _stream(stream))
+
+
 def conv_wgrad(dy, x, dw, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, Cout: int,
                accumulate: bool = False, deterministic: bool = False, stream=None):
     """dw[Cout, kh*kw*C] = dy^T . unfold(x NHWC) as an implicit GEMM (no col matrix)."""
@@ -294,15 +301,16 @@ def bn_fwd_apply(y, res, out, mean, invstd, gamma, beta, *, M: int, C: int, relu
                            int(relu), dtype_code(y.dtype), _stream(stream))
 
 
-def bn_bwd_reduce(dout, out, y, mean, invstd, dgamma, dbeta, scratch, *, M: int, C: int, stream=None):
-    _cuda(dout, out, y, mean, invstd, dgamma, dbeta, scratch)
-    get_lib().bn_bwd_reduce(ptr(dout), ptr(out), ptr(y), M, C, ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta),
+def bn_bwd_reduce(dout, out, y, mean, invstd, dgamma, dbeta, scratch, *, M: int, C: int, dout2=None, stream=None):
+    _cuda(dout, dout2, out, y, mean, invstd, dgamma, dbeta, scratch)
+    get_lib().bn_bwd_reduce(ptr(dout), ptr(dout2), ptr(out), ptr(y), M, C, ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta),
                             ptr(scratch), scratch.numel(), dtype_code(y.dtype), _stream(stream))
 
 
-def bn_bwd_apply(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, *, M: int, C: int, stream=None):
-    _cuda(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta)
-    get_lib().bn_bwd_apply(ptr(dout), ptr(out), ptr(y), ptr(dy), ptr(dz_out), M, C, ptr(mean), ptr(invstd),
+def bn_bwd_apply(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, *, M: int, C: int, dout2=None,
+                 stream=None):
+    _cuda(dout, dout2, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta)
+    get_lib().bn_bwd_apply(ptr(dout), ptr(dout2), ptr(out), ptr(y), ptr(dy), ptr(dz_out), M, C, ptr(mean), ptr(invstd),
                            ptr(gamma), ptr(dgamma), ptr(dbeta), dtype_code(y.dtype), _stream(stream))
 
 
@@ -314,9 +322,9 @@ def maxpool_fwd(x, out, taps, *, B: int, H: int, W: int, C: int, k: int = 3, str
 
 
 def maxpool_bwd(dout, taps, dx, *, B: int, H: int, W: int, C: int, k: int = 3, stride: int = 2, pad: int = 1,
-                stream=None):
-    _cuda(dout, taps, dx)
-    get_lib().maxpool_bwd(ptr(dout), ptr(taps), ptr(dx), B, H, W, C, k, stride, pad, dtype_code(dx.dtype),
+                dout2=None, stream=None):
+    _cuda(dout, dout2, taps, dx)
+    get_lib().maxpool_bwd(ptr(dout), ptr(dout2), ptr(taps), ptr(dx), B, H, W, C, k, stride, pad, dtype_code(dx.dtype),
                           _stream(stream))
 
 

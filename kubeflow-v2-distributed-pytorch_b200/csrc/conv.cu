@@ -413,7 +413,8 @@ bn_apply_kernel(const T* __restrict__ y, const T* __restrict__ res, T* __restric
 // backward, pass 1: dbeta[c] = sum_m dz, dgamma[c] = sum_m dz * xhat,  dz = dout * (out > 0) when `out` is given
 template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, const T* __restrict__ y, int64_t M, int C,
+bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, const T* __restrict__ out,
+                     const T* __restrict__ y, int64_t M, int C,
                      const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ partials,
                      uint32_t* ticket, float* __restrict__ dgamma, float* __restrict__ dbeta) {
   pdl_launch_dependents();
@@ -429,6 +430,10 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, cons
     for (int64_t r = r0 + ry; r < r1; r += lanes) {
       const int64_t off = r * C + cv * 4;
       float4 d = Vec4<T>::load(dout + off);
+      if (dout2 != nullptr) {                       // the incoming gradient is the sum of two branches
+        const float4 e = Vec4<T>::load(dout2 + off);
+        d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+      }
       if (out != nullptr) {
         const float4 o = Vec4<T>::load(out + off);
         d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
@@ -451,8 +456,8 @@ bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ out, cons
 // backward, pass 2: dy = gamma*invstd * (dz - dbeta/M - xhat*dgamma/M);  dz_out (nullable) = dz for the residual branch
 template <typename T>
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ out, const T* __restrict__ y, T* __restrict__ dy,
-                    T* __restrict__ dz_out, int64_t M, int C, const float* __restrict__ mean,
+bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, const T* __restrict__ out,
+                    const T* __restrict__ y, T* __restrict__ dy, T* __restrict__ dz_out, int64_t M, int C, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ dgamma,
                     const float* __restrict__ dbeta) {
   pdl_launch_dependents();
@@ -467,6 +472,10 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ out, const
     const float4 g = *reinterpret_cast<const float4*>(gamma + c);
     const float4 dg = *reinterpret_cast<const float4*>(dgamma + c), db = *reinterpret_cast<const float4*>(dbeta + c);
     float4 d = Vec4<T>::load(dout + off);
+    if (dout2 != nullptr) {
+      const float4 e = Vec4<T>::load(dout2 + off);
+      d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+    }
     if (out != nullptr) {
       const float4 o = Vec4<T>::load(out + off);
       d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
@@ -520,7 +529,8 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ out, uint8_t* __rest
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-maxpool_bwd_kernel(const T* __restrict__ dout, const uint8_t* __restrict__ tap_in, T* __restrict__ dx, int B, int H, int W,
+maxpool_bwd_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, const uint8_t* __restrict__ tap_in,
+                   T* __restrict__ dx, int B, int H, int W,
                    int C, int Ho, int Wo, int k, int stride, int pad) {
   pdl_launch_dependents();
   pdl_wait();
@@ -545,7 +555,11 @@ maxpool_bwd_kernel(const T* __restrict__ dout, const uint8_t* __restrict__ tap_i
         if (wq * stride != wn || wq >= Wo) continue;
         const int64_t m = (b * Ho + hq) * (int64_t)Wo + wq;
         const uchar4 tp = *reinterpret_cast<const uchar4*>(tap_in + m * C + c);
-        const float4 d = Vec4<T>::load(dout + m * C + c);
+        float4 d = Vec4<T>::load(dout + m * C + c);
+        if (dout2 != nullptr) {
+          const float4 e = Vec4<T>::load(dout2 + m * C + c);
+          d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+        }
         const int me = ky * k + kx;
         if (tp.x == me) acc.x += d.x;
         if (tp.y == me) acc.y += d.y;
@@ -750,56 +764,56 @@ extern "C" int b200_bn_fwd_apply(const void* y, const void* res, void* out, int6
 }
 
 template <typename T>
-static int bn_bwd_reduce_t(const void* dout, const void* out, const void* y, int64_t M, int C, const float* mean,
+static int bn_bwd_reduce_t(const void* dout, const void* dout2, const void* out, const void* y, int64_t M, int C, const float* mean,
                            const float* invstd, float* scratch, float* dgamma, float* dbeta, cudaStream_t st) {
   B200_CHECK_CUDA(launch_pdl(bn_bwd_reduce_kernel<T>, dim3(bn_blocks(M, C)), dim3(BN_THREADS), 0, st, (const T*)dout,
-                             (const T*)out, (const T*)y, M, C, mean, invstd, scratch + BN_SCRATCH_HEAD,
+                             (const T*)dout2, (const T*)out, (const T*)y, M, C, mean, invstd, scratch + BN_SCRATCH_HEAD,
                              reinterpret_cast<uint32_t*>(scratch), dgamma, dbeta));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
-extern "C" int b200_bn_bwd_reduce(const void* dout, const void* out, const void* y, int64_t M, int64_t C,
+extern "C" int b200_bn_bwd_reduce(const void* dout, const void* dout2, const void* out, const void* y, int64_t M, int64_t C,
                                   const float* mean, const float* invstd, float* dgamma, float* dbeta, float* scratch,
                                   int64_t scratch_floats, int dtype, b200_stream_t stream) {
-  CONV_COMMON("bn_bwd_reduce", ALIGNED16(dout) && ALIGNED16(y) && ALIGNED16_OR_NULL(out) && ALIGNED16(mean) &&
+  CONV_COMMON("bn_bwd_reduce", ALIGNED16(dout) && ALIGNED16_OR_NULL(dout2) && ALIGNED16(y) && ALIGNED16_OR_NULL(out) && ALIGNED16(mean) &&
                                    ALIGNED16(invstd) && dgamma != nullptr && dbeta != nullptr && scratch != nullptr);
   if (int r = bn_check("bn_bwd_reduce", M, C, scratch, scratch_floats)) return r;
-  return dtype == B200_BF16 ? bn_bwd_reduce_t<bf16_t>(dout, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st)
-                            : bn_bwd_reduce_t<float>(dout, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st);
+  return dtype == B200_BF16 ? bn_bwd_reduce_t<bf16_t>(dout, dout2, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st)
+                            : bn_bwd_reduce_t<float>(dout, dout2, out, y, M, (int)C, mean, invstd, scratch, dgamma, dbeta, st);
 }
 
 template <typename T>
-static int bn_bwd_apply_t(const void* dout, const void* out, const void* y, void* dy, void* dz, int64_t M, int C,
+static int bn_bwd_apply_t(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz, int64_t M, int C,
                           const float* mean, const float* invstd, const float* gamma, const float* dgamma,
                           const float* dbeta, cudaStream_t st) {
   B200_CHECK_CUDA(launch_pdl(bn_bwd_apply_kernel<T>, dim3(grid_for(M * (C / 4), 256, 16)), dim3(256), 0, st,
-                             (const T*)dout, (const T*)out, (const T*)y, (T*)dy, (T*)dz, M, C, mean, invstd, gamma,
+                             (const T*)dout, (const T*)dout2, (const T*)out, (const T*)y, (T*)dy, (T*)dz, M, C, mean, invstd, gamma,
                              dgamma, dbeta));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
-extern "C" int b200_bn_bwd_apply(const void* dout, const void* out, const void* y, void* dy, void* dz_out, int64_t M,
+extern "C" int b200_bn_bwd_apply(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz_out, int64_t M,
                                  int64_t C, const float* mean, const float* invstd, const float* gamma,
                                  const float* dgamma, const float* dbeta, int dtype, b200_stream_t stream) {
-  CONV_COMMON("bn_bwd_apply", ALIGNED16(dout) && ALIGNED16(y) && ALIGNED16(dy) && ALIGNED16_OR_NULL(out) &&
+  CONV_COMMON("bn_bwd_apply", ALIGNED16(dout) && ALIGNED16_OR_NULL(dout2) && ALIGNED16(y) && ALIGNED16(dy) && ALIGNED16_OR_NULL(out) &&
                                   ALIGNED16_OR_NULL(dz_out) && ALIGNED16(mean) && ALIGNED16(invstd) && ALIGNED16(gamma) &&
                                   ALIGNED16(dgamma) && ALIGNED16(dbeta));
   if (int r = bn_check("bn_bwd_apply", M, C, nullptr, 0)) return r;
   return dtype == B200_BF16
-             ? bn_bwd_apply_t<bf16_t>(dout, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st)
-             : bn_bwd_apply_t<float>(dout, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st);
+             ? bn_bwd_apply_t<bf16_t>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st)
+             : bn_bwd_apply_t<float>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st);
 }
 
 // ---- pooling entry points -------------------------------------------------------------------------------------------
 template <typename T>
-static int maxpool_t(bool fwd, const void* in, void* out, uint8_t* taps, int B, int H, int W, int C, int Ho, int Wo, int k,
+static int maxpool_t(bool fwd, const void* in, const void* in2, void* out, uint8_t* taps, int B, int H, int W, int C, int Ho, int Wo, int k,
                      int stride, int pad, cudaStream_t st) {
   if (fwd)
     B200_CHECK_CUDA(launch_pdl(maxpool_fwd_kernel<T>, dim3(grid_for((int64_t)B * Ho * Wo * (C / 4), 256, 16)), dim3(256),
                                0, st, (const T*)in, (T*)out, taps, B, H, W, C, Ho, Wo, k, stride, pad));
   else
     B200_CHECK_CUDA(launch_pdl(maxpool_bwd_kernel<T>, dim3(grid_for((int64_t)B * H * W * (C / 4), 256, 16)), dim3(256), 0,
-                               st, (const T*)in, (const uint8_t*)taps, (T*)out, B, H, W, C, Ho, Wo, k, stride, pad));
+                               st, (const T*)in, (const T*)in2, (const uint8_t*)taps, (T*)out, B, H, W, C, Ho, Wo, k, stride, pad));
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -814,17 +828,17 @@ extern "C" int b200_maxpool_fwd(const void* x, void* out, uint8_t* taps, int64_t
   CONV_COMMON("maxpool_fwd", ALIGNED16(x) && ALIGNED16(out) && ALIGNED16(taps));
   if (int r = maxpool_check(B, H, W, C, k, stride, pad)) return r;
   const int Ho = conv_out(H, k, stride, pad), Wo = conv_out(W, k, stride, pad);
-  return dtype == B200_BF16 ? maxpool_t<bf16_t>(true, x, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
-                            : maxpool_t<float>(true, x, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
+  return dtype == B200_BF16 ? maxpool_t<bf16_t>(true, x, nullptr, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
+                            : maxpool_t<float>(true, x, nullptr, out, taps, (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
 }
-extern "C" int b200_maxpool_bwd(const void* dout, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
+extern "C" int b200_maxpool_bwd(const void* dout, const void* dout2, const uint8_t* taps, void* dx, int64_t B, int H, int W, int C, int k,
                                 int stride, int pad, int dtype, b200_stream_t stream) {
-  CONV_COMMON("maxpool_bwd", ALIGNED16(dout) && ALIGNED16(dx) && ALIGNED16(taps));
+  CONV_COMMON("maxpool_bwd", ALIGNED16(dout) && ALIGNED16_OR_NULL(dout2) && ALIGNED16(dx) && ALIGNED16(taps));
   if (int r = maxpool_check(B, H, W, C, k, stride, pad)) return r;
   const int Ho = conv_out(H, k, stride, pad), Wo = conv_out(W, k, stride, pad);
   return dtype == B200_BF16
-             ? maxpool_t<bf16_t>(false, dout, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
-             : maxpool_t<float>(false, dout, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
+             ? maxpool_t<bf16_t>(false, dout, dout2, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st)
+             : maxpool_t<float>(false, dout, dout2, dx, const_cast<uint8_t*>(taps), (int)B, H, W, C, Ho, Wo, k, stride, pad, st);
 }
 
 template <typename T>

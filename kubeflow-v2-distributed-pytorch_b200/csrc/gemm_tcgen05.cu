@@ -47,7 +47,8 @@ struct GemmParams {
   // convolution as implicit GEMM: the K-major A operand comes from an im2col-mode tensor map over the NHWC input
   // (k-block kb = filter tap kb / cv_cpb, channels (kb % cv_cpb) * BLOCK_K ...); 0 = plain matrix A
   int cv_on, cv_Ho, cv_Wo, cv_stride, cv_pad, cv_kw, cv_cpb;
-  int cv_C, cv_K;            // wgrad (MN-major B from the input): channels and kh*kw*C
+  int cv_C, cv_K;            // wgrad (cv_on 1, MN-major B from the input): channels and kh*kw*C;
+                             // dgrad (cv_on 2): input channels and the number of filter taps
 };
 
 // kCtas = 2: the two CTAs of a cluster form a pair (tcgen05 cta_group::2).  The pair owns a 256 x 256 tile: each CTA
@@ -159,6 +160,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if constexpr (!kBMN) {
               tma_load_2d_pair(sb, &tmB, fb, kb * BLOCK_K, n0);
+            } else if (p.cv_on == 2) {
+              // dgrad of a stride-1 convolution = a convolution of dy with the flipped filter: k-block kb is
+              // (tap', Cout slice); B(n' = ci, k' = co) is the [co][ci] block of Wg at the FLIPPED tap's columns
+              const int tap = kb / p.cv_cpb, co0 = (kb - tap * p.cv_cpb) * BLOCK_K;
+              const int wc0 = (p.cv_K - 1 - tap) * p.cv_C + n0;
+#pragma unroll
+              for (int j = 0; j < B_ROWS / EPR; ++j)
+                tma_load_2d_pair(sb + j * MN_BOX_BYTES, &tmB, fb, wc0 + j * EPR, co0);
             } else if (p.cv_on) {
               // wgrad of a convolution: B(n' = filter column, k' = pixel) straight from the NHWC input; this k-block
               // is BLOCK_K consecutive output pixels, each 128-byte column group one (tap, channel slice)
@@ -194,6 +203,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if constexpr (!kBMN) {
               tma_load_2d(sb, &tmB, &full_bar[s], kb * BLOCK_K, n0);
+            } else if (p.cv_on == 2) {
+              const int tap = kb / p.cv_cpb, co0 = (kb - tap * p.cv_cpb) * BLOCK_K;
+              const int wc0 = (p.cv_K - 1 - tap) * p.cv_C + n0;
+#pragma unroll
+              for (int j = 0; j < B_ROWS / EPR; ++j)
+                tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], wc0 + j * EPR, co0);
             } else if (p.cv_on) {
               const int pix = kb * BLOCK_K, q = pix % p.cv_Wo, t = pix / p.cv_Wo;
               const int bw = q * p.cv_stride - p.cv_pad, bh = (t % p.cv_Ho) * p.cv_stride - p.cv_pad, bn = t / p.cv_Ho;
@@ -1002,6 +1017,44 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
   }
   return tf32 ? launch_gemm<1, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
               : launch_gemm<0, true, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st);
+}
+
+// Input gradient of a STRIDE-1 convolution as an implicit GEMM: dx = conv2d(dy, flipped filter) with padding k-1-pad.
+// A tiles: im2col-mode TMA over dy [B, Ho, Wo, Cout]; B tiles: the [co][ci] block of Wg at the flipped tap, read as an
+// MN-major operand from the SAME filter matrix the forward pass uses (no transposed copy); dx is written once — the
+// 9x larger dcol matrix and the col2im pass of the explicit path do not exist.
+extern "C" int b200_conv_dgrad(const void* dy, const void* w, int64_t ldw, void* dx, int64_t lddx, int64_t B, int H, int W,
+                               int C, int kh, int kw, int pad, int64_t Cout, int dtype, b200_stream_t stream) {
+  B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
+  const int tf32 = dtype == B200_F32;
+  const int bk = tf32 ? 32 : 64, epr = bk;
+  B200_REQUIRE(B > 0 && H > 0 && W > 0 && kh > 0 && kw > 0 && kh * kw < 256 && pad >= 0 && pad < kh && pad < kw &&
+                   C > 0 && C % 8 == 0 && Cout > 0 && Cout % bk == 0,
+               "conv_dgrad: Cout=%lld must be a multiple of %d, C=%d of 8, padding < kernel", (long long)Cout, bk, C);
+  const int Ho = H + 2 * pad - kh + 1, Wo = W + 2 * pad - kw + 1;      // stride 1
+  B200_REQUIRE(Ho > 0 && Wo > 0, "conv_dgrad: empty output");
+  const int64_t M = B * H * W, K = (int64_t)kh * kw * C, Kc = (int64_t)kh * kw * Cout;
+  if (int r = check_dims(M, Cout, C, dtype)) return r;
+  B200_REQUIRE(ldw >= K, "conv_dgrad: filter row stride %lld < kh*kw*C = %lld", (long long)ldw, (long long)K);
+  CUtensorMap ta, tb, tc;
+  // "full" correlation of dy: a kh x kw window over dy padded by k-1-pad gives back H x W positions
+  if (int r = make_tmap_im2col(&ta, tf32, dy, B, Ho, Wo, (int)Cout, kh, kw, 1, kh - 1 - pad, bk, BLOCK_M)) return r;
+  if (int r = make_tmap(&tb, tf32, w, K, Cout, ldw, epr, bk, true)) return r;
+  if (int r = make_tmap(&tc, tf32, dx, C, M, lddx, epr, 32, false, true)) return r;
+  B200_REQUIRE(kh == kw, "conv_dgrad: square filters only");
+  GemmParams p{};
+  p.M = (int)M; p.N = C;
+  const int tile_m = BLOCK_M * gemm_ctas();
+  p.k_blocks = (int)(Kc / bk);
+  p.m_tiles = (int)((M + tile_m - 1) / tile_m);
+  p.n_tiles = (C + BLOCK_N - 1) / BLOCK_N;
+  p.splits = 1; p.kb_per_split = p.k_blocks;
+  p.out = dx; p.ldo = lddx; p.flags = 0; p.dscale = 1.f;
+  p.cv_on = 2; p.cv_Ho = H; p.cv_Wo = W; p.cv_stride = 1; p.cv_pad = kh - 1 - pad; p.cv_kw = kw;
+  p.cv_cpb = (int)(Cout / bk); p.cv_C = C; p.cv_K = kh * kw;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st)
+              : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st);
 }
 
 // Filter gradient of a convolution as an implicit GEMM: dw[Cout, kh*kw*C] (+)= dy[B*Ho*Wo, Cout]^T . unfold(x), with the

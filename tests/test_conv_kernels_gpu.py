@@ -354,3 +354,67 @@ def test_implicit_gemm_filter_gradient(ops, dtype, B, H, C, k, stride, pad, Cout
     for t in (dw, dw2):
         got = gemm_to_filter(t.cpu(), (Cout, C, k, k))
         assert (got - wr.grad).abs().max().item() <= rt * scale
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["tf32", "bf16"])
+@pytest.mark.parametrize("B,H,C,k,pad,Cout", [(32, 8, 64, 3, 1, 64), (16, 4, 128, 3, 1, 128), (32, 1, 512, 3, 1, 512),
+                                              (8, 2, 256, 3, 1, 256), (3, 5, 64, 3, 1, 128), (1024, 8, 64, 3, 1, 64),
+                                              (4, 6, 72, 1, 0, 64)])
+def test_implicit_gemm_input_gradient(ops, dtype, B, H, C, k, pad, Cout):
+    """b200_conv_dgrad (stride 1: dy convolved with the flipped filter, A tiles by im2col-mode TMA over dy, B tiles from
+    the forward's own filter matrix) against dgrad GEMM + col2im and against autograd."""
+    from b200step.convnet import filter_to_gemm
+
+    g = torch.Generator().manual_seed(10)
+    w = (torch.randn(Cout, C, k, k, generator=g) / (C * k * k) ** 0.5).to(dtype)
+    xr = torch.zeros(B, C, H, H, requires_grad=True)
+    yr = F.conv2d(xr, w.float(), stride=1, padding=pad)
+    dyr = torch.randn(yr.shape, generator=g).to(dtype)
+    yr.backward(dyr.float())
+    Ho = ops.conv_out_size(H, k, 1, pad)
+    M, K = B * Ho * Ho, k * k * C
+    wg = filter_to_gemm(w, K).cuda()
+    dy = _nhwc(dyr).view(M, Cout)
+    dcol = torch.empty(M, K, dtype=dtype, device="cuda")
+    dx_explicit = torch.empty(B * H * H, C, dtype=dtype, device="cuda")
+    ops.linear_dgrad(dy, wg, None, dcol, M=M, N=Cout, K=K, relu=False)
+    ops.col2im(dcol, None, dx_explicit, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=1, pad=pad)
+    dx = torch.full((B * H * H, C), 3.0, dtype=dtype, device="cuda")
+    ops.conv_dgrad(dy, wg, dx, B=B, H=H, W=H, C=C, kh=k, kw=k, pad=pad, Cout=Cout)
+    torch.cuda.synchronize()
+    rt = 2e-2 if dtype == torch.bfloat16 else 5e-3
+    scale = xr.grad.abs().max().item()
+    got = _nchw(dx, B, H, H, C)
+    assert (got - xr.grad).abs().max().item() <= 2 * rt * scale
+    # same products, fp32 accumulation in another order (one long contraction instead of 9 rounded partial sums)
+    assert (dx.float() - dx_explicit.float()).abs().max().item() <= 2 * rt * scale
+
+
+def test_batchnorm_backward_sums_two_incoming_gradients(ops):
+    g = torch.Generator().manual_seed(12)
+    M, C = 2048, 64
+    f32 = dict(dtype=torch.float32, device="cuda")
+    y, out = torch.randn(M, C, generator=g).cuda(), torch.randn(M, C, generator=g).cuda()
+    a, b = torch.randn(M, C, generator=g).cuda(), torch.randn(M, C, generator=g).cuda()
+    mean, invstd, gamma = torch.randn(C, generator=g).cuda(), (torch.rand(C, generator=g) + 0.5).cuda(), torch.ones(C, **f32)
+    scr = torch.zeros(ops.bn_scratch_floats(C), **f32)
+    res = []
+    for d1, d2 in ((a + b, None), (a, b)):
+        dg, db = torch.empty(C, **f32), torch.empty(C, **f32)
+        dy, dz = torch.empty(M, C, **f32), torch.empty(M, C, **f32)
+        ops.bn_bwd_reduce(d1, out, y, mean, invstd, dg, db, scr, M=M, C=C, dout2=d2)
+        ops.bn_bwd_apply(d1, out, y, dy, dz, mean, invstd, gamma, dg, db, M=M, C=C, dout2=d2)
+        res.append((dg, db, dy, dz))
+    for u, v in zip(*res):
+        assert torch.equal(u, v)
+    # max-pool backward too
+    B, H = 4, 8
+    x = torch.relu(torch.randn(B * H * H, C, generator=g)).cuda()
+    o = torch.empty(B * 16, C, **f32)
+    taps = torch.empty(B * 16, C, dtype=torch.uint8, device="cuda")
+    ops.maxpool_fwd(x, o, taps, B=B, H=H, W=H, C=C)
+    d1, d2 = torch.randn(B * 16, C, generator=g).cuda(), torch.randn(B * 16, C, generator=g).cuda()
+    r1, r2 = torch.empty(B * H * H, C, **f32), torch.empty(B * H * H, C, **f32)
+    ops.maxpool_bwd(d1 + d2, taps, r1, B=B, H=H, W=H, C=C)
+    ops.maxpool_bwd(d1, taps, r2, B=B, H=H, W=H, C=C, dout2=d2)
+    assert torch.equal(r1, r2)
