@@ -299,14 +299,20 @@ int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, int H, int W
                 int pad, int dtype, b200_stream_t stream);
 /* Convolution forward as an IMPLICIT GEMM (no col matrix): y[B*Ho*Wo, Cout] = conv2d(x NHWC, w) with w stored as
  * Wg[Cout][ky][kx][c] (row stride ldw).  The tcgen05 GEMM's A tiles are fetched by im2col-mode TMA straight from x
- * (padding halo zero-filled by the hardware).  C must be a multiple of 64 (bf16) / 32 (fp32); flags: B200_FLAG_RELU. */
+ * (padding halo zero-filled by the hardware).  C must be a multiple of 64 (bf16) / 32 (fp32); flags: B200_FLAG_RELU,
+ * B200_FLAG_DETERMINISTIC.  ws (nullable, >= B*Ho*Wo*Cout floats): fp32 workspace that lets a convolution with few
+ * output tiles but a long contraction (a ResNet's last stages) split the contraction over the idle SMs; the partial
+ * tiles are combined with fp32 atomics (not with B200_FLAG_DETERMINISTIC) and cast to `dtype` by a second launch. */
 int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y, int64_t ldy, int64_t B, int H, int W, int C,
-                  int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags, b200_stream_t stream);
+                  int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags, float* ws,
+                  int64_t ws_floats, b200_stream_t stream);
 /* Input gradient of a STRIDE-1 convolution without the dcol matrix and the col2im pass: dx[B*H*W, C] = conv2d(dy,
  * flipped filter, padding k-1-pad); dy is [B, Ho, Wo, Cout] NHWC, w the same Wg[Cout][ky][kx][c] the forward uses (read
- * as an MN-major operand at the flipped tap).  Cout a multiple of 64 (bf16) / 32 (fp32), square filters. */
+ * as an MN-major operand at the flipped tap).  Cout a multiple of 64 (bf16) / 32 (fp32), square filters.  flags / ws
+ * (>= B*H*W*C floats) as for b200_conv_fwd. */
 int b200_conv_dgrad(const void* dy, const void* w, int64_t ldw, void* dx, int64_t lddx, int64_t B, int H, int W, int C,
-                    int kh, int kw, int pad, int64_t Cout, int dtype, b200_stream_t stream);
+                    int kh, int kw, int pad, int64_t Cout, int dtype, int flags, float* ws, int64_t ws_floats,
+                    b200_stream_t stream);
 /* Filter gradient of the same convolution, also without a col matrix: dw[Cout, kh*kw*C] (+)= dy^T . unfold(x), fp32
  * (row stride lddw); flags: B200_FLAG_ACCUMULATE, B200_FLAG_DETERMINISTIC as for b200_linear_wgrad. */
 int b200_conv_wgrad(const void* dy, int64_t lddy, const void* x, float* dw, int64_t lddw, int64_t B, int H, int W,

@@ -307,6 +307,10 @@ class ConvTrainStep:
                          os.environ.get("B200STEP_IMPLICIT_CONV", "1") != "0" for c in convs}
         self.col = {c.name: torch.zeros(B * c.Ho * c.Wo, c.Kp, **act) for c in convs if not self.implicit[c.name]}
         self.xin: Dict[str, torch.Tensor] = {}          # implicit convs: the input activation seen in forward
+        # fp32 workspace for the split contraction of the small-M convolutions (main stream only); the layers that
+        # split have <= 37 output tiles of 256 x 256
+        self.conv_ws = torch.zeros(37 * 256 * 256, **f32) if (self.dt == torch.bfloat16 and
+                                                              os.environ.get("B200STEP_CONV_SPLIT", "1") != "0") else None
         self.yc = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs}      # conv output (pre-BN)
         self.a = {c.name: torch.zeros(B * c.Ho * c.Wo, c.cout, **act) for c in convs if ".downsample" not in c.name}
         self.sc = {b.name: torch.zeros_like(self.yc[b.down.name]) for b in layout.blocks if b.down is not None}
@@ -433,7 +437,8 @@ class ConvTrainStep:
         if self.implicit[c.name]:
             self.xin[c.name] = x
             ops.conv_fwd(x, self._w(c.name), self.yc[c.name][:M], B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k,
-                         stride=c.stride, pad=c.pad, Cout=c.cout, stream=self.main)
+                         stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det, ws=self.conv_ws,
+                         stream=self.main)
             return 1
         col, y = self.col[c.name][:M], self.yc[c.name][:M]
         ops.im2col(x, col, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, stride=c.stride, pad=c.pad, stream=self.main)
@@ -460,7 +465,7 @@ class ConvTrainStep:
         M = rows_b * c.Ho * c.Wo
         if add is None and self._implicit_dgrad(c):
             ops.conv_dgrad(dy, self._w(c.name), dx, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, pad=c.pad,
-                           Cout=c.cout, stream=self.main)
+                           Cout=c.cout, deterministic=self.det, ws=self.conv_ws, stream=self.main)
             return 1
         n = 2
         dcol = self.dcol[: M * c.Kp].view(M, c.Kp)

@@ -56,8 +56,8 @@ SIGNATURES = {
     "b200_split_tf32": (_i, [_p, _i64, _i64, _i64, _p, _i, _p, _i, _p]),
     "b200_cast_bf16": (_i, [_p, _p, _i64, _p]),
     "b200_image_augment": (_i, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p, _i, _p, _p, _i64, _i, _i, _i, _p]),
-    "b200_conv_fwd": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p]),
-    "b200_conv_dgrad": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i64, _i, _p]),
+    "b200_conv_fwd": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p, _i64, _p]),
+    "b200_conv_dgrad": (_i, [_p, _p, _i64, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p, _i64, _p]),
     "b200_conv_wgrad": (_i, [_p, _i64, _p, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i64, _i, _i, _p]),
     "b200_im2col": (_i, [_p, _p, _i64, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_col2im": (_i, [_p, _i64, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _p]),

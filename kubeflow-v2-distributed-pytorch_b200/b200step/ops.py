@@ -253,18 +253,22 @@ def im2col(x, col, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: 
 
 
 def conv_fwd(x, w, y, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, Cout: int,
-             relu: bool = False, stream=None):
-    """y = conv2d(x NHWC, w[Cout, kh*kw*C]) as an implicit GEMM (im2col-mode TMA, no col matrix)."""
-    _cuda(x, w, y)
+             relu: bool = False, deterministic: bool = False, ws=None, stream=None):
+    """y = conv2d(x NHWC, w[Cout, kh*kw*C]) as an implicit GEMM (im2col-mode TMA, no col matrix).  ws: optional fp32
+    workspace (>= y.numel() floats) that allows the contraction of a small-M convolution to be split over idle SMs."""
+    _cuda(x, w, y, ws)
     get_lib().conv_fwd(ptr(x), ptr(w), w.stride(0), ptr(y), y.stride(0), B, H, W, C, kh, kw, stride, pad, Cout,
-                       dtype_code(x.dtype), FLAG_RELU if relu else 0, _stream(stream))
+                       dtype_code(x.dtype), (FLAG_RELU if relu else 0) | (FLAG_DETERMINISTIC if deterministic else 0),
+                       ptr(ws), ws.numel() if ws is not None else 0, _stream(stream))
 
 
-def conv_dgrad(dy, w, dx, *, B: int, H: int, W: int, C: int, kh: int, kw: int, pad: int, Cout: int, stream=None):
+def conv_dgrad(dy, w, dx, *, B: int, H: int, W: int, C: int, kh: int, kw: int, pad: int, Cout: int,
+               deterministic: bool = False, ws=None, stream=None):
     """dx[B*H*W, C] of a stride-1 convolution as an implicit GEMM over dy (no dcol matrix, no col2im)."""
-    _cuda(dy, w, dx)
+    _cuda(dy, w, dx, ws)
     get_lib().conv_dgrad(ptr(dy), ptr(w), w.stride(0), ptr(dx), dx.stride(0), B, H, W, C, kh, kw, pad, Cout,
-                         dtype_code(dx.dtype), _stream(stream))
+                         dtype_code(dx.dtype), FLAG_DETERMINISTIC if deterministic else 0, ptr(ws),
+                         ws.numel() if ws is not None else 0, _stream(stream))
 
 
 def conv_wgrad(dy, x, dw, *, B: int, H: int, W: int, C: int, kh: int, kw: int, stride: int, pad: int, Cout: int,

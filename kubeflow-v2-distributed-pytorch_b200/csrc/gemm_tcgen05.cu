@@ -864,11 +864,26 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
               : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);
 }
 
+// Small-M convolutions (layer3/4 of a ResNet on 32x32 images: 1024-4096 output pixels) have 8-16 output tiles for 74 CTA
+// pairs while their contraction is 36-72 k-blocks long.  With a caller-provided fp32 workspace the contraction is split
+// across CTA pairs: every split adds its partial tile onto the zeroed workspace (red.global.add.v4.f32, the wgrad
+// epilogue), and one cast pass writes the bf16 result (fp32 outputs are accumulated in place, no workspace needed).
+// Not used with B200_FLAG_DETERMINISTIC (the sum order of the splits is not fixed).
+static int conv_splits(const GemmParams& p, int flags) {
+  if (flags & B200_FLAG_DETERMINISTIC) return 1;
+  const int tiles = p.m_tiles * p.n_tiles, units = sm_count() / gemm_ctas();
+  if (tiles * 2 > units || p.k_blocks < 8) return 1;
+  int splits = units / tiles;
+  if (splits > p.k_blocks / 4) splits = p.k_blocks / 4;       // at least 4 k-blocks per split
+  return splits < 2 ? 1 : splits;
+}
+extern "C" int b200_cast_bf16(const float* src, void* dst, int64_t n, b200_stream_t stream);
+
 // Convolution forward as an implicit GEMM: y[B*Ho*Wo, Cout] = unfold(x)[.., kh*kw*C] . w[Cout, kh*kw*C]^T without the
 // unfold ever being stored — the A tiles come from an im2col-mode tensor map over the NHWC input.
 extern "C" int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y, int64_t ldy, int64_t B, int H, int W,
                              int C, int kh, int kw, int stride, int pad, int64_t Cout, int dtype, int flags,
-                             b200_stream_t stream) {
+                             float* ws, int64_t ws_floats, b200_stream_t stream) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64;
@@ -893,6 +908,21 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y,
   p.out = y; p.ldo = ldy; p.flags = flags & (B200_FLAG_RELU | B200_FLAG_REVERSE_M); p.dscale = 1.f;
   p.cv_on = 1; p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_stride = stride; p.cv_pad = pad; p.cv_kw = kw; p.cv_cpb = C / bk;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int splits = (flags & B200_FLAG_RELU) ? 1 : conv_splits(p, flags);
+  const bool ws_ok = tf32 ? (ldy % 4 == 0) : (ws != nullptr && ws_floats >= M * Cout && ldy == Cout &&
+                                              (reinterpret_cast<uintptr_t>(ws) & 15) == 0);
+  if (splits > 1 && ws_ok) {
+    float* acc = tf32 ? static_cast<float*>(y) : ws;
+    const int64_t ldacc = tf32 ? ldy : Cout;
+    p.kb_per_split = (p.k_blocks + splits - 1) / splits;
+    p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+    p.out = acc; p.ldo = ldacc; p.flags = 0;
+    B200_CHECK_CUDA(cudaMemset2DAsync(acc, ldacc * sizeof(float), 0, Cout * sizeof(float), M, st));
+    if (int r = tf32 ? launch_gemm<1, false, false, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
+                     : launch_gemm<0, false, false, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st))
+      return r;
+    return tf32 ? 0 : b200_cast_bf16(ws, y, M * Cout, stream);
+  }
   return tf32 ? launch_gemm<1, false, false, EPI_FWD>(ta, tb, tc, p, st)
               : launch_gemm<0, false, false, EPI_FWD>(ta, tb, tc, p, st);
 }
@@ -1024,7 +1054,8 @@ extern "C" int b200_linear_wgrad(const void* dy, int64_t lddy, const void* x, in
 // MN-major operand from the SAME filter matrix the forward pass uses (no transposed copy); dx is written once — the
 // 9x larger dcol matrix and the col2im pass of the explicit path do not exist.
 extern "C" int b200_conv_dgrad(const void* dy, const void* w, int64_t ldw, void* dx, int64_t lddx, int64_t B, int H, int W,
-                               int C, int kh, int kw, int pad, int64_t Cout, int dtype, b200_stream_t stream) {
+                               int C, int kh, int kw, int pad, int64_t Cout, int dtype, int flags, float* ws,
+                               int64_t ws_floats, b200_stream_t stream) {
   B200_REQUIRE(dtype == B200_F32 || dtype == B200_BF16, "unknown dtype code %d", dtype);
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64, epr = bk;
@@ -1053,6 +1084,21 @@ extern "C" int b200_conv_dgrad(const void* dy, const void* w, int64_t ldw, void*
   p.cv_on = 2; p.cv_Ho = H; p.cv_Wo = W; p.cv_stride = 1; p.cv_pad = kh - 1 - pad; p.cv_kw = kw;
   p.cv_cpb = (int)(Cout / bk); p.cv_C = C; p.cv_K = kh * kw;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int splits = conv_splits(p, flags);
+  const bool ws_ok = tf32 ? (lddx % 4 == 0) : (ws != nullptr && ws_floats >= M * C && lddx == C &&
+                                               (reinterpret_cast<uintptr_t>(ws) & 15) == 0);
+  if (splits > 1 && ws_ok) {
+    float* acc = tf32 ? static_cast<float*>(dx) : ws;
+    const int64_t ldacc = tf32 ? lddx : C;
+    p.kb_per_split = (p.k_blocks + splits - 1) / splits;
+    p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+    p.out = acc; p.ldo = ldacc;
+    B200_CHECK_CUDA(cudaMemset2DAsync(acc, ldacc * sizeof(float), 0, C * sizeof(float), M, st));
+    if (int r = tf32 ? launch_gemm<1, false, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st)
+                     : launch_gemm<0, false, true, EPI_WGRAD>(ta, tb, ta /*unused*/, p, st))
+      return r;
+    return tf32 ? 0 : b200_cast_bf16(ws, dx, M * C, stream);
+  }
   return tf32 ? launch_gemm<1, false, true, EPI_DGRAD>(ta, tb, tc, p, st)
               : launch_gemm<0, false, true, EPI_DGRAD>(ta, tb, tc, p, st);
 }

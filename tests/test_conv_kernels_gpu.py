@@ -316,7 +316,8 @@ def test_implicit_gemm_convolution_forward(ops, dtype, B, H, C, k, stride, pad, 
     ops.im2col(xg, col, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad)
     ops.linear_fwd(col, wg, None, y_explicit, M=M, N=Cout, K=K, relu=False)
     y = torch.full((M, Cout), 9.0, dtype=dtype, device="cuda")
-    ops.conv_fwd(xg, wg, y, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout)
+    # deterministic: fp32 outputs may otherwise split the contraction of a small convolution (atomics, see the split test)
+    ops.conv_fwd(xg, wg, y, B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout, deterministic=True)
     torch.cuda.synchronize()
     assert torch.equal(y, y_explicit)
     rt = 2e-2 if dtype == torch.bfloat16 else 5e-3
@@ -418,3 +419,38 @@ def test_batchnorm_backward_sums_two_incoming_gradients(ops):
     ops.maxpool_bwd(d1 + d2, taps, r1, B=B, H=H, W=H, C=C)
     ops.maxpool_bwd(d1, taps, r2, B=B, H=H, W=H, C=C, dout2=d2)
     assert torch.equal(r1, r2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["tf32", "bf16"])
+@pytest.mark.parametrize("B,H,C,k,stride,pad,Cout", [(1024, 1, 512, 3, 1, 1, 512), (1024, 2, 256, 3, 1, 1, 256),
+                                                     (1024, 2, 256, 3, 2, 1, 512), (37, 2, 128, 3, 1, 1, 192)])
+def test_split_contraction_of_small_convolutions(ops, dtype, B, H, C, k, stride, pad, Cout):
+    """With a workspace, b200_conv_fwd / b200_conv_dgrad split the contraction of a small-M convolution over the idle
+    SMs (partials combined by fp32 atomics).  Same products: the result equals the unsplit one up to the order of the
+    fp32 additions (and one final rounding for bf16)."""
+    from b200step.convnet import filter_to_gemm
+
+    g = torch.Generator().manual_seed(13)
+    x = torch.randn(B, C, H, H, generator=g).to(dtype)
+    w = (torch.randn(Cout, C, k, k, generator=g) / (C * k * k) ** 0.5).to(dtype)
+    Ho = ops.conv_out_size(H, k, stride, pad)
+    M, K = B * Ho * Ho, k * k * C
+    wg, xg = filter_to_gemm(w, K).cuda(), _nhwc(x)
+    ws = torch.full((37 * 256 * 256,), 7.0, dtype=torch.float32, device="cuda")
+    y0 = torch.empty(M, Cout, dtype=dtype, device="cuda")
+    y1 = torch.full((M, Cout), 9.0, dtype=dtype, device="cuda")
+    kw = dict(B=B, H=H, W=H, C=C, kh=k, kw=k, stride=stride, pad=pad, Cout=Cout)
+    ops.conv_fwd(xg, wg, y0, deterministic=True, **kw)
+    for _ in range(2):                                   # twice: the workspace is re-zeroed by the call itself
+        ops.conv_fwd(xg, wg, y1, ws=ws, **kw)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+    assert torch.allclose(y1.float(), y0.float(), rtol=tol, atol=tol), (y1.float() - y0.float()).abs().max()
+    if stride == 1:
+        dy = torch.randn(M, Cout, generator=g).to(dtype).cuda()
+        d0 = torch.empty(B * H * H, C, dtype=dtype, device="cuda")
+        d1 = torch.full((B * H * H, C), 9.0, dtype=dtype, device="cuda")
+        kd = dict(B=B, H=H, W=H, C=C, kh=k, kw=k, pad=pad, Cout=Cout)
+        ops.conv_dgrad(dy, wg, d0, deterministic=True, **kd)
+        ops.conv_dgrad(dy, wg, d1, ws=ws, **kd)
+        s = d0.float().abs().max().item()
+        assert (d1.float() - d0.float()).abs().max().item() <= tol * max(1.0, s)
