@@ -305,7 +305,15 @@ class ConvTrainStep:
         vec = 64 if self.dt == torch.bfloat16 else 32
         self.implicit = {c.name: (not self.x3) and c.cin % vec == 0 and c.K == c.Kp and
                          os.environ.get("B200STEP_IMPLICIT_CONV", "1") != "0" for c in convs}
-        self.col = {c.name: torch.zeros(B * c.Ho * c.Wo, c.Kp, **act) for c in convs if not self.implicit[c.name]}
+        # 3xTF32 mode, implicit too: the hi/lo copies are taken of the ACTIVATION (not of its 9x larger unfolding) and
+        # laid out so that the unchanged implicit-GEMM entry points see them as a longer contraction:
+        #   forward  x -> [hi | hi | lo] along the channels (3C input channels), filter rows [tap][hi | lo | hi]
+        #   wgrad    x -> [hi ; lo ; hi] stacked as 3B images against dy [hi ; hi ; lo] (contraction over 3M pixels)
+        #   dgrad    dy -> [hi | hi | lo] along Cout (3 Cout channels) against the filter rows stacked [hi ; lo ; hi]
+        self.implicit3 = {c.name: self.x3 and c.cin % 32 == 0 and c.K == c.Kp and
+                          os.environ.get("B200STEP_IMPLICIT_CONV", "1") != "0" for c in convs}
+        self.col = {c.name: torch.zeros(B * c.Ho * c.Wo, c.Kp, **act) for c in convs
+                    if not (self.implicit[c.name] or self.implicit3[c.name])}
         self.xin: Dict[str, torch.Tensor] = {}          # implicit convs: the input activation seen in forward
         # fp32 workspace for the split contraction of the small-M convolutions (main stream only); the layers that
         # split have <= 37 output tiles of 256 x 256
@@ -340,8 +348,13 @@ class ConvTrainStep:
             self.wr = {c.name: torch.zeros(3 * c.cout, c.Kp, **f32) for c in convs}
             self.wk["fc"] = torch.zeros(layout.num_classes, 3 * 512, **f32)
             self.wr["fc"] = torch.zeros(3 * layout.num_classes, 512, **f32)
-            self.colr = {c.name: torch.zeros(3 * B * c.Ho * c.Wo, c.Kp, **f32) for c in convs}
-            self.colk = torch.zeros(max(B * c.Ho * c.Wo * 3 * c.Kp for c in convs), **f32)
+            ex = [c for c in convs if not self.implicit3[c.name]]
+            self.colr = {c.name: torch.zeros(3 * B * c.Ho * c.Wo, c.Kp, **f32) for c in ex}
+            self.colk = torch.zeros(max([B * c.Ho * c.Wo * 3 * c.Kp for c in ex] + [4]), **f32)
+            im = [c for c in convs if self.implicit3[c.name]]
+            self.wk3 = {c.name: torch.zeros(c.cout, 3 * c.K, **f32) for c in im}        # [Cout][tap][hi | lo | hi]
+            self.xr3 = {c.name: torch.zeros(3 * B * c.H * c.W, c.cin, **f32) for c in im}   # kept for wgrad
+            self.xk3 = torch.zeros(max([B * c.H * c.W * 3 * c.cin for c in im] + [4]), **f32)
             self.dyk = torch.zeros(3 * max(amax, B * self.dlogits.shape[1]), **f32)
             self.dyr = torch.zeros(3 * max(amax, B * self.dlogits.shape[1]), **f32)
             self.featk = torch.zeros(B, 3 * 512, **f32)
@@ -388,8 +401,15 @@ class ConvTrainStep:
         names = list(self.convs) + ["fc"]
         for nm in names:
             w = self._pv(nm + ".weight")
-            ops.split_tf32(w, self.wk[nm], ops.SPLIT_RIGHT, self.wr[nm], ops.SPLIT_RIGHT, rows=w.shape[0],
-                           cols=w.shape[1], stream=self.main)
+            if self.implicit3.get(nm, False):
+                c = self.convs[nm]          # one launch: rows of the filter seen as [Cout*taps, C]
+                rows = c.cout * c.k * c.k
+                ops.split_tf32(w.view(rows, c.cin), self.wk3[nm].view(rows, 3 * c.cin), ops.SPLIT_RIGHT,
+                               self.wr[nm].view(3 * rows, c.cin), ops.SPLIT_RIGHT, rows=rows, cols=c.cin,
+                               stream=self.main)
+            else:
+                ops.split_tf32(w, self.wk[nm], ops.SPLIT_RIGHT, self.wr[nm], ops.SPLIT_RIGHT, rows=w.shape[0],
+                               cols=w.shape[1], stream=self.main)
         return len(names)
 
     def _make_buckets(self) -> None:
@@ -440,6 +460,14 @@ class ConvTrainStep:
                          stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det, ws=self.conv_ws,
                          stream=self.main)
             return 1
+        if self.implicit3[c.name]:
+            Min = rows_b * c.H * c.W
+            xk = self.xk3[: Min * 3 * c.cin].view(Min, 3 * c.cin)
+            ops.split_tf32(x, xk, ops.SPLIT_LEFT, self.xr3[c.name][: 3 * Min], ops.SPLIT_RIGHT, rows=Min, cols=c.cin,
+                           stream=self.main)
+            ops.conv_fwd(xk, self.wk3[c.name], self.yc[c.name][:M], B=rows_b, H=c.H, W=c.W, C=3 * c.cin, kh=c.k, kw=c.k,
+                         stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det, stream=self.main)
+            return 2
         col, y = self.col[c.name][:M], self.yc[c.name][:M]
         ops.im2col(x, col, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, stride=c.stride, pad=c.pad, stream=self.main)
         n = 2
@@ -456,13 +484,22 @@ class ConvTrainStep:
     def _implicit_dgrad(self, c: ConvDesc) -> bool:
         """b200_conv_dgrad applies: implicit conv, stride 1, Cout in whole 128-byte k-blocks."""
         vec = 64 if self.dt == torch.bfloat16 else 32
-        return self.implicit[c.name] and c.stride == 1 and c.cout % vec == 0 and \
+        return (self.implicit[c.name] or self.implicit3[c.name]) and c.stride == 1 and c.cout % vec == 0 and \
             os.environ.get("B200STEP_IMPLICIT_DGRAD", "1") != "0"
 
     def _conv_bwd_input(self, c: ConvDesc, dy: torch.Tensor, rows_b: int, dx: torch.Tensor, add, dyk=None) -> int:
         """dx = gradient of conv c wrt its input (+ add).  Implicit GEMM over dy when it applies, else dgrad GEMM into
         the dcol scratch + col2im."""
         M = rows_b * c.Ho * c.Wo
+        if add is None and self._implicit_dgrad(c) and self.x3:
+            n = 1
+            if dyk is None:
+                dyk = self.dyk[: M * 3 * c.cout].view(M, 3 * c.cout)
+                ops.split_tf32(dy, dyk, ops.SPLIT_LEFT, None, 0, rows=M, cols=c.cout, stream=self.main)
+                n += 1
+            ops.conv_dgrad(dyk, self.wr[c.name], dx, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, pad=c.pad,
+                           Cout=3 * c.cout, deterministic=self.det, stream=self.main)
+            return n
         if add is None and self._implicit_dgrad(c):
             ops.conv_dgrad(dy, self._w(c.name), dx, B=rows_b, H=c.H, W=c.W, C=c.cin, kh=c.k, kw=c.k, pad=c.pad,
                            Cout=c.cout, deterministic=self.det, ws=self.conv_ws, stream=self.main)
@@ -494,8 +531,13 @@ class ConvTrainStep:
             dyr = self.dyr[: 3 * M * c.cout].view(3 * M, c.cout)
             ops.split_tf32(dy, dyk, ops.SPLIT_LEFT, dyr, ops.SPLIT_LEFT, rows=M, cols=c.cout, stream=self.main)
             n += 1
-            ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
-                             stream=self.main)
+            if self.implicit3[c.name]:
+                ops.conv_wgrad(dyr, self.xr3[c.name][: 3 * rows_b * c.H * c.W], gw, B=3 * rows_b, H=c.H, W=c.W, C=c.cin,
+                               kh=c.k, kw=c.k, stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det,
+                               stream=self.main)
+            else:
+                ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
+                                 stream=self.main)
             if dx is not None and not defer_input:
                 n += self._conv_bwd_input(c, dy, rows_b, dx, add, dyk)
         else:
