@@ -121,3 +121,27 @@ def test_ddp_emulation_equals_real_ddp_over_gloo(tmp_path):
             assert err <= 2e-3, (k, err)
         else:
             assert torch.equal(so[k], v), k
+
+
+@pytest.mark.parametrize("seed,n", [(0, 1), (5, 207), (123, 1000), (7, 3000)])
+def test_vectorised_draws_equal_the_per_sample_torch_calls(seed, n):
+    """draw_augmentation replays torch's own mt19937 in one vectorised pass: same draws as the calls torchvision makes,
+    and the global generator is left in the same state (the next torch draw is identical) — fresh after manual_seed,
+    mid-stream, and across several state refills."""
+    from b200step.convnet import draw_augmentation, draw_augmentation_loop
+
+    for warm in (0, 3, 700):
+        torch.manual_seed(seed)
+        if warm:
+            torch.rand(warm)
+        a = draw_augmentation_loop(n)
+        a2 = draw_augmentation_loop(5)
+        tail_a = (torch.randint(0, 1 << 30, (4,)), torch.rand(3), torch.randn(2))
+        torch.manual_seed(seed)
+        if warm:
+            torch.rand(warm)
+        b = draw_augmentation(n)
+        b2 = draw_augmentation(5)
+        tail_b = (torch.randint(0, 1 << 30, (4,)), torch.rand(3), torch.randn(2))
+        assert torch.equal(a, b) and torch.equal(a2, b2)
+        assert all(torch.equal(x, y) for x, y in zip(tail_a, tail_b))
