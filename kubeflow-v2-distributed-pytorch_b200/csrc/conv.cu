@@ -175,19 +175,26 @@ im2col_smallc_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H,
   const int taps = kh * kw, K = taps * C;
   const int64_t rows = (int64_t)B * Ho * Wo;
   const int kcols = (int)ldcol;
+  const uint32_t inv_kw = 65536u / (uint32_t)kw + 1u;     // tap / kw for tap < 64: exact (the host checks kh*kw < 64)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
   for (int64_t m0 = (int64_t)blockIdx.x * IM_ROWS; m0 < rows; m0 += (int64_t)gridDim.x * IM_ROWS) {
     const int nr = (int)min((int64_t)IM_ROWS, rows - m0);
-    for (int i = threadIdx.x; i < nr * taps; i += blockDim.x) {
-      const int r = i / taps, tap = i - r * taps;
-      const int ky = tap / kw, kx = tap - ky * kw;
+    // a warp per col row: the row's pixel coordinates are computed once, the lanes walk its taps
+    for (int r = warp; r < nr; r += nwarp) {
       const int64_t m = m0 + r;
       const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho);
       const int64_t b = m / ((int64_t)Wo * Ho);
-      const int h = ho * stride - pad + ky, w = wo * stride - pad + kx;
-      const bool inside = h >= 0 && h < H && w >= 0 && w < W;
-      const T* src = x + ((b * H + h) * (int64_t)W + w) * C;
-      T* d = tile + r * kcols + tap * C;
-      for (int c = 0; c < C; ++c) d[c] = inside ? src[c] : from_float<T>(0.f);
+      const int h0 = ho * stride - pad, w0 = wo * stride - pad;
+      const T* img = x + b * H * (int64_t)W * C;
+      T* drow = tile + r * kcols;
+      for (int tap = lane; tap < taps; tap += 32) {
+        const int ky = (int)(((uint32_t)tap * inv_kw) >> 16), kx = tap - ky * kw;
+        const int h = h0 + ky, w = w0 + kx;
+        const bool inside = h >= 0 && h < H && w >= 0 && w < W;
+        const T* src = img + ((int64_t)h * W + w) * C;
+        T* d = drow + tap * C;
+        for (int c = 0; c < C; ++c) d[c] = inside ? src[c] : from_float<T>(0.f);
+      }
     }
     for (int i = threadIdx.x; i < nr * (kcols - K); i += blockDim.x) {     // the GEMM's K padding
       const int r = i / (kcols - K);
@@ -666,7 +673,7 @@ extern "C" int b200_im2col(const void* x, void* col, int64_t ldcol, int64_t B, i
     const int grid = grid_for(rows * 32, 256, 16);
     if (dtype == B200_BF16) B200_CHECK_CUDA(launch_pdl(im2col_vec_kernel<bf16_t>, dim3(grid), dim3(256), 0, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, cshift));
     else B200_CHECK_CUDA(launch_pdl(im2col_vec_kernel<float>, dim3(grid), dim3(256), 0, st, (const float*)x, (float*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol, cshift));
-  } else if (C <= 8 && ldcol % vecn == 0 && ldcol * es * IM_ROWS <= 48 * 1024) {   // conv1: rows staged in shared memory
+  } else if (C <= 8 && kh * kw < 64 && ldcol % vecn == 0 && ldcol * es * IM_ROWS <= 48 * 1024) {   // conv1: rows staged in shared memory
     const int grid = grid_for((rows + IM_ROWS - 1) / IM_ROWS * 256, 256, 8);
     const size_t smem = (size_t)ldcol * es * IM_ROWS;
     if (dtype == B200_BF16) B200_CHECK_CUDA(launch_pdl(im2col_smallc_kernel<bf16_t>, dim3(grid), dim3(256), smem, st, (const bf16_t*)x, (bf16_t*)col, (int)B, H, W, C, Ho, Wo, kh, kw, stride, pad, ldcol));
