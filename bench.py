@@ -361,6 +361,8 @@ def run_b200(args, rank, local_rank, world):
         cfg.grouped_wgrad = os.environ["B200STEP_GROUPED_WGRAD"] != "0"
     if os.environ.get("B200STEP_PREFETCH_CTAS"):          # A/B: CTA slots per SM of the overlapped K-pre
         cfg.prefetch_ctas_per_sm = int(os.environ["B200STEP_PREFETCH_CTAS"])
+    if os.environ.get("B200STEP_EMB_SIDE"):               # A/B: K-embbwd on a side stream under the grouped wgrad
+        cfg.emb_bwd_side = os.environ["B200STEP_EMB_SIDE"] != "0"
     if os.environ.get("B200STEP_PREFETCH_PRE"):           # A/B: K-pre of the next batch under wgrad / the all-reduces
         cfg.prefetch_pre = os.environ["B200STEP_PREFETCH_PRE"] != "0"
     idx = rank_indices(rows, world, rank)

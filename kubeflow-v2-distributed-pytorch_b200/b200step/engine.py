@@ -79,6 +79,7 @@ class StepConfig:
     deterministic_wgrad: bool = False    # convolutional path: filter gradients summed in a fixed order (no split of the
                                          # batch dimension, B200_FLAG_DETERMINISTIC): the whole step is then
                                          # bit-reproducible run to run, at the cost of wgrad occupancy
+    emb_bwd_side: Optional[bool] = None  # world == 1: K-embbwd on a side stream under the grouped wgrad GEMM (None = on)
     grouped_wgrad: Optional[bool] = None # all layers' wgrad GEMMs in one launch.  None = only when world == 1:
                                          # equal at B = 65536, 3 % faster at B = 4096; per-layer launches let each
                                          # bucket's all-reduce start earlier when world > 1
@@ -425,6 +426,7 @@ class TrainStep:
         if cfg.world > 1 and cfg.overlap_comm:
             reserve = DEFAULT_COMM_SM_RESERVE if cfg.comm_sm_reserve is None else cfg.comm_sm_reserve
         comm_live = False
+        join_emb = False
         for ci, (r0, rows) in enumerate(chunks):
             sl = slice(r0, r0 + rows)
             last_chunk = ci == len(chunks) - 1
@@ -483,9 +485,23 @@ class TrainStep:
                     ops.linear_dgrad(self.dyk[0][:rows] if x3 else dys[0], self.wr[0] if x3 else self._w(0), None,
                                      self.dx0[sl], M=rows, N=3 * dims[0][1] if x3 else dims[0][1], K=self.k0,
                                      relu=False, reverse_m=cfg.l2_tile_order and (L - 1) % 2 == 0, stream=st)
+                    # K-embbwd only feeds the optimizer.  On one GPU (single chunk, no overlapped prefetch) it runs on
+                    # the side stream UNDER the grouped wgrad GEMM: its 28-register blocks fit next to the persistent
+                    # GEMM CTA (66 registers x 384 threads, all the shared memory) and it is bound by L2 atomics, not
+                    # by the tensor pipe.  Joined before K-opt.
+                    emb_side = (cfg.emb_bwd_side if cfg.emb_bwd_side is not None else True) and cfg.world == 1 and \
+                        len(chunks) == 1 and not (prefetch and self.overlap_pre)
+                    es = st
+                    if emb_side:
+                        self._ev_fork.record(st)
+                        self.pre_stream.wait_event(self._ev_fork)
+                        es = self.pre_stream
                     ops.emb_bwd(self.dx0[sl], self.idx[sl], self.gtables, batch=rows, emb_col0=0,
                                 num_cat=spec.num_cat, table_rows=spec.cardinality, embed_dim=spec.embed_dim,
-                                stream=st)
+                                stream=es)
+                    if emb_side:
+                        self._ev_join.record(self.pre_stream)
+                        join_emb = True
                     n += 2
                 if last_chunk:
                     for bi in bucket_of.get(-1, []):
@@ -563,6 +579,8 @@ class TrainStep:
         # all-reduce was issued first), K-pre of the next batch follows it and runs under the all-reduces that are
         # still in flight; the step counter (dropout stream, Adam's t) still moves in the last launch.
         cur = self.cursor if advance else None
+        if join_emb:
+            st.wait_event(self._ev_join)       # the table gradients from the side stream
         for ri, (ev, s_, e_) in enumerate(ranges):
             first_range, last_range = ri == 0, ri == len(ranges) - 1
             adv_cursor = cur if (first_range if prefetch else last_range) else None
