@@ -406,6 +406,9 @@ class ConvTrainStep:
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.side = torch.cuda.Stream(device=dev)          # filter-gradient GEMMs, off the backward chain's critical path
         self.side_wgrad = (not self.x3) and os.environ.get("B200STEP_SIDE_WGRAD", "1") != "0"
+        self.side_wgrad3 = self.x3 and os.environ.get("B200STEP_SIDE_WGRAD", "1") != "0"
+        if self.side_wgrad3:     # the side stream reads dy's [hi ; hi ; lo] copy after the main stream has moved on
+            self.dyr3 = {c.name: torch.zeros(3 * B * c.Ho * c.Wo, c.cout, **f32) for c in convs}
         self._ev_dy = {c.name: torch.cuda.Event() for c in convs}
         self._ev_wg = {c.name: torch.cuda.Event() for c in convs}
         self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -569,16 +572,25 @@ class ConvTrainStep:
         n = 0
         if self.x3:
             dyk = self.dyk[: M * 3 * c.cout].view(M, 3 * c.cout)
-            dyr = self.dyr[: 3 * M * c.cout].view(3 * M, c.cout)
+            side = self.side_wgrad3
+            dyr = (self.dyr3[c.name][: 3 * M] if side else self.dyr[: 3 * M * c.cout].view(3 * M, c.cout))
             ops.split_tf32(dy, dyk, ops.SPLIT_LEFT, dyr, ops.SPLIT_LEFT, rows=M, cols=c.cout, stream=self.main)
             n += 1
+            wstream = self.main
+            if side:             # fork: the filter gradient (its own hi/lo copy of dy) runs beside the backward chain
+                self._ev_dy[c.name].record(self.main)
+                self.side.wait_event(self._ev_dy[c.name])
+                wstream = self.side
             if self.implicit3[c.name]:
                 ops.conv_wgrad(dyr, self.xr3[c.name][: 3 * rows_b * c.H * c.W], gw, B=3 * rows_b, H=c.H, W=c.W, C=c.cin,
                                kh=c.k, kw=c.k, stride=c.stride, pad=c.pad, Cout=c.cout, deterministic=self.det,
-                               stream=self.main)
+                               stream=wstream)
             else:
                 ops.linear_wgrad(dyr, self.colr[c.name][: 3 * M], gw, M=3 * M, N=c.cout, K=c.Kp, deterministic=self.det,
-                                 stream=self.main)
+                                 stream=wstream)
+            if side:
+                self._ev_wg[c.name].record(self.side)
+                self._side_pending.append((c.name + ".weight", self._ev_wg[c.name]))
             if dx is not None and not defer_input:
                 n += self._conv_bwd_input(c, dy, rows_b, dx, add, dyk)
         else:
