@@ -227,16 +227,14 @@ col2im_kernel(const T* __restrict__ dcol, int64_t ldcol, const T* __restrict__ a
     const int w = (int)(pix % W), h = (int)((pix / W) % H);
     const int64_t b = pix / ((int64_t)W * H);
     float4 acc = add != nullptr ? Vec4<T>::load(add + pix * C + c) : make_float4(0, 0, 0, 0);
-    for (int ky = 0; ky < kh; ++ky) {
-      const int hn = h + pad - ky;
-      if (hn < 0 || hn % stride != 0) continue;
-      const int ho = hn / stride;
-      if (ho >= Ho) continue;
-      for (int kx = 0; kx < kw; ++kx) {
-        const int wn = w + pad - kx;
-        if (wn < 0 || wn % stride != 0) continue;
-        const int wo = wn / stride;
-        if (wo >= Wo) continue;
+    // only the windows that contain this pixel: ho in [ceil((h + pad - kh + 1) / stride), floor((h + pad) / stride)]
+    const int hn = h + pad - kh + 1, wn = w + pad - kw + 1;
+    const int hlo = hn <= 0 ? 0 : (hn + stride - 1) / stride, wlo = wn <= 0 ? 0 : (wn + stride - 1) / stride;
+    const int hhi = min(Ho - 1, (h + pad) / stride), whi = min(Wo - 1, (w + pad) / stride);
+    for (int ho = hhi; ho >= hlo; --ho) {                 // descending ho = ascending tap: the order of the sums is kept
+      const int ky = h + pad - ho * stride;
+      for (int wo = whi; wo >= wlo; --wo) {
+        const int kx = w + pad - wo * stride;
         const int64_t m = (b * Ho + ho) * (int64_t)Wo + wo;
         const float4 v = Vec4<T>::load(dcol + m * ldcol + (int64_t)(ky * kw + kx) * C + c);
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
@@ -549,17 +547,18 @@ maxpool_bwd_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, cons
     const int w = (int)(pix % W), h = (int)((pix / W) % H);
     const int64_t b = pix / ((int64_t)W * H);
     float4 acc = make_float4(0, 0, 0, 0);
-    const bool s2 = stride == 2;                          // the ResNet stem: shifts instead of divisions
-    for (int ky = 0; ky < k; ++ky) {
-      const int hn = h + pad - ky;
-      if (hn < 0) continue;
-      const int hq = s2 ? hn >> 1 : hn / stride;
-      if (hq * stride != hn || hq >= Ho) continue;
-      for (int kx = 0; kx < k; ++kx) {
-        const int wn = w + pad - kx;
-        if (wn < 0) continue;
-        const int wq = s2 ? wn >> 1 : wn / stride;
-        if (wq * stride != wn || wq >= Wo) continue;
+    // only the windows that contain this pixel: ho in [ceil((h + pad - k + 1) / stride), floor((h + pad) / stride)]
+    // (at most two per dimension for the ResNet stem's 3x3 / stride 2), clipped to the output
+    const bool s2 = stride == 2;
+    const int hn = h + pad - k + 1, wn = w + pad - k + 1;
+    const int hlo = hn <= 0 ? 0 : (s2 ? (hn + 1) >> 1 : (hn + stride - 1) / stride);
+    const int wlo = wn <= 0 ? 0 : (s2 ? (wn + 1) >> 1 : (wn + stride - 1) / stride);
+    const int hhi = min(Ho - 1, s2 ? (h + pad) >> 1 : (h + pad) / stride);
+    const int whi = min(Wo - 1, s2 ? (w + pad) >> 1 : (w + pad) / stride);
+    for (int hq = hlo; hq <= hhi; ++hq) {
+      const int ky = h + pad - hq * stride;
+      for (int wq = wlo; wq <= whi; ++wq) {
+        const int kx = w + pad - wq * stride;
         const int64_t m = (b * Ho + hq) * (int64_t)Wo + wq;
         const uchar4 tp = *reinterpret_cast<const uchar4*>(tap_in + m * C + c);
         float4 d = Vec4<T>::load(dout + m * C + c);
