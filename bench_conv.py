@@ -136,7 +136,7 @@ def profile_kernels(eng, B):
 
     es = 2 if eng.dt == torch.bfloat16 else 4
     x3 = 3 if eng.x3 else 1
-    names = ["image_augment", "im2col", "col2im", "bn_fwd_stats", "bn_fwd_apply", "bn_bwd_reduce", "bn_bwd_apply",
+    names = ["image_augment", "im2col", "col2im", "bn_fwd_stats", "bn_fwd_apply", "bn_bwd_reduce", "bn_bwd_apply", "bn_fwd", "bn_bwd",
              "maxpool_fwd", "maxpool_bwd", "avgpool_fwd", "avgpool_bwd", "linear_fwd", "linear_ce", "linear_dgrad",
              "linear_wgrad", "conv_fwd", "conv_wgrad", "conv_dgrad", "sgd_step", "adam_step", "split_tf32"]
     orig = {n: getattr(ops, n) for n in names}
@@ -163,6 +163,11 @@ def profile_kernels(eng, B):
             return name, {"bytes": es * (k["B"] * k["H"] * k["W"] * k["C"] + k["B"] * Ho * Wo * a[1].shape[1])}
         if name == "col2im":
             return name, {"bytes": es * (a[0].shape[0] * a[0].shape[1] + k["B"] * k["H"] * k["W"] * k["C"] * (2 if a[1] is not None else 1))}
+        if name == "bn_fwd":       # y read (twice, the second time from cache), out written, residual read
+            return name, {"bytes": es * k["M"] * k["C"] * (3 if a[1] is not None else 2)}
+        if name == "bn_bwd":       # dout (+dout2), out, y read; dy (+dz) written
+            ins = 2 + (a[1] is not None) + (k.get("dout2") is not None)
+            return name, {"bytes": es * k["M"] * k["C"] * (ins + (2 if a[4] is not None else 1))}
         if name == "bn_fwd_stats":
             return name, {"bytes": es * k["M"] * k["C"]}
         if name == "bn_fwd_apply":

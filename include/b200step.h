@@ -350,6 +350,17 @@ int b200_bn_bwd_apply(const void* dout, const void* dout2, const void* out, cons
                       const float* mean, const float* invstd, const float* gamma, const float* dgamma,
                       const float* dbeta, int dtype, b200_stream_t stream);
 
+/* The same two pairs as ONE launch each: statistics + apply (b200_bn_fwd) and reduce + apply (b200_bn_bwd).  Every
+ * block waits inside the kernel for the last block's per-channel result and then treats its own rows, which are still in
+ * cache: one launch and one DRAM pass instead of two.  Same arguments, results and scratch rule as the pairs above. */
+int b200_bn_fwd(const void* y, const void* res, void* out, int64_t M, int64_t C, float eps, float momentum, float* mean,
+                float* invstd, const float* gamma, const float* beta, int relu, float* running_mean,
+                float* running_var, int64_t* num_batches, float* scratch, int64_t scratch_floats, int dtype,
+                b200_stream_t stream);
+int b200_bn_bwd(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz_out, int64_t M,
+                int64_t C, const float* mean, const float* invstd, const float* gamma, float* dgamma, float* dbeta,
+                float* scratch, int64_t scratch_floats, int dtype, b200_stream_t stream);
+
 /* nn.MaxPool2d(k, stride, pad) on NHWC; taps[m, c] (one byte per output element) records the winning window position
  * (first maximum in row-major window order, NaN wins — aten's rule) for the backward gather. */
 int b200_maxpool_fwd(const void* x, void* out, uint8_t* taps, int64_t B, int H, int W, int C, int k, int stride,

@@ -334,6 +334,11 @@ class ConvTrainStep:
         self.bn_mean = torch.zeros(o, **f32)
         self.bn_invstd = torch.zeros(o, **f32)
         self.bn_scratch = torch.zeros(ops.bn_scratch_floats(512), **f32)
+        # statistics + apply (and reduce + apply) as one launch each (blocks wait in-kernel for the per-channel result).
+        # Off: measured 2.29 against 2.01 ms/step — the waiting blocks keep their shared memory, so the side stream's
+        # wgrad GEMM CTAs cannot start under them, and the apply phase runs with the reduction's narrow grid
+        # (profiles/r02_bn_fused_ab.md)
+        self.bn_fused = os.environ.get("B200STEP_BN_FUSED", "0") == "1"
 
         # ---- activations (NHWC matrices) ------------------------------------------------------------------------
         convs = [layout.stem] + [c for b in layout.blocks for c in (b.conv1, b.conv2, b.down) if c is not None]
@@ -620,6 +625,10 @@ class ConvTrainStep:
         M, C = y.shape
         mean, invstd, rm, rv, nb = self._bn(bn)
         n = 1
+        if training and self.bn_fused:
+            ops.bn_fwd(y, res, out, mean, invstd, self._pv(bn + ".weight"), self._pv(bn + ".bias"), rm, rv, nb,
+                       self.bn_scratch, M=M, C=C, relu=relu, stream=self.main)
+            return 1
         if training:
             ops.bn_fwd_stats(y, mean, invstd, rm, rv, nb, self.bn_scratch, M=M, C=C, stream=self.main)
             n += 1
@@ -633,6 +642,10 @@ class ConvTrainStep:
         M, C = y.shape
         mean, invstd, _, _, _ = self._bn(bn)
         dg, db = self._pv(bn + ".weight", self.g), self._pv(bn + ".bias", self.g)
+        if self.bn_fused:
+            ops.bn_bwd(dout, out, y, dy, dz, mean, invstd, self._pv(bn + ".weight"), dg, db, self.bn_scratch, M=M, C=C,
+                       dout2=dout2, stream=self.main)
+            return 1 + self._grad_done(bn + ".bias") + self._grad_done(bn + ".weight")
         ops.bn_bwd_reduce(dout, out, y, mean, invstd, dg, db, self.bn_scratch, M=M, C=C, dout2=dout2, stream=self.main)
         ops.bn_bwd_apply(dout, out, y, dy, dz, mean, invstd, self._pv(bn + ".weight"), dg, db, M=M, C=C, dout2=dout2,
                          stream=self.main)

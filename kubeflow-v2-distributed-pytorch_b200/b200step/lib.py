@@ -66,6 +66,8 @@ SIGNATURES = {
     "b200_bn_fwd_apply": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _i, _i, _p]),
     "b200_bn_bwd_reduce": (_i, [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i64, _i, _p]),
     "b200_bn_bwd_apply": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _i, _p]),
+    "b200_bn_fwd": (_i, [_p, _p, _p, _i64, _i64, _f, _f, _p, _p, _p, _p, _i, _p, _p, _p, _p, _i64, _i, _p]),
+    "b200_bn_bwd": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _i, _p]),
     "b200_maxpool_fwd": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_maxpool_bwd": (_i, [_p, _p, _p, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200_avgpool_fwd": (_i, [_p, _p, _i64, _i, _i, _i, _p]),

@@ -318,6 +318,24 @@ def bn_bwd_apply(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, *
                            ptr(gamma), ptr(dgamma), ptr(dbeta), dtype_code(y.dtype), _stream(stream))
 
 
+def bn_fwd(y, res, out, mean, invstd, gamma, beta, running_mean, running_var, num_batches, scratch, *, M: int, C: int,
+           relu: bool, eps: float = 1e-5, momentum: float = 0.1, stream=None):
+    """bn_fwd_stats + bn_fwd_apply as one launch (include/b200step.h: b200_bn_fwd)."""
+    _cuda(y, res, out, mean, invstd, gamma, beta, running_mean, running_var, num_batches, scratch)
+    get_lib().bn_fwd(ptr(y), ptr(res), ptr(out), M, C, float(eps), float(momentum), ptr(mean), ptr(invstd), ptr(gamma),
+                     ptr(beta), int(relu), ptr(running_mean), ptr(running_var), ptr(num_batches), ptr(scratch),
+                     scratch.numel(), dtype_code(y.dtype), _stream(stream))
+
+
+def bn_bwd(dout, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, scratch, *, M: int, C: int, dout2=None,
+           stream=None):
+    """bn_bwd_reduce + bn_bwd_apply as one launch (include/b200step.h: b200_bn_bwd)."""
+    _cuda(dout, dout2, out, y, dy, dz_out, mean, invstd, gamma, dgamma, dbeta, scratch)
+    get_lib().bn_bwd(ptr(dout), ptr(dout2), ptr(out), ptr(y), ptr(dy), ptr(dz_out), M, C, ptr(mean), ptr(invstd),
+                     ptr(gamma), ptr(dgamma), ptr(dbeta), ptr(scratch), scratch.numel(), dtype_code(y.dtype),
+                     _stream(stream))
+
+
 def maxpool_fwd(x, out, taps, *, B: int, H: int, W: int, C: int, k: int = 3, stride: int = 2, pad: int = 1,
                 stream=None):
     _cuda(x, out, taps)

@@ -496,6 +496,165 @@ bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, con
   }
 }
 
+// ---- fused variants: statistics AND apply in one launch ------------------------------------------------------------
+// Same first phase as above.  Then, instead of ending the grid and launching the apply kernel, every block waits for
+// the last block's result (an epoch word next to the ticket: read before arriving, bumped with a release store after the
+// per-channel results are written) and applies it to ITS OWN rows, which it read a few microseconds earlier and
+// which are still in L1 / L2.  One launch and one DRAM pass instead of two.  All blocks are co-resident (the grid is at
+// most two blocks per SM and no other kernel waits on this one while it runs), so the wait cannot deadlock.
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void bn_wait_epoch(const uint32_t* epoch, uint32_t e0) {
+  if (threadIdx.x == 0)
+    while (ld_acquire_u32(epoch) == e0) __nanosleep(40);
+  __syncthreads();
+}
+__device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_fwd_fused_kernel(const T* __restrict__ y, const T* __restrict__ res, T* __restrict__ out, int64_t M, int C,
+                    float* __restrict__ partials, uint32_t* ticket, uint32_t* epoch, float eps, float momentum,
+                    float* mean, float* invstd, const float* __restrict__ gamma, const float* __restrict__ beta, int relu,
+                    float* __restrict__ running_mean, float* __restrict__ running_var, int64_t* __restrict__ num_batches) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4, lanes = BN_THREADS / vc;
+  const int cv = threadIdx.x % vc, ry = threadIdx.x / vc;
+  const int64_t chunk = (M + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = blockIdx.x * chunk, r1 = min(M, r0 + chunk);
+  __shared__ uint32_t s_e0;
+  if (threadIdx.x == 0) s_e0 = ld_acquire_u32(epoch);          // before this block arrives at the ticket
+  float4 s = make_float4(0, 0, 0, 0), q = make_float4(0, 0, 0, 0);
+  if (ry < lanes)
+#pragma unroll 8
+    for (int64_t r = r0 + ry; r < r1; r += lanes) {
+      const float4 v = Vec4<T>::load(y + r * C + cv * 4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      q.x = fmaf(v.x, v.x, q.x); q.y = fmaf(v.y, v.y, q.y); q.z = fmaf(v.z, v.z, q.z); q.w = fmaf(v.w, v.w, q.w);
+    }
+  bn_block_reduce(s, q, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
+  const uint32_t e0 = s_e0;
+  if (bn_last_block(ticket)) {
+    __shared__ double totals[2 * BN_MAX_C];
+    bn_fold_partials(partials, (int)gridDim.x, C, totals);
+    for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+      const double ds = totals[c], dq = totals[C + c];
+      const double mu = ds / (double)M;
+      double var = dq / (double)M - mu * mu;
+      if (var < 0.0) var = 0.0;
+      mean[c] = (float)mu;
+      invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+      if (running_mean != nullptr) {
+        const double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mu);
+        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+      }
+    }
+    if (threadIdx.x == 0 && num_batches != nullptr) num_batches[0] += 1;
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_u32(epoch, e0 + 1);
+  }
+  bn_wait_epoch(epoch, e0);
+  if (ry >= lanes) return;
+  const float4 mu = ldcg4(mean + cv * 4), is = ldcg4(invstd + cv * 4);
+  const float4 g = *reinterpret_cast<const float4*>(gamma + cv * 4), be = *reinterpret_cast<const float4*>(beta + cv * 4);
+#pragma unroll 4
+  for (int64_t r = r0 + ry; r < r1; r += lanes) {
+    const int64_t off = r * C + cv * 4;
+    const float4 v = Vec4<T>::load(y + off);
+    float4 o;
+    o.x = fmaf((v.x - mu.x) * is.x, g.x, be.x); o.y = fmaf((v.y - mu.y) * is.y, g.y, be.y);
+    o.z = fmaf((v.z - mu.z) * is.z, g.z, be.z); o.w = fmaf((v.w - mu.w) * is.w, g.w, be.w);
+    if (res != nullptr) {
+      const float4 rr = Vec4<T>::load(res + off);
+      o.x += rr.x; o.y += rr.y; o.z += rr.z; o.w += rr.w;
+    }
+    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+    Vec4<T>::store(out + off, o);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_fused_kernel(const T* __restrict__ dout, const T* __restrict__ dout2, const T* __restrict__ out,
+                    const T* __restrict__ y, T* __restrict__ dy, T* __restrict__ dz_out, int64_t M, int C,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    float* __restrict__ partials, uint32_t* ticket, uint32_t* epoch, float* dgamma, float* dbeta) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int vc = C / 4, lanes = BN_THREADS / vc;
+  const int cv = threadIdx.x % vc, ry = threadIdx.x / vc;
+  const int64_t chunk = (M + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = blockIdx.x * chunk, r1 = min(M, r0 + chunk);
+  __shared__ uint32_t s_e0;
+  if (threadIdx.x == 0) s_e0 = ld_acquire_u32(epoch);
+  const float4 mu = *reinterpret_cast<const float4*>(mean + cv * 4), is = *reinterpret_cast<const float4*>(invstd + cv * 4);
+  float4 sb = make_float4(0, 0, 0, 0), sg = make_float4(0, 0, 0, 0);
+  if (ry < lanes)
+#pragma unroll 4
+    for (int64_t r = r0 + ry; r < r1; r += lanes) {
+      const int64_t off = r * C + cv * 4;
+      float4 d = Vec4<T>::load(dout + off);
+      if (dout2 != nullptr) {
+        const float4 e = Vec4<T>::load(dout2 + off);
+        d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+      }
+      if (out != nullptr) {
+        const float4 o = Vec4<T>::load(out + off);
+        d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
+      }
+      const float4 v = Vec4<T>::load(y + off);
+      sb.x += d.x; sb.y += d.y; sb.z += d.z; sb.w += d.w;
+      sg.x = fmaf(d.x, (v.x - mu.x) * is.x, sg.x); sg.y = fmaf(d.y, (v.y - mu.y) * is.y, sg.y);
+      sg.z = fmaf(d.z, (v.z - mu.z) * is.z, sg.z); sg.w = fmaf(d.w, (v.w - mu.w) * is.w, sg.w);
+    }
+  bn_block_reduce(sb, sg, vc, partials + (int64_t)blockIdx.x * 2 * C, C);
+  const uint32_t e0 = s_e0;
+  if (bn_last_block(ticket)) {
+    __shared__ double totals[2 * BN_MAX_C];
+    bn_fold_partials(partials, (int)gridDim.x, C, totals);
+    for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+      dbeta[c] = (float)totals[c];
+      dgamma[c] = (float)totals[C + c];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_u32(epoch, e0 + 1);
+  }
+  bn_wait_epoch(epoch, e0);
+  if (ry >= lanes) return;
+  const float4 g = *reinterpret_cast<const float4*>(gamma + cv * 4);
+  const float4 dg = ldcg4(dgamma + cv * 4), db = ldcg4(dbeta + cv * 4);
+  const float inv_m = 1.f / (float)M;
+#pragma unroll 2
+  for (int64_t r = r0 + ry; r < r1; r += lanes) {
+    const int64_t off = r * C + cv * 4;
+    float4 d = Vec4<T>::load(dout + off);
+    if (dout2 != nullptr) {
+      const float4 e = Vec4<T>::load(dout2 + off);
+      d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+    }
+    if (out != nullptr) {
+      const float4 o = Vec4<T>::load(out + off);
+      d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
+    }
+    if (dz_out != nullptr) Vec4<T>::store(dz_out + off, d);
+    const float4 v = Vec4<T>::load(y + off);
+    float4 rr;
+    rr.x = g.x * is.x * (d.x - db.x * inv_m - (v.x - mu.x) * is.x * dg.x * inv_m);
+    rr.y = g.y * is.y * (d.y - db.y * inv_m - (v.y - mu.y) * is.y * dg.y * inv_m);
+    rr.z = g.z * is.z * (d.z - db.z * inv_m - (v.z - mu.z) * is.z * dg.z * inv_m);
+    rr.w = g.w * is.w * (d.w - db.w * inv_m - (v.w - mu.w) * is.w * dg.w * inv_m);
+    Vec4<T>::store(dy + off, rr);
+  }
+}
+
 // ---- MaxPool2d(kernel 3, stride 2, padding 1) (torchvision resnet.py: self.maxpool) ------------------------------------
 // fwd keeps the winning tap (first maximum in (ky, kx) order, NaN wins: aten's `val > max || isnan(val)`) as one byte
 // per output element; bwd is the gather over the <= 4 windows that contain an input pixel.
@@ -808,6 +967,69 @@ extern "C" int b200_bn_bwd_apply(const void* dout, const void* dout2, const void
   return dtype == B200_BF16
              ? bn_bwd_apply_t<bf16_t>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st)
              : bn_bwd_apply_t<float>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, dgamma, dbeta, st);
+}
+
+// ---- fused BatchNorm entry points ----------------------------------------------------------------------------------
+// the grid must be co-resident (blocks wait for the last one): clamp it to what the device can hold at once
+template <typename K>
+static int bn_fused_blocks(K kern, int64_t M, int64_t C) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, BN_THREADS, 0) != cudaSuccess || per_sm < 1) return 0;
+  const int64_t cap = (int64_t)std::min(per_sm, 2) * sm_count();
+  return (int)std::min<int64_t>(bn_blocks(M, C), cap);
+}
+template <typename T>
+static int bn_fwd_fused_t(const void* y, const void* res, void* out, int64_t M, int C, float* scratch, float eps,
+                          float momentum, float* mean, float* invstd, const float* gamma, const float* beta, int relu,
+                          float* rm, float* rv, int64_t* nb, cudaStream_t st) {
+  const int blocks = bn_fused_blocks(bn_fwd_fused_kernel<T>, M, C);
+  B200_REQUIRE(blocks >= 1, "bn_fwd: the fused kernel cannot be resident on this device");
+  uint32_t* words = reinterpret_cast<uint32_t*>(scratch);
+  B200_CHECK_CUDA(launch_pdl(bn_fwd_fused_kernel<T>, dim3(blocks), dim3(BN_THREADS), 0, st, (const T*)y, (const T*)res,
+                             (T*)out, M, C, scratch + BN_SCRATCH_HEAD, words, words + 1, eps, momentum, mean, invstd,
+                             gamma, beta, relu, rm, rv, nb));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_fwd(const void* y, const void* res, void* out, int64_t M, int64_t C, float eps, float momentum,
+                           float* mean, float* invstd, const float* gamma, const float* beta, int relu,
+                           float* running_mean, float* running_var, int64_t* num_batches, float* scratch,
+                           int64_t scratch_floats, int dtype, b200_stream_t stream) {
+  CONV_COMMON("bn_fwd", ALIGNED16(y) && ALIGNED16(out) && ALIGNED16_OR_NULL(res) && ALIGNED16(mean) && ALIGNED16(invstd) &&
+                            ALIGNED16(gamma) && ALIGNED16(beta) && scratch != nullptr);
+  if (int r = bn_check("bn_fwd", M, C, scratch, scratch_floats)) return r;
+  B200_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_fwd: running_mean / running_var go together");
+  return dtype == B200_BF16
+             ? bn_fwd_fused_t<bf16_t>(y, res, out, M, (int)C, scratch, eps, momentum, mean, invstd, gamma, beta, relu,
+                                      running_mean, running_var, num_batches, st)
+             : bn_fwd_fused_t<float>(y, res, out, M, (int)C, scratch, eps, momentum, mean, invstd, gamma, beta, relu,
+                                     running_mean, running_var, num_batches, st);
+}
+template <typename T>
+static int bn_bwd_fused_t(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz, int64_t M,
+                          int C, const float* mean, const float* invstd, const float* gamma, float* scratch,
+                          float* dgamma, float* dbeta, cudaStream_t st) {
+  const int blocks = bn_fused_blocks(bn_bwd_fused_kernel<T>, M, C);
+  B200_REQUIRE(blocks >= 1, "bn_bwd: the fused kernel cannot be resident on this device");
+  uint32_t* words = reinterpret_cast<uint32_t*>(scratch);
+  B200_CHECK_CUDA(launch_pdl(bn_bwd_fused_kernel<T>, dim3(blocks), dim3(BN_THREADS), 0, st, (const T*)dout,
+                             (const T*)dout2, (const T*)out, (const T*)y, (T*)dy, (T*)dz, M, C, mean, invstd, gamma,
+                             scratch + BN_SCRATCH_HEAD, words, words + 1, dgamma, dbeta));
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200_bn_bwd(const void* dout, const void* dout2, const void* out, const void* y, void* dy, void* dz_out,
+                           int64_t M, int64_t C, const float* mean, const float* invstd, const float* gamma,
+                           float* dgamma, float* dbeta, float* scratch, int64_t scratch_floats, int dtype,
+                           b200_stream_t stream) {
+  CONV_COMMON("bn_bwd", ALIGNED16(dout) && ALIGNED16_OR_NULL(dout2) && ALIGNED16(y) && ALIGNED16(dy) &&
+                            ALIGNED16_OR_NULL(out) && ALIGNED16_OR_NULL(dz_out) && ALIGNED16(mean) && ALIGNED16(invstd) &&
+                            ALIGNED16(gamma) && ALIGNED16(dgamma) && ALIGNED16(dbeta) && scratch != nullptr);
+  if (int r = bn_check("bn_bwd", M, C, scratch, scratch_floats)) return r;
+  return dtype == B200_BF16 ? bn_bwd_fused_t<bf16_t>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, scratch,
+                                                     dgamma, dbeta, st)
+                            : bn_bwd_fused_t<float>(dout, dout2, out, y, dy, dz_out, M, (int)C, mean, invstd, gamma, scratch,
+                                                    dgamma, dbeta, st);
 }
 
 // ---- pooling entry points -------------------------------------------------------------------------------------------
