@@ -47,6 +47,8 @@ struct GemmParams {
   // convolution as implicit GEMM: the K-major A operand comes from an im2col-mode tensor map over the NHWC input
   // (k-block kb = filter tap kb / cv_cpb, channels (kb % cv_cpb) * BLOCK_K ...); 0 = plain matrix A
   int cv_on, cv_Ho, cv_Wo, cv_stride, cv_pad, cv_kw, cv_cpb;
+  int n_eff;                 // UMMA N of this launch: 256, or 128 / 64 when the whole output is that narrow (one column
+                             // tile): the MMAs then skip the unused accumulator columns (0 = choose in launch_gemm)
   int cv_C, cv_K;            // wgrad (cv_on 1, MN-major B from the input): channels and kh*kw*C;
                              // dgrad (cv_on 2): input channels and the number of filter taps
 };
@@ -127,7 +129,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         int mt = tile / p.n_tiles;
         if (p.flags & B200_FLAG_REVERSE_M) mt = p.m_tiles - 1 - mt;       // walk the row tiles from the last one down
         const int m0 = mt * TILE_M + rank * BLOCK_M;                      // this CTA's rows of A
-        const int n0 = (tile % p.n_tiles) * BLOCK_N + rank * B_ROWS;     // this CTA's share of the B tile
+        // this CTA's share of the B tile: half of the columns the MMA really computes (p.n_eff <= BLOCK_N)
+        const int n0 = (tile % p.n_tiles) * BLOCK_N + rank * (p.n_eff / kCtas);
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
         int cv_w = 0, cv_h = 0, cv_n = 0;       // implicit GEMM: window origin of this CTA's first output pixel
@@ -236,6 +239,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
+      // narrow outputs (N <= 64 / 128 in a single column tile): issue N = 64 / 128 MMAs instead of 256-wide ones
+      const uint32_t idesc = p.n_eff == BLOCK_N ? IDESC : make_idesc(kTf32 ? 2 : 1, kAMN, kBMN, BLOCK_M * kCtas, p.n_eff);
       for (int w = unit; w < total; w += nunits, ++it) {
         const int split = w / tiles;
         const int kb0 = split * p.kb_per_split;
@@ -261,8 +266,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #ifdef B200STEP_EXPERIMENTS
             if (p.flags & 0x800) continue;  // timing experiment: stream the operands, skip the MMAs
 #endif
-            if constexpr (kCtas == 2) umma_ss_pair<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
-            else umma_ss<kTf32>(d_tmem, ad, bd, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (kCtas == 2) umma_ss_pair<kTf32>(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_ss<kTf32>(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           // frees the smem stage (in both CTAs of a pair) once these MMAs retire
           if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[s], 3);
@@ -823,6 +828,11 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
                        cudaStream_t st, int unit_multiple = 1, int* units_out = nullptr) {
   GemmParams p = p_in;
   p.flags |= gemm_debug_flags();
+  if (p.n_eff == 0) {
+    static const bool narrow = getenv("B200STEP_NARROW_MMA") == nullptr || atoi(getenv("B200STEP_NARROW_MMA")) != 0;
+    p.n_eff = BLOCK_N;
+    if (narrow && p.n_tiles == 1) p.n_eff = p.N <= 64 ? 64 : (p.N <= 128 ? 128 : BLOCK_N);
+  }
   return gemm_ctas() == 2
              ? launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 2>(ta, tb, tc, p, st, unit_multiple, units_out)
              : launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 1>(ta, tb, tc, p, st, unit_multiple, units_out);
