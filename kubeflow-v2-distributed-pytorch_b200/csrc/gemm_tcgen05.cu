@@ -124,6 +124,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
+      // B rows this CTA stages: its half of the columns the MMAs compute.  Narrow outputs (n_eff = 64 / 128) stage a
+      // quarter / half of the B tile: fewer TMA row requests per stage (the tensor map's box, built by the entry point
+      // from the same n_eff, is that small for K-major B; MN-major B simply issues fewer 128-byte column boxes)
+      const int brows = p.n_eff / kCtas;
+      const int b_boxes = brows >= EPR ? brows / EPR : 1;
+      const uint32_t stage_tx = A_TILE_BYTES + (kBMN ? b_boxes * MN_BOX_BYTES : brows * 128);
       for (int w = unit; w < total; w += nunits) {
         const int tile = w % tiles, split = w / tiles;
         int mt = tile / p.n_tiles;
@@ -146,7 +152,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint8_t* sb = sa + A_TILE_BYTES;
           if constexpr (kCtas == 2) {
             // both CTAs' bytes are credited to the LEADER's full barrier (the MMA thread waits there)
-            if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+            if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * stage_tx);
             const uint32_t fb = smem_u32(&full_bar[s]) & 0xFEFFFFFFu;  // same offset in the leader CTA
             if constexpr (!kAMN) {
               if (p.cv_on) {
@@ -169,7 +175,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const int tap = kb / p.cv_cpb, co0 = (kb - tap * p.cv_cpb) * BLOCK_K;
               const int wc0 = (p.cv_K - 1 - tap) * p.cv_C + n0;
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j)
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes)
                 tma_load_2d_pair(sb + j * MN_BOX_BYTES, &tmB, fb, wc0 + j * EPR, co0);
             } else if (p.cv_on) {
               // wgrad of a convolution: B(n' = filter column, k' = pixel) straight from the NHWC input; this k-block
@@ -177,7 +183,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const int pix = kb * BLOCK_K, q = pix % p.cv_Wo, t = pix / p.cv_Wo;
               const int bw = q * p.cv_stride - p.cv_pad, bh = (t % p.cv_Ho) * p.cv_stride - p.cv_pad, bn = t / p.cv_Ho;
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j) {
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes) {
                 const int col0 = n0 + j * EPR;
                 const bool in = col0 < p.cv_K;
                 const int tap = in ? col0 / p.cv_C : 0, ky = tap / p.cv_kw;
@@ -186,11 +192,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             } else {
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j)
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes)
                 tma_load_2d_pair(sb + j * MN_BOX_BYTES, &tmB, fb, n0 + j * EPR, kb * BLOCK_K);
             }
           } else {
-            mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+            mbar_expect_tx(&full_bar[s], stage_tx);
             if constexpr (!kAMN) {
               if (p.cv_on) {
                 const int tap = kb / p.cv_cpb, ky = tap / p.cv_kw;
@@ -210,13 +216,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const int tap = kb / p.cv_cpb, co0 = (kb - tap * p.cv_cpb) * BLOCK_K;
               const int wc0 = (p.cv_K - 1 - tap) * p.cv_C + n0;
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j)
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes)
                 tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], wc0 + j * EPR, co0);
             } else if (p.cv_on) {
               const int pix = kb * BLOCK_K, q = pix % p.cv_Wo, t = pix / p.cv_Wo;
               const int bw = q * p.cv_stride - p.cv_pad, bh = (t % p.cv_Ho) * p.cv_stride - p.cv_pad, bn = t / p.cv_Ho;
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j) {
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes) {
                 const int col0 = n0 + j * EPR;
                 const bool in = col0 < p.cv_K;
                 const int tap = in ? col0 / p.cv_C : 0, ky = tap / p.cv_kw;
@@ -225,7 +231,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             } else {
 #pragma unroll
-              for (int j = 0; j < B_ROWS / EPR; ++j)
+              for (int j = 0; j < B_ROWS / EPR; ++j) if (j < b_boxes)
                 tma_load_2d(sb + j * MN_BOX_BYTES, &tmB, &full_bar[s], n0 + j * EPR, kb * BLOCK_K);
             }
           }
@@ -776,6 +782,13 @@ static int gemm_ctas() {
   return v;
 }
 
+// UMMA N (and staged B rows) of a launch: 64 / 128 when the whole output is that narrow, else the full 256-wide tile
+static int pick_n_eff(int64_t N, int n_tiles) {
+  static const bool narrow = getenv("B200STEP_NARROW_MMA") == nullptr || atoi(getenv("B200STEP_NARROW_MMA")) != 0;
+  if (!narrow || n_tiles != 1) return BLOCK_N;
+  return N <= 64 ? 64 : (N <= 128 ? 128 : BLOCK_N);
+}
+
 // Launch on min(work items, available units) units, rounded down to a multiple of `unit_multiple`.
 template <int kTf32, bool kAMN, bool kBMN, int kEpi, int kCtas>
 static int launch_gemm_n(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
@@ -828,11 +841,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
                        cudaStream_t st, int unit_multiple = 1, int* units_out = nullptr) {
   GemmParams p = p_in;
   p.flags |= gemm_debug_flags();
-  if (p.n_eff == 0) {
-    static const bool narrow = getenv("B200STEP_NARROW_MMA") == nullptr || atoi(getenv("B200STEP_NARROW_MMA")) != 0;
-    p.n_eff = BLOCK_N;
-    if (narrow && p.n_tiles == 1) p.n_eff = p.N <= 64 ? 64 : (p.N <= 128 ? 128 : BLOCK_N);
-  }
+  if (p.n_eff == 0) p.n_eff = pick_n_eff(p.N, p.n_tiles);
   return gemm_ctas() == 2
              ? launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 2>(ta, tb, tc, p, st, unit_multiple, units_out)
              : launch_gemm_n<kTf32, kAMN, kBMN, kEpi, 1>(ta, tb, tc, p, st, unit_multiple, units_out);
@@ -855,8 +864,9 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
   const int tf32 = dtype == B200_F32;
   const int bk = tf32 ? 32 : 64;
   CUtensorMap ta, tb;
+  const int n_eff = pick_n_eff(N, (int)((N + BLOCK_N - 1) / BLOCK_N));
   if (int r = make_tmap(&ta, tf32, x, K, M, ldx, bk, BLOCK_M)) return r;
-  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, BLOCK_N / gemm_ctas())) return r;  // a pair splits the B tile
+  if (int r = make_tmap(&tb, tf32, w, K, N, ldw, bk, n_eff / gemm_ctas())) return r;  // a pair splits the B tile
   CUtensorMap tc;  // output slabs: one 128-byte row x 32 rows per TMA store
   if (int r = make_tmap(&tc, tf32, y, N, M, ldy, bk, 32, false, true)) return r;
   GemmParams p{};
@@ -866,7 +876,7 @@ extern "C" int b200_linear_fwd(const void* x, int64_t ldx, const void* w, int64_
   p.m_tiles = (int)((M + tile_m - 1) / tile_m);
   p.n_tiles = (int)((N + BLOCK_N - 1) / BLOCK_N);
   p.splits = 1; p.kb_per_split = p.k_blocks;
-  p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f;
+  p.out = y; p.ldo = ldy; p.bias = bias; p.flags = flags; p.dscale = 1.f; p.n_eff = n_eff;
   p.dropout_p = dropout_p; p.seed = seed; p.step = step; p.layer_id = layer_id;
   p.mask_out = relu_mask; p.ldmask = ldmask; p.row0 = dropout_row0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -905,8 +915,9 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y,
   if (int r = check_dims(M, Cout, K, dtype)) return r;
   B200_REQUIRE(ldw >= K, "conv_fwd: filter row stride %lld < kh*kw*C = %lld", (long long)ldw, (long long)K);
   CUtensorMap ta, tb, tc;
+  const int n_eff = pick_n_eff(Cout, (int)((Cout + BLOCK_N - 1) / BLOCK_N));
   if (int r = make_tmap_im2col(&ta, tf32, x, B, H, W, C, kh, kw, stride, pad, bk, BLOCK_M)) return r;
-  if (int r = make_tmap(&tb, tf32, w, K, Cout, ldw, bk, BLOCK_N / gemm_ctas())) return r;
+  if (int r = make_tmap(&tb, tf32, w, K, Cout, ldw, bk, n_eff / gemm_ctas())) return r;
   if (int r = make_tmap(&tc, tf32, y, Cout, M, ldy, bk, 32, false, true)) return r;
   GemmParams p{};
   p.M = (int)M; p.N = (int)Cout;
@@ -917,6 +928,7 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, int64_t ldw, void* y,
   p.splits = 1; p.kb_per_split = p.k_blocks;
   p.out = y; p.ldo = ldy; p.flags = flags & (B200_FLAG_RELU | B200_FLAG_REVERSE_M); p.dscale = 1.f;
   p.cv_on = 1; p.cv_Ho = Ho; p.cv_Wo = Wo; p.cv_stride = stride; p.cv_pad = pad; p.cv_kw = kw; p.cv_cpb = C / bk;
+  p.n_eff = n_eff;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int splits = (flags & B200_FLAG_RELU) ? 1 : conv_splits(p, flags);
   const bool ws_ok = tf32 ? (ldy % 4 == 0) : (ws != nullptr && ws_floats >= M * Cout && ldy == Cout &&
