@@ -140,6 +140,27 @@ def resnet_layout(arch: str = "resnet18", image: int = 32, num_classes: int = 10
     return lay
 
 
+def ddp_bucket_plan(lay: ResNetLayout, first_bucket_bytes: int = 1 << 20, bucket_cap_bytes: int = 25 << 20) -> List[List[str]]:
+    """DistributedDataParallel's gradient buckets for this model (task.py:189; torch/nn/parallel/distributed.py builds
+    them with `_compute_bucket_assignment_by_size(reversed(parameters), [1 MiB, bucket_cap_mb])`): parameters are taken in
+    reverse order — the order backward produces their gradients — and a bucket is closed as soon as its byte size
+    reaches the limit (1 MiB for the first, 25 MiB after).  Sizes are the TORCH sizes of the parameters.  Because the flat
+    buffer is in parameter order, every bucket is one contiguous range.  Checked against torch's own function in
+    tests/test_conv_oracle.py (ResNet-18: 3 buckets of 2 / 12 / 48 tensors = 2.05 / 28.9 / 15.9 MB)."""
+    plan: List[List[str]] = []
+    cur: List[str] = []
+    size = 0
+    for s in reversed(lay.params):
+        cur.append(s.key)
+        size += 4 * int(torch.Size(s.shape).numel())
+        if size >= (first_bucket_bytes if not plan else bucket_cap_bytes):
+            plan.append(cur)
+            cur, size = [], 0
+    if cur:
+        plan.append(cur)
+    return plan
+
+
 def filter_to_gemm(w: torch.Tensor, Kp: int) -> torch.Tensor:
     """torch OIHW -> Wg[Cout, Kp] with columns ordered (ky, kx, c) and zero padding."""
     o = w.shape[0]
@@ -464,20 +485,18 @@ class ConvTrainStep:
     def _make_buckets(self) -> None:
         """DDP's gradient buckets (task.py:189; reducer defaults: first bucket 1 MiB, then 25 MiB), filled in reverse
         parameter order = the order backward produces gradients.  A bucket is a contiguous range of the flat buffer."""
-        cfg, segs = self.cfg, self.lay.params
-        caps = [getattr(cfg, "first_bucket_bytes", 1 << 20), getattr(cfg, "bucket_cap_bytes", 25 << 20)]
+        cfg = self.cfg
+        plan = ddp_bucket_plan(self.lay, getattr(cfg, "first_bucket_bytes", 1 << 20),
+                               getattr(cfg, "bucket_cap_bytes", 25 << 20))
         self.buckets: List[List[int]] = []          # [start, end, params outstanding]
         self.bucket_of: Dict[str, int] = {}
-        end, count, size = self.lay.n_params, 0, 0
-        for i in range(len(segs) - 1, -1, -1):
-            s = segs[i]
-            self.bucket_of[s.key] = len(self.buckets)
-            count += 1
-            size += 4 * s.numel
-            cap = caps[0] if not self.buckets else caps[1]
-            if size >= cap or i == 0:
-                self.buckets.append([s.offset, end, count])
-                end, count, size = s.offset, 0, 0
+        end = self.lay.n_params
+        for keys in plan:
+            start = self.lay.seg(keys[-1]).offset       # keys run from the last parameter of the bucket to the first
+            for k in keys:
+                self.bucket_of[k] = len(self.buckets)
+            self.buckets.append([start, end, len(keys)])
+            end = start
         self._ev_ready = [torch.cuda.Event() for _ in self.buckets]
         self._ev_done = [torch.cuda.Event() for _ in self.buckets]
 

@@ -145,3 +145,33 @@ def test_vectorised_draws_equal_the_per_sample_torch_calls(seed, n):
         tail_b = (torch.randint(0, 1 << 30, (4,)), torch.rand(3), torch.randn(2))
         assert torch.equal(a, b) and torch.equal(a2, b2)
         assert all(torch.equal(x, y) for x, y in zip(tail_a, tail_b))
+
+
+@pytest.mark.parametrize("arch", ["resnet18", "resnet34"])
+def test_gradient_buckets_are_ddps_own(arch):
+    """The bucket plan the all-reduces follow is the one torch's DistributedDataParallel computes for the same model
+    (reducer defaults: 1 MiB first bucket, 25 MiB cap, parameters in reverse order)."""
+    import torchvision
+
+    from b200step.convnet import ddp_bucket_plan, resnet_layout
+
+    lay = resnet_layout(arch)
+    model = torchvision.models.__dict__[arch]()
+    named = list(model.named_parameters())
+    rev = list(reversed(named))
+    idx, _ = dist._compute_bucket_assignment_by_size([p for _, p in rev], [1024 * 1024, 25 * 1024 * 1024],
+                                                     [False] * len(rev), [])
+    ref = [[rev[i][0] for i in b] for b in idx]
+    plan = ddp_bucket_plan(lay)
+    assert plan == ref
+    if arch == "resnet18":
+        assert [len(b) for b in plan] == [2, 12, 48]
+    # every bucket is one contiguous range of the flat buffer, together they cover it
+    end = lay.n_params
+    for keys in plan:
+        segs = sorted((lay.seg(k) for k in keys), key=lambda s: s.offset)
+        assert segs[-1].offset + ((segs[-1].numel + 3) // 4) * 4 >= end - 3 and segs[-1].offset < end
+        for a, b in zip(segs, segs[1:]):
+            assert a.offset + ((a.numel + 3) // 4) * 4 == b.offset
+        end = segs[0].offset
+    assert end == 0
