@@ -127,3 +127,20 @@ def test_default_arch_resnet18_plans_the_reference_model():
     plan = json.loads([l for l in r.stdout.splitlines() if l.startswith("PLAN ")][0][5:])
     assert plan["arch"] == "resnet18" and plan["params"] == 11689512
     assert plan["samples_this_rank"] == 10000 and plan["batches_per_epoch"] == 10 and plan["last_batch_rows"] == 784
+
+
+def test_launcher_plan_world2_gloo_default_arch():
+    """The same two-process gloo launch with the reference's default model: resnet18 over the 10 000-image split, 5 000
+    images per rank in DistributedSampler order (task.py:63,256,260)."""
+    r = _run_task(["--dist-url", "env://", "--multiprocessing-distributed", "--dist-backend", "gloo", "--plan_only"],
+                  {"WORLD_SIZE": "1", "RANK": "0", "MASTER_PORT": "29553", "B200STEP_PLAN_GPUS": "2"})
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "=> creating model 'resnet18'" in r.stdout and "GPU x WORLD SIZE = 2" in r.stdout
+    plans = sorted((json.loads(m) for m in re.findall(r"PLAN (\{.*\})", r.stdout)), key=lambda p: p["rank"])
+    assert [p["rank"] for p in plans] == [0, 1]
+    from b200step.sampler import rank_indices
+
+    for p in plans:
+        assert p["arch"] == "resnet18" and p["params"] == 11689512 and p["world"] == 2
+        assert p["samples_this_rank"] == 5000 and p["batches_per_epoch"] == 5 and p["last_batch_rows"] == 5000 - 4 * 1024
+        assert p["first_indices"] == rank_indices(10000, 2, p["rank"])[:4].tolist()
